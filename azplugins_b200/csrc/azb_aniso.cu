@@ -1,0 +1,54 @@
+// TwoPatchMorse launcher (float and double; shift none/shift; virial on/off; tpp 1..32).
+#include "azb_aniso_kernel.cuh"
+#include "azb_launch.cuh"
+
+namespace azb
+    {
+template<class S, int SHIFT, bool VIRIAL> static int launch_aniso_variant(const azb_aniso_args& a, const void* d_params, cudaStream_t stream)
+    {
+    typedef TwoPatchMorse::Params<S> param_t;
+    typedef TwoPatchMorse::Coeff<S> coeff_t;
+    AnisoArgsDev<S> d;
+    d.pair = make_pair_args<S>(a.pair);
+    d.orientation = (const typename vec4<S>::type*)a.d_orientation;
+    d.torque = (typename vec4<S>::type*)a.d_torque;
+    const unsigned int tpp = pick_tpp(a.pair);
+    if (!valid_tpp(tpp))
+        return AZB_ERR_BAD_ARGUMENT;
+    const unsigned int block = pick_block(a.pair.block_size);
+    const unsigned int per_block = block / tpp;
+    const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
+    const size_t T2 = (size_t)a.pair.ntypes * a.pair.ntypes;
+    const size_t smem = T2 * (sizeof(coeff_t) + sizeof(S));
+    if (smem > 200 * 1024)
+        return AZB_ERR_BAD_ARGUMENT;
+#define AZB_CALL(TPP)                                                                           \
+    do                                                                                          \
+        {                                                                                       \
+        auto kern = aniso_force_kernel<S, SHIFT, VIRIAL, TPP>;                                  \
+        if (smem > 48 * 1024)                                                                   \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        kern<<<grid, block, smem, stream>>>(d, (const param_t*)d_params);                       \
+        } while (0)
+    AZB_DISPATCH_TPP(tpp, AZB_CALL)
+#undef AZB_CALL
+    return (int)cudaGetLastError();
+    }
+
+template<class S> int launch_aniso(const azb_aniso_args& a, const void* d_params, cudaStream_t stream)
+    {
+    if (a.pair.N == 0)
+        return 0;
+    if (!a.d_orientation || !a.d_torque)
+        return AZB_ERR_BAD_ARGUMENT;
+    const bool v = a.pair.compute_virial != 0;
+    // HOOMD's AnisoPotentialPair knows modes none and shift; TwoPatchMorse implements the shift (:122-125)
+    if (a.pair.shift_mode == AZB_SHIFT_SHIFT)
+        return v ? launch_aniso_variant<S, 1, true>(a, d_params, stream) : launch_aniso_variant<S, 1, false>(a, d_params, stream);
+    if (a.pair.shift_mode == AZB_SHIFT_NONE)
+        return v ? launch_aniso_variant<S, 0, true>(a, d_params, stream) : launch_aniso_variant<S, 0, false>(a, d_params, stream);
+    return AZB_ERR_BAD_ARGUMENT;
+    }
+template int launch_aniso<float>(const azb_aniso_args&, const void*, cudaStream_t);
+template int launch_aniso<double>(const azb_aniso_args&, const void*, cudaStream_t);
+    } // namespace azb

@@ -1,0 +1,195 @@
+// azb_aniso_kernel.cuh — anisotropic pair force + torque kernel for TwoPatchMorse (replaces HOOMD's
+// gpu_compute_pair_aniso_forces<E> as instantiated by /root/reference/src/AnisoPotentialPairGPUKernel.cu.inc:21-25;
+// per-pair math: /root/reference/src/AnisoPairEvaluatorTwoPatchMorse.h:127-216).
+//
+// The patch director n = rotate(q, e_x) depends on one particle only: n_i is computed once per particle, n_j once
+// per neighbour from the gathered quaternion. Energy shift U_M(r_cut) is hoisted into the per-type-pair table.
+#pragma once
+#include "azb_math.cuh"
+#include "azb_pair_kernel.cuh"
+
+namespace azb
+    {
+template<class S> struct AnisoArgsDev
+    {
+    PairArgsDev<S> pair;
+    const typename vec4<S>::type* orientation;
+    typename vec4<S>::type* torque;
+    };
+
+struct TwoPatchMorse
+    {
+    // AnisoPairEvaluatorTwoPatchMorse.h:63-68 — no alignment attribute: 5 Scalars + bool, padded to a Scalar multiple
+    template<class S> struct Params
+        {
+        S M_d, M_rinv, r_eq, omega, alpha;
+        bool repulsion;
+        };
+    template<class S> struct Coeff
+        {
+        S M_d, M_rinv, r_eq, omega, alpha, U_shift;
+        int repulsion;
+        };
+    template<class S> __device__ static Coeff<S> make(const Params<S>& p, S rcutsq, bool energy_shift)
+        {
+        Coeff<S> c;
+        c.M_d = p.M_d;
+        c.M_rinv = p.M_rinv;
+        c.r_eq = p.r_eq;
+        c.omega = p.omega;
+        c.alpha = p.alpha;
+        c.repulsion = p.repulsion ? 1 : 0;
+        c.U_shift = S(0);
+        if (energy_shift)
+            {
+            const S rcut = sqrt_(rcutsq);
+            const S ex = exp_(-(rcut - c.r_eq) * c.M_rinv);
+            const S om = S(1.0) - ex;
+            c.U_shift = c.M_d * (om * om - S(1.0));
+            }
+        return c;
+        }
+    };
+
+// rotate(quat(s, v), (1,0,0))
+template<class S, class Q> __device__ __forceinline__ void patch_director(const Q& q, S& nx, S& ny, S& nz)
+    {
+    const S s = q.x, vx = q.y, vy = q.z, vz = q.w;
+    nx = s * s - (vx * vx + vy * vy + vz * vz) + S(2) * vx * vx;
+    ny = S(2) * (s * vz + vx * vy);
+    nz = S(2) * (vx * vz - s * vy);
+    }
+
+template<class S, int SHIFT, bool VIRIAL, int TPP>
+__global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> d, const TwoPatchMorse::Params<S>* __restrict__ params)
+    {
+    typedef TwoPatchMorse::Coeff<S> coeff_t;
+    const PairArgsDev<S>& a = d.pair;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(smem_raw);
+    S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        {
+        const S rc = a.rcutsq[t];
+        s_coeff[t] = TwoPatchMorse::make(params[t], rc, SHIFT == 1);
+        s_rcutsq[t] = rc;
+        }
+    __syncthreads();
+
+    const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int idx = gtid / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    const bool active = idx < a.N;
+
+    S fx = S(0), fy = S(0), fz = S(0), pe = S(0), tx = S(0), ty = S(0), tz = S(0);
+    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    if (active)
+        {
+        const unsigned int nn = __ldg(a.n_neigh + idx);
+        const unsigned int* row = a.nlist + __ldg(a.head_list + idx);
+        const auto pi = ld4(a.pos + idx);
+        const auto qi = ld4(d.orientation + idx);
+        S nix, niy, niz;
+        patch_director<S>(qi, nix, niy, niz);
+        const unsigned int trow = type_of(pi.w) * a.ntypes;
+
+        for (unsigned int k = lane; k < nn; k += TPP)
+            {
+            const unsigned int j = __ldg(row + k);
+            const auto pj = ld4(a.pos + j);
+            S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            min_image(a.box, dx, dy, dz);
+            const S rsq = dx * dx + dy * dy + dz * dz;
+            const unsigned int tp = trow + type_of(pj.w);
+            if (!(rsq > s_rcutsq[tp])) // the evaluator rejects only rsq > rcutsq (strict), :135
+                {
+                const auto qj = ld4(d.orientation + j);
+                const coeff_t c = s_coeff[tp];
+                S njx, njy, njz;
+                patch_director<S>(qj, njx, njy, njz);
+                const S rinv = rsqrt_(rsq);
+                const S r = rsq * rinv;
+                const S ux = dx * rinv, uy = dy * rinv, uz = dz * rinv;
+
+                S UMorse = -c.M_d, dUMorse_dr = S(0);
+                if (r > c.r_eq || c.repulsion)
+                    {
+                    const S ex = exp_(-(r - c.r_eq) * c.M_rinv);
+                    const S om = S(1.0) - ex;
+                    UMorse = c.M_d * (om * om - S(1.0));
+                    dUMorse_dr = S(2.0) * c.M_d * c.M_rinv * ex * om;
+                    }
+                const S gi = ux * nix + uy * niy + uz * niz;
+                const S gi_exp = exp_(-c.omega * (gi * gi - c.alpha));
+                const S Oi = rcp(S(1.0) + gi_exp);
+                const S gj = ux * njx + uy * njy + uz * njz;
+                const S gj_exp = exp_(-c.omega * (gj * gj - c.alpha));
+                const S Oj = rcp(S(1.0) + gj_exp);
+
+                const S e = (UMorse - c.U_shift) * Oi * Oj;
+                const S dU_dr = dUMorse_dr * Oi * Oj;
+                const S dU_dgi = S(2.0) * c.omega * gi * gi_exp * Oi * Oi * UMorse * Oj;
+                const S dU_dgj = S(2.0) * c.omega * gj * gj_exp * Oj * Oj * UMorse * Oi;
+
+                // n_perp = -u x (u x n) = n - (u.n) u   (|u| = 1)
+                const S pix = nix - gi * ux, piy = niy - gi * uy, piz = niz - gi * uz;
+                const S pjx = njx - gj * ux, pjy = njy - gj * uy, pjz = njz - gj * uz;
+                const S Fx = -dU_dr * ux - rinv * (dU_dgi * pix + dU_dgj * pjx);
+                const S Fy = -dU_dr * uy - rinv * (dU_dgi * piy + dU_dgj * pjy);
+                const S Fz = -dU_dr * uz - rinv * (dU_dgi * piz + dU_dgj * pjz);
+                // t_i = dU_dgi (u x n_i)
+                tx += dU_dgi * (uy * niz - uz * niy);
+                ty += dU_dgi * (uz * nix - ux * niz);
+                tz += dU_dgi * (ux * niy - uy * nix);
+                fx += Fx;
+                fy += Fy;
+                fz += Fz;
+                pe += e;
+                if (VIRIAL)
+                    {
+                    vxx += S(0.5) * dx * Fx;
+                    vxy += S(0.5) * dy * Fx;
+                    vxz += S(0.5) * dz * Fx;
+                    vyy += S(0.5) * dy * Fy;
+                    vyz += S(0.5) * dz * Fy;
+                    vzz += S(0.5) * dz * Fz;
+                    }
+                }
+            }
+        }
+    if (TPP > 1)
+        {
+        fx = group_sum<TPP>(fx);
+        fy = group_sum<TPP>(fy);
+        fz = group_sum<TPP>(fz);
+        pe = group_sum<TPP>(pe);
+        tx = group_sum<TPP>(tx);
+        ty = group_sum<TPP>(ty);
+        tz = group_sum<TPP>(tz);
+        if (VIRIAL)
+            {
+            vxx = group_sum<TPP>(vxx);
+            vxy = group_sum<TPP>(vxy);
+            vxz = group_sum<TPP>(vxz);
+            vyy = group_sum<TPP>(vyy);
+            vyz = group_sum<TPP>(vyz);
+            vzz = group_sum<TPP>(vzz);
+            }
+        }
+    if (active && lane == 0)
+        {
+        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
+        st4(d.torque + idx, tx, ty, tz, S(0));
+        if (VIRIAL)
+            {
+            a.virial[0 * a.virial_pitch + idx] = vxx;
+            a.virial[1 * a.virial_pitch + idx] = vxy;
+            a.virial[2 * a.virial_pitch + idx] = vxz;
+            a.virial[3 * a.virial_pitch + idx] = vyy;
+            a.virial[4 * a.virial_pitch + idx] = vyz;
+            a.virial[5 * a.virial_pitch + idx] = vzz;
+            }
+        }
+    }
+    } // namespace azb

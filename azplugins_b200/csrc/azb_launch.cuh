@@ -1,0 +1,112 @@
+// azb_launch.cuh — host-side glue shared by the per-family translation units: converts the C-ABI argument
+// structs (include/azb200.h) into the typed device argument structs and picks launch shapes.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "azb200.h"
+#include "azb_math.cuh"
+#include "azb_pair_kernel.cuh"
+
+namespace azb
+    {
+template<class S> inline Box<S> make_box(const azb_box& b)
+    {
+    Box<S> o;
+    o.Lx = (S)b.Lx;
+    o.Ly = (S)b.Ly;
+    o.Lz = (S)b.Lz;
+    o.Lxinv = S(1.0) / o.Lx;
+    o.Lyinv = S(1.0) / o.Ly;
+    o.Lzinv = S(1.0) / o.Lz;
+    o.xy = (S)b.xy;
+    o.xz = (S)b.xz;
+    o.yz = (S)b.yz;
+    o.flags = (b.periodic[0] ? 1u : 0u) | (b.periodic[1] ? 2u : 0u) | (b.periodic[2] ? 4u : 0u);
+    if (b.xy != 0.0 || b.xz != 0.0 || b.yz != 0.0)
+        o.flags |= 8u;
+    return o;
+    }
+
+template<class S> inline PairArgsDev<S> make_pair_args(const azb_pair_args& a)
+    {
+    PairArgsDev<S> d;
+    d.force = (typename vec4<S>::type*)a.d_force;
+    d.virial = (S*)a.d_virial;
+    d.virial_pitch = a.virial_pitch;
+    d.N = a.N;
+    d.pos = (const typename vec4<S>::type*)a.d_pos;
+    d.box = make_box<S>(a.box);
+    d.n_neigh = a.d_n_neigh;
+    d.nlist = a.d_nlist;
+    d.head_list = a.d_head_list;
+    d.rcutsq = (const S*)a.d_rcutsq;
+    d.ronsq = (const S*)a.d_ronsq;
+    d.ntypes = a.ntypes;
+    return d;
+    }
+
+// threads cooperating on one particle: the caller's choice, else from the mean neighbour-row length
+inline unsigned int pick_tpp(const azb_pair_args& a)
+    {
+    unsigned int tpp = a.threads_per_particle;
+    if (tpp == 0)
+        {
+        const double nbar = a.N ? (double)a.size_nlist / (double)a.N : 0.0;
+        tpp = nbar <= 8 ? 1 : (nbar <= 24 ? 4 : (nbar <= 72 ? 8 : (nbar <= 200 ? 16 : 32)));
+        }
+    return tpp;
+    }
+inline bool valid_tpp(unsigned int tpp)
+    {
+    return tpp == 1 || tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16 || tpp == 32;
+    }
+inline unsigned int pick_block(unsigned int requested)
+    {
+    unsigned int b = requested ? requested : 128;
+    if (b < 32)
+        b = 32;
+    if (b > 256)
+        b = 256;
+    return (b / 32) * 32;
+    }
+
+inline int check_pair_args(const azb_pair_args* a)
+    {
+    if (!a || a->ntypes == 0 || a->shift_mode > 2)
+        return AZB_ERR_BAD_ARGUMENT;
+    if (a->N && (!a->d_force || !a->d_pos || !a->d_n_neigh || !a->d_nlist || !a->d_head_list || !a->d_rcutsq))
+        return AZB_ERR_BAD_ARGUMENT;
+    if (a->compute_virial && a->N && (!a->d_virial || a->virial_pitch < a->N))
+        return AZB_ERR_BAD_ARGUMENT;
+    if (a->shift_mode == AZB_SHIFT_XPLOR && !a->d_ronsq)
+        return AZB_ERR_BAD_ARGUMENT;
+    return 0;
+    }
+
+// Expands `CALL(TPPVALUE)` for the run-time tpp
+#define AZB_DISPATCH_TPP(tpp, CALL) \
+    switch (tpp)                    \
+        {                           \
+    case 1:                         \
+        CALL(1);                    \
+        break;                      \
+    case 2:                         \
+        CALL(2);                    \
+        break;                      \
+    case 4:                         \
+        CALL(4);                    \
+        break;                      \
+    case 8:                         \
+        CALL(8);                    \
+        break;                      \
+    case 16:                        \
+        CALL(16);                   \
+        break;                      \
+    default:                        \
+        CALL(32);                   \
+        break;                      \
+        }
+
+// Generic isotropic launcher: one instantiation set per (potential, scalar); defined in azb_pair_launch.cuh
+template<class Pot, class S> int launch_pair(const azb_pair_args& a, const void* d_params, cudaStream_t stream);
+    } // namespace azb

@@ -1,0 +1,159 @@
+// azb_math.cuh — scalar helpers for the sm_100a force kernels: vector loads of HOOMD Scalar4 arrays through the
+// read-only path, type-id decode, minimum image, and the float / double math flavours (the float flavour uses
+// the single-instruction MUFU approximations the way HOOMD's hoomd::fast:: does on the GPU; the double flavour is
+// IEEE).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace azb
+    {
+template<class S> struct vec4;
+template<> struct vec4<float>
+    {
+    typedef float4 type;
+    };
+struct alignas(32) double4a
+    {
+    double x, y, z, w;
+    };
+template<> struct vec4<double>
+    {
+    typedef double4a type;
+    };
+
+// ---- Scalar4 gathers ------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ld4(const float4* p)
+    {
+    return __ldg(p);
+    }
+__device__ __forceinline__ vec4<double>::type ld4(const vec4<double>::type* p)
+    {
+    // one 256-bit read-only load (sm_100+): ld.global.nc.v4.f64
+    vec4<double>::type r;
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+    return r;
+    }
+__device__ __forceinline__ void st4(float4* p, float x, float y, float z, float w)
+    {
+    *p = make_float4(x, y, z, w);
+    }
+__device__ __forceinline__ void st4(vec4<double>::type* p, double x, double y, double z, double w)
+    {
+    asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(x), "d"(y), "d"(z), "d"(w) : "memory");
+    }
+
+__device__ __forceinline__ unsigned int type_of(float w)
+    {
+    return (unsigned int)__float_as_int(w);
+    }
+__device__ __forceinline__ unsigned int type_of(double w)
+    {
+    return (unsigned int)__double_as_longlong(w);
+    }
+
+// ---- math flavours ----------------------------------------------------------------------------------
+__device__ __forceinline__ float rcp(float x)
+    {
+    return __fdividef(1.0f, x);
+    }
+__device__ __forceinline__ double rcp(double x)
+    {
+    return 1.0 / x;
+    }
+__device__ __forceinline__ float fdiv(float a, float b)
+    {
+    return __fdividef(a, b);
+    }
+__device__ __forceinline__ double fdiv(double a, double b)
+    {
+    return a / b;
+    }
+__device__ __forceinline__ float rsqrt_(float x)
+    {
+    return rsqrtf(x);
+    }
+__device__ __forceinline__ double rsqrt_(double x)
+    {
+    return rsqrt(x);
+    }
+__device__ __forceinline__ float sqrt_(float x)
+    {
+    return __fsqrt_rn(x);
+    }
+__device__ __forceinline__ double sqrt_(double x)
+    {
+    return sqrt(x);
+    }
+__device__ __forceinline__ float exp_(float x)
+    {
+    return __expf(x);
+    }
+__device__ __forceinline__ double exp_(double x)
+    {
+    return exp(x);
+    }
+__device__ __forceinline__ float log_(float x)
+    {
+    return logf(x);
+    }
+__device__ __forceinline__ double log_(double x)
+    {
+    return log(x);
+    }
+__device__ __forceinline__ float pow_(float x, float y)
+    {
+    return __powf(x, y);
+    }
+__device__ __forceinline__ double pow_(double x, double y)
+    {
+    return pow(x, y);
+    }
+__device__ __forceinline__ float rint_(float x)
+    {
+    return rintf(x);
+    }
+__device__ __forceinline__ double rint_(double x)
+    {
+    return rint(x);
+    }
+
+// ---- box ------------------------------------------------------------------------------------------------
+template<class S> struct Box
+    {
+    S Lx, Ly, Lz, Lxinv, Lyinv, Lzinv, xy, xz, yz;
+    unsigned int flags; // bit0..2 periodic x,y,z; bit3 = any tilt
+    };
+
+// BoxDim::minImage, GPU flavour: rint(w * Linv), z then y then x with tilt terms
+template<class S> __device__ __forceinline__ void min_image(const Box<S>& b, S& x, S& y, S& z)
+    {
+    if (b.flags & 8u)
+        {
+        if (b.flags & 4u)
+            {
+            const S img = rint_(z * b.Lzinv);
+            z -= b.Lz * img;
+            y -= b.Lz * b.yz * img;
+            x -= b.Lz * b.xz * img;
+            }
+        if (b.flags & 2u)
+            {
+            const S img = rint_(y * b.Lyinv);
+            y -= b.Ly * img;
+            x -= b.Ly * b.xy * img;
+            }
+        if (b.flags & 1u)
+            x -= b.Lx * rint_(x * b.Lxinv);
+        }
+    else
+        {
+        if (b.flags & 4u)
+            z -= b.Lz * rint_(z * b.Lzinv);
+        if (b.flags & 2u)
+            y -= b.Ly * rint_(y * b.Lyinv);
+        if (b.flags & 1u)
+            x -= b.Lx * rint_(x * b.Lxinv);
+        }
+    }
+    } // namespace azb

@@ -1,0 +1,153 @@
+// azb_pair_kernel.cuh — neighbour-list driven isotropic pair force kernel (replaces HOOMD's
+// gpu_compute_pair_forces<E> as instantiated by /root/reference/src/PotentialPairGPUKernel.cu.inc:25-28).
+//
+// Work decomposition: TPP lanes of a warp cooperate on one particle. Lane l walks neighbour-row entries
+// l, l+TPP, ...: the row read is a coalesced 4*TPP-byte segment, each entry is followed by one 16 B (float) or
+// 32 B (double) read-only gather of pos[j]. Per-type-pair coefficients (hoisted evaluator-constructor math and
+// the energy shift) live in shared memory. Force, energy and the six virial rows are reduced across the TPP
+// lanes with shuffles; lane 0 writes Scalar4 force (energy in .w) and the virial rows.
+#pragma once
+#include "azb_math.cuh"
+#include "azb_pair_potentials.cuh"
+
+namespace azb
+    {
+template<class S> struct PairArgsDev
+    {
+    typename vec4<S>::type* force;
+    S* virial;
+    size_t virial_pitch;
+    unsigned int N;
+    const typename vec4<S>::type* pos;
+    Box<S> box;
+    const unsigned int* n_neigh;
+    const unsigned int* nlist;
+    const size_t* head_list;
+    const S* rcutsq;
+    const S* ronsq;
+    unsigned int ntypes;
+    };
+
+template<int TPP, class S> __device__ __forceinline__ S group_sum(S v)
+    {
+#pragma unroll
+    for (int o = TPP / 2; o > 0; o >>= 1)
+        v += __shfl_down_sync(0xffffffffu, v, o, TPP);
+    return v;
+    }
+
+// SHIFT: 0 none, 1 shift, 2 xplor (azb_shift_mode)
+template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP>
+__global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a, const typename Pot::template Params<S>* __restrict__ params)
+    {
+    typedef typename Pot::template Coeff<S> coeff_t;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(smem_raw);
+    S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
+    S* s_ronsq = s_rcutsq + T2;
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        {
+        const S rc = a.rcutsq[t];
+        S ron = S(0);
+        bool energy_shift = (SHIFT == 1);
+        if (SHIFT == 2)
+            {
+            ron = a.ronsq[t];
+            energy_shift = ron > rc;
+            }
+        s_coeff[t] = Pot::make(params[t], rc, energy_shift);
+        s_rcutsq[t] = rc;
+        s_ronsq[t] = ron;
+        }
+    __syncthreads();
+
+    const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int idx = gtid / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    const bool active = idx < a.N;
+
+    S fx = S(0), fy = S(0), fz = S(0), pe = S(0);
+    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    if (active)
+        {
+        const unsigned int nn = __ldg(a.n_neigh + idx);
+        const unsigned int* row = a.nlist + __ldg(a.head_list + idx);
+        const auto pi = ld4(a.pos + idx);
+        const unsigned int trow = type_of(pi.w) * a.ntypes;
+
+        for (unsigned int k = lane; k < nn; k += TPP)
+            {
+            const unsigned int j = __ldg(row + k);
+            const auto pj = ld4(a.pos + j);
+            S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            min_image(a.box, dx, dy, dz);
+            const S rsq = dx * dx + dy * dy + dz * dz;
+            const unsigned int tp = trow + type_of(pj.w);
+            const S rcutsq = s_rcutsq[tp];
+            S fdivr = S(0), e = S(0);
+            if (Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
+                {
+                if (SHIFT == 2)
+                    {
+                    const S ronsq = s_ronsq[tp];
+                    if (rsq >= ronsq && rsq < rcutsq)
+                        {
+                        const S d = rcutsq - ronsq;
+                        const S denom_inv = S(1.0) / (d * d * d);
+                        const S q = rsq - rcutsq;
+                        const S s = q * q * (rcutsq + S(2.0) * rsq - S(3.0) * ronsq) * denom_inv;
+                        const S ds = S(12.0) * (rsq - ronsq) * q * denom_inv;
+                        const S old_e = e;
+                        e = old_e * s;
+                        fdivr = s * fdivr - ds * old_e;
+                        }
+                    }
+                fx += dx * fdivr;
+                fy += dy * fdivr;
+                fz += dz * fdivr;
+                pe += e;
+                if (VIRIAL)
+                    {
+                    const S h = S(0.5) * fdivr;
+                    vxx += h * dx * dx;
+                    vxy += h * dx * dy;
+                    vxz += h * dx * dz;
+                    vyy += h * dy * dy;
+                    vyz += h * dy * dz;
+                    vzz += h * dz * dz;
+                    }
+                }
+            }
+        }
+    if (TPP > 1)
+        {
+        fx = group_sum<TPP>(fx);
+        fy = group_sum<TPP>(fy);
+        fz = group_sum<TPP>(fz);
+        pe = group_sum<TPP>(pe);
+        if (VIRIAL)
+            {
+            vxx = group_sum<TPP>(vxx);
+            vxy = group_sum<TPP>(vxy);
+            vxz = group_sum<TPP>(vxz);
+            vyy = group_sum<TPP>(vyy);
+            vyz = group_sum<TPP>(vyz);
+            vzz = group_sum<TPP>(vzz);
+            }
+        }
+    if (active && lane == 0)
+        {
+        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
+        if (VIRIAL)
+            {
+            a.virial[0 * a.virial_pitch + idx] = vxx;
+            a.virial[1 * a.virial_pitch + idx] = vxy;
+            a.virial[2 * a.virial_pitch + idx] = vxz;
+            a.virial[3 * a.virial_pitch + idx] = vyy;
+            a.virial[4 * a.virial_pitch + idx] = vyz;
+            a.virial[5 * a.virial_pitch + idx] = vzz;
+            }
+        }
+    }
+    } // namespace azb

@@ -1,0 +1,56 @@
+// azb_pair_launch.cuh — definition of launch_pair<Pot, S>; included by the per-potential translation units so the
+// (shift mode x virial x tpp) kernel variants of different potentials compile in parallel.
+#pragma once
+#include "azb_launch.cuh"
+
+namespace azb
+    {
+template<class Pot, class S, int SHIFT, bool VIRIAL>
+static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cudaStream_t stream)
+    {
+    typedef typename Pot::template Params<S> param_t;
+    typedef typename Pot::template Coeff<S> coeff_t;
+    const PairArgsDev<S> d = make_pair_args<S>(a);
+    const unsigned int tpp = pick_tpp(a);
+    if (!valid_tpp(tpp))
+        return AZB_ERR_BAD_ARGUMENT;
+    const unsigned int block = pick_block(a.block_size);
+    const unsigned int per_block = block / tpp;
+    const unsigned int grid = (a.N + per_block - 1) / per_block;
+    const size_t T2 = (size_t)a.ntypes * a.ntypes;
+    const size_t smem = T2 * (sizeof(coeff_t) + 2 * sizeof(S));
+    if (smem > 200 * 1024)
+        return AZB_ERR_BAD_ARGUMENT;
+#define AZB_CALL(TPP)                                                                                                      \
+    do                                                                                                                     \
+        {                                                                                                                  \
+        auto kern = pair_force_kernel<Pot, S, SHIFT, VIRIAL, TPP>;                                                         \
+        if (smem > 48 * 1024)                                                                                              \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                            \
+        kern<<<grid, block, smem, stream>>>(d, (const param_t*)d_params);                                                  \
+        } while (0)
+    AZB_DISPATCH_TPP(tpp, AZB_CALL)
+#undef AZB_CALL
+    return (int)cudaGetLastError();
+    }
+
+template<class Pot, class S> int launch_pair(const azb_pair_args& a, const void* d_params, cudaStream_t stream)
+    {
+    if (a.N == 0)
+        return 0;
+    const bool v = a.compute_virial != 0;
+    switch (a.shift_mode)
+        {
+    case AZB_SHIFT_NONE:
+        return v ? launch_pair_variant<Pot, S, 0, true>(a, d_params, stream) : launch_pair_variant<Pot, S, 0, false>(a, d_params, stream);
+    case AZB_SHIFT_SHIFT:
+        return v ? launch_pair_variant<Pot, S, 1, true>(a, d_params, stream) : launch_pair_variant<Pot, S, 1, false>(a, d_params, stream);
+    default:
+        return v ? launch_pair_variant<Pot, S, 2, true>(a, d_params, stream) : launch_pair_variant<Pot, S, 2, false>(a, d_params, stream);
+        }
+    }
+    } // namespace azb
+
+#define AZB_INSTANTIATE_PAIR(Pot)                                                                              \
+    template int azb::launch_pair<azb::Pot, float>(const azb_pair_args&, const void*, cudaStream_t);         \
+    template int azb::launch_pair<azb::Pot, double>(const azb_pair_args&, const void*, cudaStream_t);

@@ -1,0 +1,213 @@
+/* azb200.h — C-ABI of the B200-native force-compute engine behind hoomd.azplugins.
+ *
+ * Every entry point replaces one explicit template instantiation that the reference stamps out of HOOMD's
+ * kernel drivers (C++-mangled, namespace hoomd::md::kernel, returning hipError_t):
+ *
+ *   azb_pair_forces   <- gpu_compute_pair_forces<PairEvaluatorX>(const pair_args_t&, const param_type*)
+ *                        /root/reference/src/PotentialPairGPUKernel.cu.inc:25-28
+ *   azb_dpd_forces    <- gpu_compute_dpd_forces<DPDPairEvaluatorGeneralWeight>(const dpd_pair_args_t&, ...)
+ *                        /root/reference/src/PotentialPairDPDThermoGPUKernel.cu.inc:21-24
+ *   azb_aniso_forces  <- gpu_compute_pair_aniso_forces<AnisoPairEvaluatorTwoPatchMorse>(const a_pair_args_t&,
+ *                        const param_type*, const shape_type*)
+ *                        /root/reference/src/AnisoPotentialPairGPUKernel.cu.inc:21-25
+ *   azb_bond_forces   <- gpu_compute_bond_forces<BondEvaluatorX, 2>(const bond_args_t<2>&, const param_type*,
+ *                        unsigned int* d_flags)   /root/reference/src/PotentialBondGPUKernel.cu.inc:25-29
+ *
+ * Conventions (HOOMD-blue v5 array layouts):
+ *  - "Scalar" is float (scalar_bits == 32) or double (scalar_bits == 64); Scalar4 is 4 packed Scalars.
+ *  - d_pos[i]   = (x, y, z, type bit-cast into .w: __int_as_float / __longlong_as_double of the int type id)
+ *  - d_vel[i]   = (vx, vy, vz, mass);  d_orientation[i] = quaternion (s, x, y, z)
+ *  - d_force[i] = (fx, fy, fz, potential energy of particle i);  d_torque[i] = (tx, ty, tz, 0)
+ *  - d_virial   = 6 rows (xx, xy, xz, yy, yz, zz) of virial_pitch Scalars
+ *  - neighbour list: FULL storage mode. d_n_neigh[i] entries at d_nlist[d_head_list[i] + k]; entries are
+ *    particle indices in [0, n_max) where indices >= N are ghosts (read, never written).
+ *  - d_params: device array of the reference's own parameter structs (same field order, size and
+ *    alignment as /root/reference/src/{Pair,AnisoPair,Bond,DPDPair}Evaluator<X>.h), indexed typei*ntypes+typej (pairs) or by bond type.
+ *  - All pointers named d_* are DEVICE pointers owned by the caller for the duration of the call. Outputs
+ *    are overwritten, not accumulated. Calls are asynchronous on `stream` (a cudaStream_t, NULL = default).
+ *  - Return value: 0 on success, otherwise a cudaError_t value (or AZB_ERR_* below). Nothing throws.
+ */
+#ifndef AZB200_H_
+#define AZB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AZB200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define AZB_API __attribute__((visibility("default")))
+#else
+#define AZB_API
+#endif
+
+/* error codes outside the cudaError_t range */
+#define AZB_ERR_BAD_POTENTIAL 10001
+#define AZB_ERR_BAD_SCALAR 10002
+#define AZB_ERR_BAD_ARGUMENT 10003
+
+/* isotropic pair potentials (evaluator getName() strings in comments) */
+enum azb_pair_potential
+    {
+    AZB_PAIR_PERTURBED_LENNARD_JONES = 0, /* "PerturbedLennardJones" */
+    AZB_PAIR_COLLOID = 1,                 /* "colloid" */
+    AZB_PAIR_EXPANDED_YUKAWA = 2,         /* "ExpandedYukawa" */
+    AZB_PAIR_HERTZ = 3,                   /* "hertz" */
+    AZB_PAIR_DPD_CONSERVATIVE = 4,        /* "dpd_gen" through evalForceAndEnergy (conservative only) */
+    AZB_PAIR_COUNT_ = 5
+    };
+enum azb_dpd_potential
+    {
+    AZB_DPD_GENERAL_WEIGHT = 0, /* "dpd_gen" through evalForceEnergyThermo */
+    AZB_DPD_COUNT_ = 1
+    };
+enum azb_aniso_potential
+    {
+    AZB_ANISO_TWO_PATCH_MORSE = 0, /* "TwoPatchMorse" */
+    AZB_ANISO_COUNT_ = 1
+    };
+enum azb_bond_potential
+    {
+    AZB_BOND_DOUBLE_WELL = 0, /* "DoubleWell" */
+    AZB_BOND_QUARTIC = 1,     /* "Quartic" */
+    AZB_BOND_COUNT_ = 2
+    };
+enum azb_shift_mode
+    {
+    AZB_SHIFT_NONE = 0,
+    AZB_SHIFT_SHIFT = 1,
+    AZB_SHIFT_XPLOR = 2
+    };
+enum azb_kind
+    {
+    AZB_KIND_PAIR = 0,
+    AZB_KIND_DPD = 1,
+    AZB_KIND_ANISO = 2,
+    AZB_KIND_BOND = 3
+    };
+
+/* Simulation box (HOOMD BoxDim): edge lengths, tilt factors, periodic flags. Always double here; the
+ * kernels convert to Scalar (L, Linv = 1/L) exactly as a Scalar-typed BoxDim would hold them. */
+typedef struct azb_box
+    {
+    double Lx, Ly, Lz;
+    double xy, xz, yz;
+    unsigned char periodic[3];
+    unsigned char pad_[5];
+    } azb_box;
+
+/* mirrors HOOMD pair_args_t */
+typedef struct azb_pair_args
+    {
+    void* d_force;                 /* Scalar4[N], overwritten */
+    void* d_virial;                /* Scalar[6*virial_pitch], overwritten when compute_virial */
+    size_t virial_pitch;           /* >= N */
+    unsigned int N;                /* local particles */
+    unsigned int n_max;            /* N + ghosts */
+    const void* d_pos;             /* Scalar4[n_max] */
+    const void* d_charge;          /* unused (needsCharge() == false for every azplugins evaluator) */
+    azb_box box;
+    const unsigned int* d_n_neigh; /* [N] */
+    const unsigned int* d_nlist;   /* [size_nlist] */
+    const size_t* d_head_list;     /* [N] */
+    const void* d_rcutsq;          /* Scalar[ntypes*ntypes] */
+    const void* d_ronsq;           /* Scalar[ntypes*ntypes] (xplor only; may be NULL otherwise) */
+    size_t size_nlist;
+    unsigned int ntypes;
+    unsigned int block_size;           /* 0 = engine default */
+    unsigned int shift_mode;           /* azb_shift_mode */
+    unsigned int compute_virial;       /* 0/1 */
+    unsigned int threads_per_particle; /* 0 = engine picks; else power of two <= 32 */
+    } azb_pair_args;
+
+/* mirrors HOOMD dpd_pair_args_t: pair args + velocities, tags, RNG key material, dt and kT */
+typedef struct azb_dpd_args
+    {
+    azb_pair_args pair;
+    const void* d_vel;         /* Scalar4[n_max] */
+    const unsigned int* d_tag; /* [n_max] */
+    uint16_t seed;             /* simulation seed */
+    uint64_t timestep;         /* truncated to 32 bits inside, as DPDPairEvaluatorGeneralWeight.h:122 does */
+    double deltaT;
+    double T;                  /* kT(timestep) */
+    } azb_dpd_args;
+
+/* mirrors HOOMD a_pair_args_t */
+typedef struct azb_aniso_args
+    {
+    azb_pair_args pair;
+    const void* d_orientation; /* Scalar4[n_max] */
+    void* d_torque;            /* Scalar4[N], overwritten */
+    const void* d_shape_params; /* unused: AnisoPairShapeParameters is empty */
+    } azb_aniso_args;
+
+/* mirrors HOOMD bond_args_t<2>. Table element (k-th bond of particle i) lives at [k*pitch + i]. */
+typedef struct azb_bond_group
+    {
+    unsigned int idx;  /* partner particle index (may be a ghost) */
+    unsigned int type; /* bond type id */
+    } azb_bond_group;
+
+typedef struct azb_bond_args
+    {
+    void* d_force;
+    void* d_virial;
+    size_t virial_pitch;
+    unsigned int N;
+    unsigned int n_max;
+    const void* d_pos;
+    const void* d_charge; /* unused */
+    azb_box box;
+    const azb_bond_group* d_gpu_bondlist; /* [max_bonds*pitch] */
+    const unsigned int* d_gpu_bond_pos;   /* [max_bonds*pitch] position of i inside the bond (unused by 2-body math) */
+    const unsigned int* d_gpu_n_bonds;    /* [N] */
+    unsigned int pitch;                   /* gpu_table_indexer width */
+    unsigned int max_bonds;               /* gpu_table_indexer height */
+    unsigned int n_bond_types;
+    unsigned int block_size;
+    unsigned int compute_virial; /* HOOMD's bond kernel always writes the virial; 0 skips the store */
+    } azb_bond_args;
+
+AZB_API int azb_abi_version(void);
+
+/* sizeof / alignof of the reference's param struct for (kind, potential, scalar_bits); 0 if unknown */
+AZB_API size_t azb_param_size(int kind, int potential, int scalar_bits);
+AZB_API size_t azb_param_align(int kind, int potential, int scalar_bits);
+/* evaluator getName() string, NULL if unknown */
+AZB_API const char* azb_potential_name(int kind, int potential);
+
+AZB_API int azb_pair_forces(int potential,
+                    int scalar_bits,
+                    const azb_pair_args* args,
+                    const void* d_params,
+                    void* stream);
+
+AZB_API int azb_dpd_forces(int potential,
+                   int scalar_bits,
+                   const azb_dpd_args* args,
+                   const void* d_params,
+                   void* stream);
+
+AZB_API int azb_aniso_forces(int potential,
+                     int scalar_bits,
+                     const azb_aniso_args* args,
+                     const void* d_params,
+                     void* stream);
+
+/* *d_flags is set non-zero by the kernel when an evaluator rejects its parameters (DoubleWell r_0 == r_1,
+ * Quartic r_0 == 0); the host class throws after the call, as HOOMD's PotentialBondGPU does. */
+AZB_API int azb_bond_forces(int potential,
+                    int scalar_bits,
+                    const azb_bond_args* args,
+                    const void* d_params,
+                    unsigned int* d_flags,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AZB200_H_ */
