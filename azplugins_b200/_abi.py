@@ -1,0 +1,158 @@
+"""ctypes mirror of ``include/azb200.h`` and the loader of the CUDA library.
+
+The structures here are field-for-field the C structs of the drop-in boundary; the product library
+(``libazb200.so``, hand-written sm_100a kernels) is loaded from the package directory and nothing else is ever
+substituted for it: if it is missing, importing a force class fails loudly.
+"""
+
+import ctypes as C
+import os
+
+ABI_VERSION = 1
+
+ERR_BAD_POTENTIAL = 10001
+ERR_BAD_SCALAR = 10002
+ERR_BAD_ARGUMENT = 10003
+
+KIND_PAIR, KIND_DPD, KIND_ANISO, KIND_BOND = 0, 1, 2, 3
+PAIR_PERTURBED_LENNARD_JONES, PAIR_COLLOID, PAIR_EXPANDED_YUKAWA, PAIR_HERTZ, PAIR_DPD_CONSERVATIVE = range(5)
+DPD_GENERAL_WEIGHT = 0
+ANISO_TWO_PATCH_MORSE = 0
+BOND_DOUBLE_WELL, BOND_QUARTIC = 0, 1
+SHIFT_NONE, SHIFT_SHIFT, SHIFT_XPLOR = 0, 1, 2
+
+
+class Box(C.Structure):
+    _fields_ = [
+        ("Lx", C.c_double),
+        ("Ly", C.c_double),
+        ("Lz", C.c_double),
+        ("xy", C.c_double),
+        ("xz", C.c_double),
+        ("yz", C.c_double),
+        ("periodic", C.c_ubyte * 3),
+        ("pad_", C.c_ubyte * 5),
+    ]
+
+
+class PairArgs(C.Structure):
+    _fields_ = [
+        ("d_force", C.c_void_p),
+        ("d_virial", C.c_void_p),
+        ("virial_pitch", C.c_size_t),
+        ("N", C.c_uint),
+        ("n_max", C.c_uint),
+        ("d_pos", C.c_void_p),
+        ("d_charge", C.c_void_p),
+        ("box", Box),
+        ("d_n_neigh", C.c_void_p),
+        ("d_nlist", C.c_void_p),
+        ("d_head_list", C.c_void_p),
+        ("d_rcutsq", C.c_void_p),
+        ("d_ronsq", C.c_void_p),
+        ("size_nlist", C.c_size_t),
+        ("ntypes", C.c_uint),
+        ("block_size", C.c_uint),
+        ("shift_mode", C.c_uint),
+        ("compute_virial", C.c_uint),
+        ("threads_per_particle", C.c_uint),
+    ]
+
+
+class DPDArgs(C.Structure):
+    _fields_ = [
+        ("pair", PairArgs),
+        ("d_vel", C.c_void_p),
+        ("d_tag", C.c_void_p),
+        ("seed", C.c_uint16),
+        ("timestep", C.c_uint64),
+        ("deltaT", C.c_double),
+        ("T", C.c_double),
+    ]
+
+
+class AnisoArgs(C.Structure):
+    _fields_ = [
+        ("pair", PairArgs),
+        ("d_orientation", C.c_void_p),
+        ("d_torque", C.c_void_p),
+        ("d_shape_params", C.c_void_p),
+    ]
+
+
+class BondArgs(C.Structure):
+    _fields_ = [
+        ("d_force", C.c_void_p),
+        ("d_virial", C.c_void_p),
+        ("virial_pitch", C.c_size_t),
+        ("N", C.c_uint),
+        ("n_max", C.c_uint),
+        ("d_pos", C.c_void_p),
+        ("d_charge", C.c_void_p),
+        ("box", Box),
+        ("d_gpu_bondlist", C.c_void_p),
+        ("d_gpu_bond_pos", C.c_void_p),
+        ("d_gpu_n_bonds", C.c_void_p),
+        ("pitch", C.c_uint),
+        ("max_bonds", C.c_uint),
+        ("n_bond_types", C.c_uint),
+        ("block_size", C.c_uint),
+        ("compute_virial", C.c_uint),
+    ]
+
+
+# every symbol include/azb200.h declares (tests check the library exports exactly these)
+EXPORTS = (
+    "azb_abi_version",
+    "azb_param_size",
+    "azb_param_align",
+    "azb_potential_name",
+    "azb_pair_forces",
+    "azb_dpd_forces",
+    "azb_aniso_forces",
+    "azb_bond_forces",
+)
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
+
+_lib = None
+
+
+def load():
+    """Load ``libazb200.so`` (built by ``__graft_entry__.build()`` / ``make -C azplugins_b200/csrc``)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA extension has not been built "
+            "(run `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    lib.azb_abi_version.restype = C.c_int
+    lib.azb_param_size.restype = C.c_size_t
+    lib.azb_param_size.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.azb_param_align.restype = C.c_size_t
+    lib.azb_param_align.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.azb_potential_name.restype = C.c_char_p
+    lib.azb_potential_name.argtypes = [C.c_int, C.c_int]
+    lib.azb_pair_forces.restype = C.c_int
+    lib.azb_pair_forces.argtypes = [C.c_int, C.c_int, C.POINTER(PairArgs), C.c_void_p, C.c_void_p]
+    lib.azb_dpd_forces.restype = C.c_int
+    lib.azb_dpd_forces.argtypes = [C.c_int, C.c_int, C.POINTER(DPDArgs), C.c_void_p, C.c_void_p]
+    lib.azb_aniso_forces.restype = C.c_int
+    lib.azb_aniso_forces.argtypes = [C.c_int, C.c_int, C.POINTER(AnisoArgs), C.c_void_p, C.c_void_p]
+    lib.azb_bond_forces.restype = C.c_int
+    lib.azb_bond_forces.argtypes = [C.c_int, C.c_int, C.POINTER(BondArgs), C.c_void_p, C.c_void_p, C.c_void_p]
+    if lib.azb_abi_version() != ABI_VERSION:
+        raise ImportError("libazb200.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(code, what):
+    """Turn a C-ABI return code into an exception (the ABI itself never throws)."""
+    if code == 0:
+        return
+    names = {ERR_BAD_POTENTIAL: "unknown potential id", ERR_BAD_SCALAR: "scalar_bits must be 32 or 64", ERR_BAD_ARGUMENT: "bad argument"}
+    raise RuntimeError(f"{what} failed: {names.get(code, 'cudaError_t ' + str(code))}")

@@ -1,0 +1,322 @@
+"""Host classes that call the C-ABI — the B200 stand-ins for HOOMD's ``PotentialPairGPU<E>``,
+``PotentialPairDPDThermoGPU<E>``, ``AnisoPotentialPairGPU<E>`` and ``PotentialBondGPU<E, BondData>`` (the templates
+the reference instantiates in /root/reference/src/export_*GPU.cc.inc) plus the slice of ``hoomd.md.pair.Pair`` /
+``hoomd.md.bond.Bond`` their Python classes inherit: ``params`` / ``r_cut`` / ``r_on`` type parameters, ``mode``,
+``forces`` / ``energies`` / ``torques`` / ``virials`` / ``energy``.
+
+Per ``compute(timestep)`` exactly one kernel launch is issued through ``azb_*_forces``; outputs are overwritten.
+There is no CPU path: a state that does not live on a CUDA device raises.
+"""
+
+import ctypes as C
+import itertools
+
+import numpy as np
+import torch
+
+from . import _abi
+from .state import scalar_dtype
+
+
+class TypeParameter(dict):
+    """``params[(a, b)] = dict(...)`` store with hoomd's symmetric pair keys and schema validation."""
+
+    def __init__(self, owner, validate, pairwise):
+        super().__init__()
+        self._owner, self._validate, self._pairwise = owner, validate, pairwise
+
+    def _keys(self, key):
+        if not self._pairwise:
+            return [key]
+        a, b = key
+        a_list = [a] if isinstance(a, str) else list(a)
+        b_list = [b] if isinstance(b, str) else list(b)
+        return [tuple(sorted(k)) for k in itertools.product(a_list, b_list)]
+
+    def __setitem__(self, key, value):
+        for k in self._keys(key):
+            super().__setitem__(k, self._validate(value))
+        self._owner._dirty = True
+
+    def __getitem__(self, key):
+        return super().__getitem__(self._keys(key)[0])
+
+
+class Force:
+    """Common output handling (``hoomd.md.force.Force`` loggables)."""
+
+    _kind = None
+
+    def __init__(self):
+        self._dirty = True
+        self._state = None
+        self._force = None
+        self._virial = None
+        self._torque = None
+        self.compute_virial = True  # HOOMD sets this from the pressure_tensor flag each step
+        self.block_size = 0
+        self.threads_per_particle = 0
+        self.launches = 0
+
+    def _attach(self, state):
+        if state.device.type != "cuda":
+            raise RuntimeError("azplugins_b200 forces run on a CUDA device only (no CPU fallback)")
+        self._lib = _abi.load()
+        self._state = state
+        _, _, td = scalar_dtype(state.scalar_bits)
+        self._force = torch.zeros((state.N, 4), dtype=td, device=state.device)
+        self._virial = torch.zeros((6, max(state.N, 1)), dtype=td, device=state.device)
+        self._dirty = True
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self._state.device).cuda_stream)
+
+    # ---- loggables -----------------------------------------------------------------------------------------
+    @property
+    def forces(self):
+        return self._force[:, :3].cpu().numpy()
+
+    @property
+    def energies(self):
+        return self._force[:, 3].cpu().numpy()
+
+    @property
+    def energy(self):
+        return float(self._force[:, 3].double().sum().item())
+
+    @property
+    def virials(self):
+        return self._virial[:, : self._state.N].T.cpu().numpy()
+
+    @property
+    def torques(self):
+        if self._torque is None:
+            return np.zeros((self._state.N, 3))
+        return self._torque[:, :3].cpu().numpy()
+
+
+class Pair(Force):
+    """Isotropic pair force over a neighbour list (``hoomd.md.pair.Pair`` + ``PotentialPairGPU<E>``)."""
+
+    _spec = None
+    _accepted_modes = ("none", "shift", "xplor")
+    _kind = _abi.KIND_PAIR
+
+    def __init__(self, nlist, default_r_cut=None, default_r_on=0.0, mode="none"):
+        super().__init__()
+        if mode not in self._accepted_modes:
+            raise ValueError(f"mode must be one of {self._accepted_modes}")
+        self.mode = mode
+        self.nlist = nlist
+        self.params = TypeParameter(self, self._spec.validate, True)
+        self.r_cut = TypeParameter(self, float, True)
+        self.r_on = TypeParameter(self, float, True)
+        self._default_r_cut = default_r_cut
+        self._default_r_on = default_r_on
+        nlist._subscribe(self)
+
+    @property
+    def _cpp_class_name(self):
+        return self._spec.cpp_class
+
+    def _pair_value(self, store, a, b, default):
+        key = tuple(sorted((a, b)))
+        if dict.__contains__(store, key):
+            return dict.__getitem__(store, key)
+        if default is None:
+            raise KeyError(f"{type(self).__name__}: no value set for type pair {key}")
+        return default
+
+    def _r_cut_matrix(self, types):
+        T = len(types)
+        r = np.zeros((T, T))
+        for i, a in enumerate(types):
+            for j, b in enumerate(types):
+                r[i, j] = self._pair_value(self.r_cut, a, b, self._default_r_cut)
+        return r
+
+    def _tables(self):
+        """Device tables indexed typei*T+typej: param structs, rcutsq, ronsq (symmetric fill)."""
+        st = self._state
+        types = st.types
+        T = len(types)
+        ftype = scalar_dtype(st.scalar_bits)[0]
+        dt = self._spec.dtype(st.scalar_bits)
+        par = np.zeros(T * T, dtype=dt)
+        rc = self._r_cut_matrix(types)
+        ron = np.zeros((T, T))
+        for i, a in enumerate(types):
+            for j, b in enumerate(types):
+                par[i * T + j] = self._spec.pack(self._pair_value(self.params, a, b, None), st.scalar_bits)
+                ron[i, j] = self._pair_value(self.r_on, a, b, self._default_r_on)
+        rcs = (rc.astype(ftype) * rc.astype(ftype)).reshape(-1)
+        rons = (ron.astype(ftype) * ron.astype(ftype)).reshape(-1)
+        self._d_params = torch.from_numpy(par.view(np.uint8).copy()).to(st.device)
+        self._d_rcutsq = torch.from_numpy(rcs).to(st.device)
+        self._d_ronsq = torch.from_numpy(rons).to(st.device)
+        self._dirty = False
+
+    def _fill_pair_args(self, a):
+        st, nl = self._state, self.nlist
+        a.d_force = self._force.data_ptr()
+        a.d_virial = self._virial.data_ptr()
+        a.virial_pitch = self._virial.shape[1]
+        a.N = st.N
+        a.n_max = st.n_max
+        a.d_pos = st.pos.data_ptr()
+        a.d_charge = None
+        a.box = st.box.as_abi()
+        a.d_n_neigh = nl.n_neigh.data_ptr()
+        a.d_nlist = nl.nlist.data_ptr()
+        a.d_head_list = nl.head_list.data_ptr()
+        a.d_rcutsq = self._d_rcutsq.data_ptr()
+        a.d_ronsq = self._d_ronsq.data_ptr()
+        a.size_nlist = nl.size_nlist
+        a.ntypes = len(st.types)
+        a.block_size = self.block_size
+        a.shift_mode = {"none": _abi.SHIFT_NONE, "shift": _abi.SHIFT_SHIFT, "xplor": _abi.SHIFT_XPLOR}[self.mode]
+        a.compute_virial = 1 if self.compute_virial else 0
+        a.threads_per_particle = self.threads_per_particle
+
+    def compute(self, timestep=0):
+        if self._state is None:
+            raise RuntimeError("force is not attached to a state")
+        self.nlist.compute(self._state)
+        if self._dirty:
+            self._tables()
+        args = _abi.PairArgs()
+        self._fill_pair_args(args)
+        code = self._lib.azb_pair_forces(self._spec.potential_id, self._state.scalar_bits, C.byref(args),
+                                         self._d_params.data_ptr(), self._stream())
+        _abi.check(code, f"azb_pair_forces[{self._spec.name}]")
+        self.launches += 1
+
+
+class DPDThermoPair(Pair):
+    """``PotentialPairDPDThermoGPU<E>``: pair force + velocity/tag gathers + Philox random force."""
+
+    _accepted_modes = ("none",)
+    _kind = _abi.KIND_DPD
+
+    def __init__(self, nlist, kT, default_r_cut=None):
+        super().__init__(nlist, default_r_cut, 0.0, "none")
+        self.kT = kT
+        self.dt = 0.005  # set by the integrator (hoomd passes m_deltaT to the force)
+
+    def _kT_at(self, timestep):
+        return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)
+
+    def compute(self, timestep=0):
+        if self._state is None:
+            raise RuntimeError("force is not attached to a state")
+        st = self._state
+        self.nlist.compute(st)
+        if self._dirty:
+            self._tables()
+        args = _abi.DPDArgs()
+        self._fill_pair_args(args.pair)
+        args.d_vel = st.vel.data_ptr()
+        args.d_tag = st.tag.data_ptr()
+        args.seed = st.seed
+        args.timestep = int(timestep)
+        args.deltaT = float(self.dt)
+        args.T = self._kT_at(timestep)
+        code = self._lib.azb_dpd_forces(self._spec.potential_id, st.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
+        _abi.check(code, f"azb_dpd_forces[{self._spec.name}]")
+        self.launches += 1
+
+
+class AnisotropicPair(Pair):
+    """``AnisoPotentialPairGPU<E>``: force + torque (``hoomd.md.pair.aniso.AnisotropicPair``)."""
+
+    _accepted_modes = ("none", "shift")
+    _kind = _abi.KIND_ANISO
+
+    def __init__(self, nlist, default_r_cut=None, mode="none"):
+        super().__init__(nlist, default_r_cut, 0.0, mode)
+
+    def _attach(self, state):
+        super()._attach(state)
+        self._torque = torch.zeros((state.N, 4), dtype=self._force.dtype, device=state.device)
+
+    def compute(self, timestep=0):
+        if self._state is None:
+            raise RuntimeError("force is not attached to a state")
+        st = self._state
+        self.nlist.compute(st)
+        if self._dirty:
+            self._tables()
+        args = _abi.AnisoArgs()
+        self._fill_pair_args(args.pair)
+        args.d_orientation = st.orientation.data_ptr()
+        args.d_torque = self._torque.data_ptr()
+        args.d_shape_params = None
+        code = self._lib.azb_aniso_forces(self._spec.potential_id, st.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
+        _abi.check(code, f"azb_aniso_forces[{self._spec.name}]")
+        self.launches += 1
+
+
+class Bond(Force):
+    """``PotentialBondGPU<E, BondData>`` (``hoomd.md.bond.Bond``)."""
+
+    _spec = None
+    _kind = _abi.KIND_BOND
+
+    def __init__(self):
+        super().__init__()
+        self.params = TypeParameter(self, self._spec.validate, False)
+
+    @property
+    def _cpp_class_name(self):
+        return self._spec.cpp_class
+
+    def _attach(self, state):
+        super()._attach(state)
+        self._flags = torch.zeros(1, dtype=torch.int32, device=state.device)
+
+    def _tables(self):
+        st = self._state
+        dt = self._spec.dtype(st.scalar_bits)
+        par = np.zeros(max(len(st.bond_types), 1), dtype=dt)
+        for i, name in enumerate(st.bond_types):
+            if not dict.__contains__(self.params, name):
+                raise KeyError(f"{type(self).__name__}: no parameters set for bond type {name!r}")
+            par[i] = self._spec.pack(dict.__getitem__(self.params, name), st.scalar_bits)
+        self._d_params = torch.from_numpy(par.view(np.uint8).copy()).to(st.device)
+        self._dirty = False
+
+    def compute(self, timestep=0):
+        if self._state is None:
+            raise RuntimeError("force is not attached to a state")
+        st = self._state
+        if self._dirty:
+            self._tables()
+        tb = st.bond_table()
+        a = _abi.BondArgs()
+        a.d_force = self._force.data_ptr()
+        a.d_virial = self._virial.data_ptr()
+        a.virial_pitch = self._virial.shape[1]
+        a.N = st.N
+        a.n_max = st.n_max
+        a.d_pos = st.pos.data_ptr()
+        a.d_charge = None
+        a.box = st.box.as_abi()
+        a.d_gpu_bondlist = tb["bondlist"].data_ptr()
+        a.d_gpu_bond_pos = tb["bond_pos"].data_ptr()
+        a.d_gpu_n_bonds = tb["n_bonds"].data_ptr()
+        a.pitch = tb["pitch"]
+        a.max_bonds = tb["max_bonds"]
+        a.n_bond_types = max(len(st.bond_types), 1)
+        a.block_size = self.block_size
+        a.compute_virial = 1 if self.compute_virial else 0
+        self._flags.zero_()
+        code = self._lib.azb_bond_forces(self._spec.potential_id, st.scalar_bits, C.byref(a), self._d_params.data_ptr(),
+                                         self._flags.data_ptr(), self._stream())
+        _abi.check(code, f"azb_bond_forces[{self._spec.name}]")
+        self.launches += 1
+        return self
+
+    def check_flags(self):
+        """Host-side error check HOOMD's PotentialBondGPU performs after the kernel (device flag -> exception)."""
+        if int(self._flags.item()) != 0:
+            raise RuntimeError(f"bond.{self._spec.name}: bond out of bounds / invalid parameters")

@@ -1,0 +1,72 @@
+"""Neighbour lists in HOOMD-blue's array layout (``n_neigh`` u32, ``head_list`` size_t, ``nlist`` u32; FULL mode).
+
+``Cell`` mirrors ``hoomd.md.nlist.Cell(buffer=..., exclusions=('bond',))`` as used by every reference test
+(/root/reference/src/pytest/test_pair.py:337). The list itself is what the force kernels consume through
+``pair_args_t`` (SURVEY.md §8 b); how it is produced is outside the reference (HOOMD's NeighborListGPU*).
+"""
+
+import numpy as np
+import torch
+
+
+class NeighborList:
+    """Device arrays of one neighbour list plus the per-type-pair r_cut bookkeeping of its consumers."""
+
+    def __init__(self, buffer=0.4, exclusions=("bond",)):
+        self.buffer = float(buffer)
+        self.exclusions = tuple(exclusions)
+        self._consumers = []
+        self.n_neigh = None
+        self.head_list = None
+        self.nlist = None
+        self.size_nlist = 0
+        self._state = None
+
+    # consumers (pair forces) register so the list covers max r_cut per type pair, like hoomd's nlist subscribers
+    def _subscribe(self, force):
+        if force not in self._consumers:
+            self._consumers.append(force)
+            self.invalidate()
+
+    def invalidate(self):
+        self.n_neigh = None
+
+    def r_list(self, types):
+        """(T,T) matrix of r_cut_max + buffer over all consumers; 0 where no consumer interacts."""
+        T = len(types)
+        r = np.zeros((T, T))
+        for f in self._consumers:
+            r = np.maximum(r, f._r_cut_matrix(types))
+        return np.where(r > 0, r + self.buffer, 0.0)
+
+    def set_arrays(self, n_neigh, head_list, nlist, device):
+        """Adopt externally built arrays (numpy, HOOMD layout)."""
+        n_neigh = np.ascontiguousarray(n_neigh, dtype=np.uint32)
+        head_list = np.ascontiguousarray(head_list, dtype=np.uint64)
+        nlist = np.ascontiguousarray(nlist, dtype=np.uint32)
+        self.n_neigh = torch.from_numpy(n_neigh.view(np.int32)).to(device)
+        self.head_list = torch.from_numpy(head_list.view(np.int64)).to(device)
+        self.nlist = torch.from_numpy(nlist.view(np.int32) if nlist.size else np.zeros(1, np.int32)).to(device)
+        self.size_nlist = int(nlist.size)
+        return self
+
+    def compute(self, state):
+        if self.n_neigh is None or self._state is not state:
+            self.build(state)
+            self._state = state
+        return self
+
+    def build(self, state):
+        raise RuntimeError("this NeighborList has no builder: use nlist.Cell or set_arrays()")
+
+    def mean_neighbors(self, N):
+        return self.size_nlist / max(N, 1)
+
+
+class Cell(NeighborList):
+    """Cell-list neighbour list built on the GPU (``hoomd.md.nlist.Cell``)."""
+
+    def build(self, state):
+        from . import _nlist_gpu
+
+        _nlist_gpu.build_cell_nlist(self, state)
