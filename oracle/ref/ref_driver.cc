@@ -10,7 +10,7 @@
 // BondEvaluator.h:62,84).
 //
 // Compiled twice (HOOMD_LONGREAL_SIZE = 32 and 64) with AZREF_PREFIX = azref32 / azref64 and linked into
-// one oracle/_ref/libazref.so. Arrays use the exact layouts of include/azb200.h but with HOST pointers.
+// oracle/_ref/libazref32.so and libazref64.so (separately: the class names are identical in both builds). Arrays use the exact layouts of include/azb200.h but with HOST pointers.
 #include <pybind11/pybind11.h>
 
 #include <cstring>

@@ -1,7 +1,7 @@
 """Test-side access to the CPU oracles (tests/ is one of the few places allowed to load anything under oracle/).
 
 ``port``: oracle/_build/libazoracle.so — the plain-C restatement (always buildable: gcc only).
-``ref`` : oracle/_ref/libazref.so — the reference's evaluator headers compiled unmodified (built in the container
+``ref`` : oracle/_ref/libazref{32,64}.so — the reference's evaluator headers compiled unmodified (built in the container
           where /root/reference exists; the prebuilt .so travels to the GPU box).
 
 Both take the structs of include/azb200.h with HOST pointers; this module fills them from numpy arrays.
@@ -10,6 +10,7 @@ Both take the structs of include/azb200.h with HOST pointers; this module fills 
 import ctypes as C
 import os
 import subprocess
+import types
 
 import numpy as np
 
@@ -18,7 +19,7 @@ from azplugins_b200.state import pack_scalar4, scalar_dtype
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PORT_PATH = os.path.join(ROOT, "oracle", "_build", "libazoracle.so")
-REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libazref.so")
+REF_PATHS = {b: os.path.join(ROOT, "oracle", "_ref", f"libazref{b}.so") for b in (32, 64)}
 
 _port = None
 _ref = None
@@ -53,15 +54,19 @@ def port():
 
 
 def have_ref():
-    return os.path.exists(REF_PATH)
+    return all(os.path.exists(p) for p in REF_PATHS.values())
 
 
 def ref():
     global _ref
     if _ref is None:
-        lib = C.PyDLL(REF_PATH)  # keeps the GIL: make_params / params_as_dict touch Python objects
+        lib = types.SimpleNamespace()
         for bits in (32, 64):
+            # PyDLL keeps the GIL: make_params / params_as_dict touch Python objects. One library per precision.
+            dll = C.PyDLL(REF_PATHS[bits])
             p = f"azref{bits}_"
+            for name in ("pair_forces", "dpd_forces", "aniso_forces", "bond_forces", "dpd_alpha", "param_size", "make_params", "params_as_dict"):
+                setattr(lib, p + name, getattr(dll, p + name))
             for name in ("pair_forces", "dpd_forces", "aniso_forces"):
                 fn = getattr(lib, p + name)
                 fn.restype = C.c_int

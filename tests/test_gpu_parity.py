@@ -1,0 +1,312 @@
+"""Parity tests proper: the CUDA path, called through the C-ABI, against the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): per-particle forces / torques / virials within 1e-5 relative, energies
+summed within 1e-6 relative; DPD random numbers bit-exact. "Relative" is per particle against
+max(|f_i|, rms|f|) — a net force is a sum of ~100 cancelling pair terms, so a ratio to |f_i| alone is ill-defined
+for the particles whose net force happens to vanish. The double path is held to 1e-9; the float path to
+FLOAT_TOL below (a float pipeline accumulates ~1e-7 per term against the double oracle).
+"""
+
+import json
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import golden_cases as G
+import gpu_cases as GC
+import oracle_api as O
+from azplugins_b200 import _abi
+
+pytestmark = pytest.mark.gpu
+
+FLOAT_TOL = 1e-5
+DOUBLE_TOL = 1e-9
+REPORT = {}
+
+
+def _tol(bits):
+    return FLOAT_TOL if bits == 32 else DOUBLE_TOL
+
+
+class _Masked:
+    """View of a force object / oracle system restricted to the particles kept by a boolean mask."""
+
+    def __init__(self, src, keep, is_oracle):
+        if is_oracle:
+            self.force, self.torque, self.virial = src.force[keep], src.torque[keep], src.virial[:, : len(keep)][:, keep]
+        else:
+            self.forces, self.energies, self.virials, self.torques = src.forces[keep], src.energies[keep], src.virials[keep], src.torques[keep]
+
+
+def _check(name, f, hs, bits, torque=False, virial=True):
+    out = {}
+    if bits == 32 and getattr(hs, "nlist", None) is not None and hasattr(hs, "_rcutsq"):
+        amb = GC.cutoff_ambiguous(hs, hs._rcutsq)
+        out["skipped_cutoff_ambiguous"] = int(amb.sum())
+        assert amb.sum() <= 5 + 1e-3 * len(amb)
+        if amb.any():
+            f, hs = _Masked(f, ~amb, False), _Masked(hs, ~amb, True)
+    e_f, i = GC.error_metrics(f.forces, hs.force[:, :3])
+    out["force"] = e_f
+    e_e, _ = GC.error_metrics(f.energies, hs.force[:, 3])
+    out["energy_pp"] = e_e
+    etot, etot_ref = float(np.sum(f.energies.astype(np.float64))), float(np.sum(hs.force[:, 3]))
+    out["energy_sum_rel"] = abs(etot - etot_ref) / max(abs(etot_ref), np.sum(np.abs(hs.force[:, 3])) * 1e-3, 1e-30)
+    if virial:
+        v = f.virials
+        vr = hs.virial.T
+        e_v, _ = GC.error_metrics(v, vr)
+        out["virial"] = e_v
+        p, pr = v.astype(np.float64).sum(axis=0), vr.sum(axis=0)
+        out["pressure_rel"] = float(np.max(np.abs(p - pr)) / max(np.max(np.abs(pr)), 1e-30))
+    if torque:
+        out["torque"] = GC.error_metrics(f.torques, hs.torque[:, :3])[0]
+    REPORT[name] = out
+    tol = _tol(bits)
+    for k, val in out.items():
+        if k.startswith("skipped"):
+            continue
+        lim = (1e-6 if bits == 32 else 1e-10) if k in ("energy_sum_rel", "pressure_rel") else tol
+        assert val <= lim, (name, k, val, lim)
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _write_report():
+    yield
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/parity_report.json", "w") as fh:
+        json.dump(REPORT, fh, indent=1, sort_keys=True)
+
+
+# ---- the reference's own 2-particle known answers through the CUDA path ------------------------------------------
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("case", G.PAIR_CASES, ids=lambda c: c[0])
+def test_pair_golden_gpu(case, bits):
+    api, params, r_cut, shift, d, energy, force = case
+    box = cases.two_particle_box(r_cut)
+    pos = np.array([[-d / 2, 0, 0], [d / 2, 0, 0]])
+    if api == "DPDGeneralWeight":
+        import azplugins_b200 as az
+        from azplugins_b200 import nlist, pair
+
+        hs = O.HostSystem(box, pos, np.zeros(2, dtype=np.int64), 1, bits).build_nlist(r_cut + 0.4)
+        st = az.State(az.Snapshot(box, pos), device="cuda", scalar_bits=bits, seed=1)
+        f = pair.DPDGeneralWeight(nlist=nlist.NeighborList(), kT=0.0, default_r_cut=r_cut)
+        f.params[("A", "A")] = params
+        GC.attach_with_oracle_nlist(f, st, hs)
+        f.compute(0)
+    else:
+        f, _ = GC.run_pair(api, {(0, 0): params}, {(0, 0): r_cut}, bits, ntypes=1, mode="shift" if shift else "none",
+                           system=(box, pos, np.zeros(2, dtype=np.int64)), buffer=0.4)
+    cases.assert_golden(f.energies, [0.5 * energy, 0.5 * energy], bits)
+    cases.assert_golden(f.forces, [[-force, 0, 0], [force, 0, 0]], bits)
+    assert f.params[("A", "A")] == pytest.approx({k: float(v) for k, v in params.items()})
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("case", G.ANISO_CASES, ids=lambda c: f"rc{c[1]}")
+def test_aniso_golden_gpu(case, bits):
+    import azplugins_b200 as az
+    from azplugins_b200 import nlist, pair
+
+    params, r_cut, shift, energy, force, torque = case
+    box = cases.two_particle_box(r_cut)
+    pos = np.array(G.ANISO_POSITIONS)
+    hs = O.HostSystem(box, pos, np.zeros(2, dtype=np.int64), 1, bits).build_nlist(r_cut + 0.4)
+    st = az.State(az.Snapshot(box, pos), device="cuda", scalar_bits=bits)
+    f = pair.TwoPatchMorse(nlist=nlist.NeighborList(), default_r_cut=r_cut, mode="shift" if shift else "none")
+    f.params[("A", "A")] = params
+    GC.attach_with_oracle_nlist(f, st, hs)
+    f.compute(0)
+    cases.assert_golden(f.energies, [0.5 * energy, 0.5 * energy], bits)
+    if force is not None:
+        cases.assert_golden(f.forces, [-np.array(force), np.array(force)], bits)
+    if torque is not None:
+        cases.assert_golden(f.torques, [torque, torque], bits)
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("case", G.BOND_CASES, ids=lambda c: c[0])
+def test_bond_golden_gpu(case, bits):
+    import azplugins_b200 as az
+    from azplugins_b200 import bond
+
+    api, params, d, energy, force = case
+    snap = az.Snapshot(az.Box.cube(20.0), np.array([[-d / 2, 0, 0], [d / 2, 0, 0]]), bond_group=[[0, 1]], bond_typeid=[0], bond_types=["A-A"])
+    st = az.State(snap, device="cuda", scalar_bits=bits)
+    f = getattr(bond, api)()
+    f.params["A-A"] = params
+    f._attach(st)
+    f.compute(0).check_flags()
+    cases.assert_golden(f.energies, [0.5 * energy, 0.5 * energy], bits)
+    cases.assert_golden(f.forces, [[-force, 0, 0], [force, 0, 0]], bits)
+
+
+def test_bond_invalid_parameters_raise():
+    import azplugins_b200 as az
+    from azplugins_b200 import bond
+
+    snap = az.Snapshot(az.Box.cube(20.0), np.array([[-0.5, 0, 0], [0.5, 0, 0]]), bond_group=[[0, 1]], bond_typeid=[0], bond_types=["A-A"])
+    st = az.State(snap, device="cuda", scalar_bits=32)
+    f = bond.DoubleWell()
+    f.params["A-A"] = dict(r_0=1.0, r_1=1.0, U_1=1.0, U_tilt=0.0)
+    f._attach(st)
+    with pytest.raises(RuntimeError):
+        f.compute(0).check_flags()
+
+
+# ---- seeded many-particle systems ------------------------------------------------------------------------------
+PAIRS = {
+    "PerturbedLennardJones": ({(0, 0): dict(epsilon=1.0, sigma=1.0, attraction_scale_factor=0.5), (0, 1): dict(epsilon=1.5, sigma=0.9, attraction_scale_factor=0.0),
+                               (1, 1): dict(epsilon=0.0, sigma=1.0, attraction_scale_factor=1.0)}, {(0, 0): 3.0, (0, 1): 2.5, (1, 1): 2.0}),
+    "Colloid": ({(0, 0): dict(A=144.0, a_1=0.0, a_2=0.0, sigma=1.0), (0, 1): dict(A=100.0, a_1=0.0, a_2=0.3, sigma=1.0),
+                 (1, 1): dict(A=40.0, a_1=0.3, a_2=0.3, sigma=1.0)}, {(0, 0): 3.0, (0, 1): 3.0, (1, 1): 3.0}),
+    "ExpandedYukawa": ({(0, 0): dict(epsilon=1.0, kappa=1.0, delta=0.2), (0, 1): dict(epsilon=2.0, kappa=0.5, delta=0.1),
+                        (1, 1): dict(epsilon=0.0, kappa=1.0, delta=0.0)}, {(0, 0): 2.0, (0, 1): 2.5, (1, 1): 2.0}),
+    "Hertz": ({(0, 0): dict(epsilon=100.0), (0, 1): dict(epsilon=50.0), (1, 1): dict(epsilon=0.0)}, {(0, 0): 1.2, (0, 1): 1.5, (1, 1): 1.0}),
+    "DPDConservativeGeneralWeight": ({(0, 0): dict(A=25.0, gamma=4.5, s=2.0), (0, 1): dict(A=50.0, gamma=4.5, s=2.0), (1, 1): dict(A=0.0, gamma=1.0, s=1.0)},
+                                     {(0, 0): 1.5, (0, 1): 1.2, (1, 1): 1.0}),
+}
+cases.SPEC_BY_API["DPDConservativeGeneralWeight"] = __import__("azplugins_b200").params.DPD_CONSERVATIVE
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("mode", ["none", "shift", "xplor"])
+@pytest.mark.parametrize("api", list(PAIRS))
+def test_pair_random_system(api, mode, bits):
+    par_by, rc_by = PAIRS[api]
+    if api == "DPDConservativeGeneralWeight" and mode != "none":
+        pytest.skip("mode none only")
+    ron_by = {k: 0.8 * v for k, v in rc_by.items()}
+    ron_by[(0, 1)] = rc_by[(0, 1)] + 0.5
+    f, hs = GC.run_pair(api, par_by, rc_by, bits, mode=mode, ron_by=ron_by)
+    _check(f"pair/{api}/{mode}/{bits}", f, hs, bits)
+
+
+@pytest.mark.parametrize("tpp", [1, 2, 4, 8, 16, 32])
+def test_pair_threads_per_particle_variants(tpp):
+    par_by, rc_by = PAIRS["PerturbedLennardJones"]
+    f, hs = GC.run_pair("PerturbedLennardJones", par_by, rc_by, 32, n=3000, tpp=tpp)
+    _check(f"pair/plj/tpp{tpp}", f, hs, 32)
+
+
+def test_pair_without_virial_leaves_virial_untouched():
+    par_by, rc_by = PAIRS["ExpandedYukawa"]
+    f, hs = GC.run_pair("ExpandedYukawa", par_by, rc_by, 32, n=2000, virial=False)
+    assert np.all(f.virials == 0)
+    _check("pair/yukawa/novirial", f, hs, 32, virial=False)
+
+
+def test_pair_c1_configuration():
+    """BASELINE config 1: PerturbedLJ fluid, 32k particles, rho = 0.8, r_cut = 3.0 sigma, buffer 0.4."""
+    par = {(0, 0): dict(epsilon=1.0, sigma=1.0, attraction_scale_factor=0.5)}
+    for bits in (32, 64):
+        for mode in ("none", "shift"):
+            f, hs = GC.run_pair("PerturbedLennardJones", par, {(0, 0): 3.0}, bits, n=32000, rho=0.8, ntypes=1, mode=mode, seed=1001, buffer=0.4)
+            _check(f"C1/plj/{mode}/{bits}", f, hs, bits)
+
+
+DPD_PARAMS = ({(0, 0): dict(A=25.0, gamma=4.5, s=2.0), (0, 1): dict(A=50.0, gamma=4.5, s=2.0), (1, 1): dict(A=25.0, gamma=4.5, s=2.0)},
+              {(0, 0): 1.0, (0, 1): 1.0, (1, 1): 1.0})
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("s_exp", [2.0, 0.5])
+@pytest.mark.parametrize("timestep", [0, 1, 2**32 - 1, 2**32])
+def test_dpd_random_system(timestep, s_exp, bits):
+    par_by = {k: dict(v, s=s_exp) for k, v in DPD_PARAMS[0].items()}
+    f, hs, hs_same = GC.run_dpd(par_by, DPD_PARAMS[1], bits, timestep=timestep)
+    _check(f"dpd/s{s_exp}/t{timestep}/{bits}", f, hs, bits)
+
+
+def test_dpd_timestep_truncation_and_stream_change():
+    par_by, rc_by = DPD_PARAMS
+    f0, _, _ = GC.run_dpd(par_by, rc_by, 32, n=3000, timestep=5)
+    f1, _, _ = GC.run_dpd(par_by, rc_by, 32, n=3000, timestep=5 + 2**32)
+    f2, _, _ = GC.run_dpd(par_by, rc_by, 32, n=3000, timestep=6)
+    assert np.array_equal(f0.forces, f1.forces)  # u32 truncation of the timestep (DPDPairEvaluatorGeneralWeight.h:122)
+    assert not np.array_equal(f0.forces, f2.forces)
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_dpd_random_stream_bit_exact(bits):
+    """One pair, zero velocity, A = 0, s = 2: f/r = sigma * wR * alpha, so alpha is recovered from the force and must
+    equal the oracle's Philox draw to the last bit that the arithmetic around it preserves; pin it through the
+    conservative-free force ratio for many tag pairs."""
+    import azplugins_b200 as az
+    from azplugins_b200 import nlist, pair
+
+    rng = np.random.default_rng(77)
+    n = 512
+    tags = rng.choice(2**32, size=2 * n, replace=False).astype(np.uint32)
+    # n isolated pairs on a line, spacing 4, separation 0.5
+    pos = np.zeros((2 * n, 3))
+    pos[0::2, 0] = np.arange(n) * 4.0 - 2.0 * n
+    pos[1::2, 0] = pos[0::2, 0] + 0.5
+    box = az.Box(4.0 * n + 8.0, 10.0, 10.0)
+    hs = O.HostSystem(box, pos, np.zeros(2 * n, dtype=np.int64), 1, bits, tag=tags).build_nlist(1.4)
+    st = az.State(az.Snapshot(box, pos, tag=tags), device="cuda", scalar_bits=bits, seed=42)
+    f = pair.DPDGeneralWeight(nlist=nlist.NeighborList(), kT=1.0, default_r_cut=1.0)
+    f.dt = 0.01
+    f.params[("A", "A")] = dict(A=0.0, gamma=4.5, s=2.0)
+    GC.attach_with_oracle_nlist(f, st, hs)
+    for timestep in (0, 123456789):
+        f.compute(timestep)
+        fx = f.forces[0::2, 0].astype(np.float64)
+        ftype = np.float32 if bits == 32 else np.float64
+        dx = (hs.pos[0::2, 0] - hs.pos[1::2, 0]).astype(ftype)
+        alpha_expect = np.array([O.port().azo_dpd_alpha(bits, int(a), int(b), timestep & 0xFFFFFFFF, 42) for a, b in zip(tags[0::2], tags[1::2])])
+        # expected force from the oracle's alpha with the same float formula: f = dx * sigma * (w/r) * alpha
+        r = np.abs(dx)
+        sigma = ftype(1.0) / np.sqrt(ftype(0.01) / (ftype(1.0) * ftype(4.5) * ftype(6.0)))
+        expect = dx.astype(np.float64) * float(sigma) * ((1.0 - r) / r) * alpha_expect
+        # sign and value: any wrong bit in the upper ~20 bits of the draw would move alpha by >= 2^-20
+        np.testing.assert_allclose(fx, expect, rtol=3e-6 if bits == 32 else 1e-12, atol=1e-6 if bits == 32 else 1e-12)
+
+
+TPM_PARAMS = ({(0, 0): dict(M_d=1.8347, M_r=0.0302, r_eq=1.0043, omega=20.0, alpha=0.5, repulsion=True),
+               (0, 1): dict(M_d=1.0, M_r=0.1, r_eq=1.0, omega=5.0, alpha=0.4, repulsion=False),
+               (1, 1): dict(M_d=0.0, M_r=0.1, r_eq=1.0, omega=5.0, alpha=0.4, repulsion=False)}, {(0, 0): 1.6, (0, 1): 2.0, (1, 1): 1.6})
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("mode", ["none", "shift"])
+def test_aniso_random_system(mode, bits):
+    f, hs = GC.run_aniso(TPM_PARAMS[0], TPM_PARAMS[1], bits, mode=mode)
+    _check(f"aniso/tpm/{mode}/{bits}", f, hs, bits, torque=True)
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_bond_random_system(bits):
+    for api, plist in (("DoubleWell", [dict(r_0=1.0, r_1=2.0, U_1=1.0, U_tilt=0.5), dict(r_0=0.5, r_1=2.5, U_1=5.0, U_tilt=0.0)]),
+                       ("Quartic", [dict(k=1434.3, r_0=1.5, b_1=-0.7589, b_2=0.0, U_0=67.2234, sigma=1.0, epsilon=1.0, delta=0.0),
+                                    dict(k=100.0, r_0=1.2, b_1=-0.5, b_2=0.1, U_0=10.0, sigma=0.8, epsilon=1.0, delta=0.3)])):
+        f, hs = GC.run_bond(api, plist, bits)
+        f.check_flags()
+        _check(f"bond/{api}/{bits}", f, hs, bits)
+
+
+def test_empty_and_ragged_inputs():
+    """N = 0, particles with no neighbours, a single particle."""
+    import azplugins_b200 as az
+    from azplugins_b200 import nlist, pair
+
+    box = az.Box.cube(30.0)
+    pos = np.array([[0.0, 0, 0], [1.0, 0, 0], [10.0, 10, 10]])  # third particle is isolated
+    hs = O.HostSystem(box, pos, np.zeros(3, dtype=np.int64), 1, 32).build_nlist(3.4)
+    st = az.State(az.Snapshot(box, pos), device="cuda", scalar_bits=32)
+    f = pair.PerturbedLennardJones(nlist=nlist.NeighborList(), default_r_cut=3.0)
+    f.params[("A", "A")] = dict(epsilon=1.0, sigma=1.0, attraction_scale_factor=1.0)
+    GC.attach_with_oracle_nlist(f, st, hs)
+    f.compute(0)
+    assert np.all(f.forces[2] == 0) and f.energies[2] == 0
+    assert f.forces[0, 0] == pytest.approx(-f.forces[1, 0]) and f.forces[0, 0] != 0
+    # N = 0 through the raw ABI
+    import ctypes as C
+
+    a = _abi.PairArgs()
+    a.ntypes = 1
+    d = C.c_double(0)
+    assert _abi.load().azb_pair_forces(0, 32, C.byref(a), C.addressof(d), None) == 0
