@@ -101,6 +101,29 @@ class BondArgs(C.Structure):
     ]
 
 
+class NlistArgs(C.Structure):
+    _fields_ = [
+        ("d_pos", C.c_void_p),
+        ("N", C.c_uint),
+        ("n_max", C.c_uint),
+        ("box", Box),
+        ("ext_lo", C.c_double * 3),
+        ("ext_hi", C.c_double * 3),
+        ("r_list_max", C.c_double),
+        ("d_r_listsq", C.c_void_p),
+        ("ntypes", C.c_uint),
+        ("row_align", C.c_uint),
+        ("d_excl_head", C.c_void_p),
+        ("d_excl_list", C.c_void_p),
+        ("d_n_neigh", C.c_void_p),
+        ("d_head_list", C.c_void_p),
+        ("d_nlist", C.c_void_p),
+        ("capacity", C.c_size_t),
+        ("d_workspace", C.c_void_p),
+        ("workspace_bytes", C.c_size_t),
+    ]
+
+
 # every symbol include/azb200.h declares (tests check the library exports exactly these)
 EXPORTS = (
     "azb_abi_version",
@@ -111,6 +134,9 @@ EXPORTS = (
     "azb_dpd_forces",
     "azb_aniso_forces",
     "azb_bond_forces",
+    "azb_nlist_workspace_size",
+    "azb_nlist_count",
+    "azb_nlist_fill",
 )
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
@@ -144,6 +170,12 @@ def load():
     lib.azb_aniso_forces.argtypes = [C.c_int, C.c_int, C.POINTER(AnisoArgs), C.c_void_p, C.c_void_p]
     lib.azb_bond_forces.restype = C.c_int
     lib.azb_bond_forces.argtypes = [C.c_int, C.c_int, C.POINTER(BondArgs), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.azb_nlist_workspace_size.restype = C.c_int
+    lib.azb_nlist_workspace_size.argtypes = [C.POINTER(NlistArgs), C.POINTER(C.c_size_t)]
+    lib.azb_nlist_count.restype = C.c_int
+    lib.azb_nlist_count.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(C.c_size_t), C.c_void_p]
+    lib.azb_nlist_fill.restype = C.c_int
+    lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

@@ -1,0 +1,60 @@
+"""Host side of the GPU cell-list builder (azb_nlist_count / azb_nlist_fill in csrc/azb_nlist.cu)."""
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _abi
+from .state import scalar_dtype
+
+
+def build_cell_nlist(nl, state, row_align=1):
+    if state.device.type != "cuda":
+        raise RuntimeError("nlist.Cell builds on a CUDA device only (no CPU fallback)")
+    lib = _abi.load()
+    ftype, _, tdtype = scalar_dtype(state.scalar_bits)
+    r_list = nl.r_list(state.types)
+    if not np.any(r_list > 0):
+        raise RuntimeError("neighbour list has no consumer with a positive r_cut")
+    dev = state.device
+    a = _abi.NlistArgs()
+    a.d_pos = state.pos.data_ptr()
+    a.N, a.n_max = state.N, state.n_max
+    a.box = state.box.as_abi()
+    if not all(state.box.periodic):
+        p = state.pos[:, :3]
+        lo, hi = p.min(dim=0).values.double().cpu().numpy(), p.max(dim=0).values.double().cpu().numpy()
+        for d in range(3):
+            a.ext_lo[d], a.ext_hi[d] = float(lo[d]) - 1e-6, float(hi[d]) + 1e-6 + 1e-6 * abs(float(hi[d]))
+    a.r_list_max = float(r_list.max())
+    rl = r_list.astype(ftype)
+    rlsq = torch.from_numpy(np.where(r_list > 0, rl * rl, ftype(-1)).reshape(-1).astype(ftype)).to(dev)
+    a.d_r_listsq = rlsq.data_ptr()
+    a.ntypes = len(state.types)
+    a.row_align = row_align
+    keep = [rlsq]
+    if "bond" in nl.exclusions and len(state.bond_group):
+        head, lst = state.exclusions_csr()
+        d_head = torch.from_numpy(head.view(np.int64)).to(dev)
+        d_lst = torch.from_numpy(lst.view(np.int32) if lst.size else np.zeros(1, np.int32)).to(dev)
+        a.d_excl_head, a.d_excl_list = d_head.data_ptr(), d_lst.data_ptr()
+        keep += [d_head, d_lst]
+    n_neigh = torch.zeros(max(state.N, 1), dtype=torch.int32, device=dev)
+    head_list = torch.zeros(max(state.N, 1), dtype=torch.int64, device=dev)
+    a.d_n_neigh, a.d_head_list = n_neigh.data_ptr(), head_list.data_ptr()
+    ws_bytes = C.c_size_t(0)
+    _abi.check(lib.azb_nlist_workspace_size(C.byref(a), C.byref(ws_bytes)), "azb_nlist_workspace_size")
+    ws = torch.empty(ws_bytes.value, dtype=torch.uint8, device=dev)
+    a.d_workspace, a.workspace_bytes = ws.data_ptr(), ws_bytes.value
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    total = C.c_size_t(0)
+    _abi.check(lib.azb_nlist_count(state.scalar_bits, C.byref(a), C.byref(total), stream), "azb_nlist_count")
+    nlist = torch.zeros(max(total.value, 1), dtype=torch.int32, device=dev)
+    a.d_nlist, a.capacity = nlist.data_ptr(), max(total.value, 1)
+    _abi.check(lib.azb_nlist_fill(state.scalar_bits, C.byref(a), stream), "azb_nlist_fill")
+    torch.cuda.current_stream(dev).synchronize()
+    del keep
+    nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
+    nl.launches = getattr(nl, "launches", 0) + 1
+    return nl

@@ -99,8 +99,14 @@ __global__ void __launch_bounds__(256) dpd_force_kernel(const DPDArgsDev<S> d, c
                 const S alpha = dpd_alpha<S>(tag_i, tag_j, d.rk);
                 const S fcons = c.A * (rinv - c.rcutinv);
                 // w = 1 - r/rc can round a hair below 0 right at the cutoff; clamp so pow() never sees a negative base
-                const S w = fmax(S(0), S(1.0) - r * c.rcutinv);
-                const S wpow = (c.half_s == S(1.0)) ? w : ((c.half_s == S(0)) ? S(1.0) : pow_(w, c.half_s));
+                S w = fmax(S(0), S(1.0) - r * c.rcutinv);
+                S wpow = w;
+                if (c.half_s != S(1.0))
+                    {
+                    // w^(s/2) with s < 2 is infinitely steep at the cutoff: take r from a correctly rounded sqrt there
+                    w = fmax(S(0), S(1.0) - sqrt_(rsq) * c.rcutinv);
+                    wpow = (c.half_s == S(0)) ? S(1.0) : pow_(w, c.half_s);
+                    }
                 const S wR = wpow * rinv;
                 S fdivr = fcons - c.gamma * wR * wR * rdotv;
                 fdivr += c.sigma * wR * alpha;

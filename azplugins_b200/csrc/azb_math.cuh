@@ -87,7 +87,10 @@ __device__ __forceinline__ double sqrt_(double x)
     }
 __device__ __forceinline__ float exp_(float x)
     {
-    return __expf(x);
+    // ex2.approx on a two-term product x*log2(e): __expf alone loses |x|*1e-7 relative to the rounding of x*log2(e)
+    const float t = x * 1.4426950216293335f;
+    const float r = __fmaf_rn(x, 1.4426950216293335f, -t) + x * 1.925963033500011e-8f;
+    return exp2f(t) * __fmaf_rn(r, 0.6931471824645996f, 1.0f);
     }
 __device__ __forceinline__ double exp_(double x)
     {

@@ -207,6 +207,38 @@ AZB_API int azb_bond_forces(int potential,
                     unsigned int* d_flags,
                     void* stream);
 
+/* ---- neighbour list: cell list -> HOOMD-layout n_neigh / head_list / nlist, FULL mode --------
+ * Two calls, like HOOMD's NeighborListGPU (count, grow the buffer if needed, fill):
+ *   azb_nlist_count: bins particles, counts neighbours within r_list(type_i,type_j), writes d_n_neigh and d_head_list
+ *                    (rows padded to row_align entries) and returns the required nlist length in *h_total (this call
+ *                    synchronises the stream);
+ *   azb_nlist_fill : writes d_nlist[capacity >= *h_total]; must follow azb_nlist_count with the same arguments and the
+ *                    same workspace contents. Row order is deterministic (cell traversal, then particle index). */
+typedef struct azb_nlist_args
+    {
+    const void* d_pos;               /* Scalar4[n_max] */
+    unsigned int N;                  /* rows are built for the N local particles */
+    unsigned int n_max;              /* candidates are all n_max particles (locals + ghosts) */
+    azb_box box;                     /* orthorhombic only (tilt factors must be 0) */
+    double ext_lo[3], ext_hi[3];     /* extent of the particle cloud along NON-periodic directions */
+    double r_list_max;               /* max over type pairs of r_cut + r_buff: sets the cell width */
+    const void* d_r_listsq;          /* Scalar[ntypes*ntypes], (r_cut + r_buff)^2; <= 0 disables the pair */
+    unsigned int ntypes;
+    unsigned int row_align;          /* 0/1 = tight rows */
+    const size_t* d_excl_head;       /* [N+1] CSR of excluded partner indices per local particle, or NULL */
+    const unsigned int* d_excl_list;
+    unsigned int* d_n_neigh;         /* out [N] */
+    size_t* d_head_list;             /* out [N] */
+    unsigned int* d_nlist;           /* out [capacity] (fill only) */
+    size_t capacity;
+    void* d_workspace;               /* >= azb_nlist_workspace_size bytes, 256-byte aligned */
+    size_t workspace_bytes;
+    } azb_nlist_args;
+
+AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
+AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
+AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

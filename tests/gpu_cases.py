@@ -53,6 +53,10 @@ def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", r
     shift = {"none": 0, "shift": 1, "xplor": 2}[mode]
     hs.pair(spec.potential_id, par64, rcsq64, ronsq64, shift_mode=shift, compute_virial=True,
             which=which or ("ref" if O.have_ref() else "port"), nthreads=4)
+    # same-precision oracle: what the reference computes when built with Scalar = float / double
+    hs_b.pair(spec.potential_id, par, rcsq, ronsq, shift_mode=shift, compute_virial=True,
+              which=which or ("ref" if O.have_ref() else "port"), nthreads=4)
+    hs_b.hs64 = hs
 
     st = make_state(box, pos, typeid, ntypes, bits)
     cls = getattr(pair, api)
@@ -67,7 +71,7 @@ def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", r
     f.compute_virial = virial
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(0)
-    return f, hs
+    return f, hs_b
 
 
 def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0, sim_seed=42, dt=0.01, kT=1.0, tpp=0, buffer=0.4):
@@ -96,7 +100,8 @@ def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0
     f.threads_per_particle = tpp
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(timestep)
-    return f, hs, hs_b
+    hs_b.hs64 = hs
+    return f, hs_b, hs
 
 
 def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=301, tpp=0, buffer=0.4):
@@ -109,6 +114,8 @@ def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=
     hs = O.HostSystem(box, hs_b.pos[:, :3].astype(np.float64), typeid, ntypes, 64, orientation=hs_b.ori.astype(np.float64))
     hs.n_neigh, hs.head_list, hs.nlist = hs_b.n_neigh, hs_b.head_list, hs_b.nlist
     hs.aniso(par64, rcsq64, shift_mode=1 if mode == "shift" else 0, which="ref" if O.have_ref() else "port", nthreads=4)
+    hs_b.aniso(par, rcsq, shift_mode=1 if mode == "shift" else 0, which="ref" if O.have_ref() else "port", nthreads=4)
+    hs_b.hs64 = hs
 
     snap = az.Snapshot(box, pos, typeid=typeid, types=TYPE_NAMES[:ntypes], orientation=q)
     st = az.State(snap, device="cuda", scalar_bits=bits)
@@ -120,7 +127,7 @@ def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=
     f.threads_per_particle = tpp
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(0)
-    return f, hs
+    return f, hs_b
 
 
 def run_bond(api, plist, bits, n=20000, seed=401, bond_fraction=0.9):
@@ -147,7 +154,10 @@ def run_bond(api, plist, bits, n=20000, seed=401, bond_fraction=0.9):
     table = build_bond_table(n, n, bonds, btype)
     par64 = np.array([spec.pack(p, 64) for p in plist])
     hs.bond(spec.potential_id, par64, *table, len(plist), which="ref" if O.have_ref() else "port", nthreads=4)
-    return f, hs
+    hs_b = O.HostSystem(box, pos, typeid, 1, bits)
+    hs_b.bond(spec.potential_id, np.array([spec.pack(p, bits) for p in plist]), *table, len(plist), which="ref" if O.have_ref() else "port", nthreads=4)
+    hs_b.hs64 = hs
+    return f, hs_b
 
 
 def cutoff_ambiguous(hs, rcutsq, rel=2e-6):
