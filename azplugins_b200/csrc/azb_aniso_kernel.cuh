@@ -60,7 +60,7 @@ template<class S, class Q> __device__ __forceinline__ void patch_director(const 
     nz = S(2) * (vx * vz - s * vy);
     }
 
-template<class S, int SHIFT, bool VIRIAL, int TPP>
+template<class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX>
 __global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> d, const TwoPatchMorse::Params<S>* __restrict__ params)
     {
     typedef TwoPatchMorse::Coeff<S> coeff_t;
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> 
             const unsigned int j = __ldg(row + k);
             const auto pj = ld4(a.pos + j);
             S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            min_image(a.box, dx, dy, dz);
+            min_image_t<FASTBOX>(a.box, dx, dy, dz);
             const S rsq = dx * dx + dy * dy + dz * dz;
             const unsigned int tp = trow + type_of(pj.w);
             if (!(rsq > s_rcutsq[tp])) // the evaluator rejects only rsq > rcutsq (strict), :135

@@ -131,7 +131,10 @@ template<class Pot, class S> __global__ void __launch_bounds__(256) bond_force_k
         const uint2 g = __ldg(a.bondlist + (size_t)k * a.pitch + idx);
         const auto pj = ld4(a.pos + g.x);
         S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-        min_image(a.box, dx, dy, dz);
+        if (a.box.flags == 7u)
+            min_image_ortho(a.box, dx, dy, dz);
+        else
+            min_image(a.box, dx, dy, dz);
         const S rsq = dx * dx + dy * dy + dz * dz;
         S fdivr = S(0), e = S(0);
         if (Pot::eval(rsq, s_params[g.y], fdivr, e))

@@ -24,15 +24,15 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
     const size_t T2 = (size_t)a.pair.ntypes * a.pair.ntypes;
     const size_t smem = T2 * (sizeof(coeff_t) + sizeof(S));
-    if (smem > 200 * 1024)
+    if (smem > 48 * 1024)
         return AZB_ERR_BAD_ARGUMENT;
 #define AZB_CALL(TPP)                                                                           \
     do                                                                                          \
         {                                                                                       \
-        auto kern = dpd_force_kernel<S, VIRIAL, TPP>;                                           \
-        if (smem > 48 * 1024)                                                                   \
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        kern<<<grid, block, smem, stream>>>(d, (const param_t*)d_params);                       \
+        if (d.pair.box.flags == 7u)                                                             \
+            dpd_force_kernel<S, VIRIAL, TPP, true><<<grid, block, smem, stream>>>(d, (const param_t*)d_params);  \
+        else                                                                                    \
+            dpd_force_kernel<S, VIRIAL, TPP, false><<<grid, block, smem, stream>>>(d, (const param_t*)d_params); \
         } while (0)
     AZB_DISPATCH_TPP(tpp, AZB_CALL)
 #undef AZB_CALL

@@ -46,7 +46,7 @@ struct DPDThermo
         }
     };
 
-template<class S, bool VIRIAL, int TPP>
+template<class S, bool VIRIAL, int TPP, bool FASTBOX>
 __global__ void __launch_bounds__(256) dpd_force_kernel(const DPDArgsDev<S> d, const DPDThermo::Params<S>* __restrict__ params)
     {
     typedef DPDThermo::Coeff<S> coeff_t;
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) dpd_force_kernel(const DPDArgsDev<S> d, c
             const unsigned int j = __ldg(row + k);
             const auto pj = ld4(a.pos + j);
             S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            min_image(a.box, dx, dy, dz);
+            min_image_t<FASTBOX>(a.box, dx, dy, dz);
             const S rsq = dx * dx + dy * dy + dz * dz;
             const unsigned int tp = trow + type_of(pj.w);
             const S rcutsq = s_rcutsq[tp];

@@ -53,9 +53,13 @@ __device__ __forceinline__ unsigned int type_of(double w)
     }
 
 // ---- math flavours ----------------------------------------------------------------------------------
+// Single-instruction MUFU approximations with flush-to-zero (no denormal fix-up code around them): the float
+// flavour of hoomd::fast::. Relative error <= 2 ulp each.
 __device__ __forceinline__ float rcp(float x)
     {
-    return __fdividef(1.0f, x);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
     }
 __device__ __forceinline__ double rcp(double x)
     {
@@ -71,7 +75,9 @@ __device__ __forceinline__ double fdiv(double a, double b)
     }
 __device__ __forceinline__ float rsqrt_(float x)
     {
-    return rsqrtf(x);
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
     }
 __device__ __forceinline__ double rsqrt_(double x)
     {
@@ -90,7 +96,9 @@ __device__ __forceinline__ float exp_(float x)
     // ex2.approx on a two-term product x*log2(e): __expf alone loses |x|*1e-7 relative to the rounding of x*log2(e)
     const float t = x * 1.4426950216293335f;
     const float r = __fmaf_rn(x, 1.4426950216293335f, -t) + x * 1.925963033500011e-8f;
-    return exp2f(t) * __fmaf_rn(r, 0.6931471824645996f, 1.0f);
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    return e * __fmaf_rn(r, 0.6931471824645996f, 1.0f);
     }
 __device__ __forceinline__ double exp_(double x)
     {
@@ -120,6 +128,16 @@ __device__ __forceinline__ double rint_(double x)
     {
     return rint(x);
     }
+// Round-to-nearest-even without the XU pipe (FRND / F2I run at quarter rate): adding and subtracting 1.5 * 2^(p-1)
+// leaves rint(x) for |x| < 2^(p-2). Image counts are tiny integers, far inside that range.
+__device__ __forceinline__ float rint_small(float x)
+    {
+    return __fadd_rn(__fadd_rn(x, 12582912.0f), -12582912.0f);
+    }
+__device__ __forceinline__ double rint_small(double x)
+    {
+    return __dadd_rn(__dadd_rn(x, 6755399441055744.0), -6755399441055744.0);
+    }
 
 // ---- box ------------------------------------------------------------------------------------------------
 template<class S> struct Box
@@ -127,6 +145,16 @@ template<class S> struct Box
     S Lx, Ly, Lz, Lxinv, Lyinv, Lzinv, xy, xz, yz;
     unsigned int flags; // bit0..2 periodic x,y,z; bit3 = any tilt
     };
+
+// Fully periodic orthorhombic box (flags == 7): straight-line code, no flag tests, no XU instructions.
+template<class S> __device__ __forceinline__ void min_image_ortho(const Box<S>& b, S& x, S& y, S& z)
+    {
+    x -= b.Lx * rint_small(x * b.Lxinv);
+    y -= b.Ly * rint_small(y * b.Lyinv);
+    z -= b.Lz * rint_small(z * b.Lzinv);
+    }
+
+template<bool FASTBOX, class S> __device__ __forceinline__ void min_image_t(const Box<S>& b, S& x, S& y, S& z);
 
 // BoxDim::minImage, GPU flavour: rint(w * Linv), z then y then x with tilt terms
 template<class S> __device__ __forceinline__ void min_image(const Box<S>& b, S& x, S& y, S& z)
@@ -158,5 +186,12 @@ template<class S> __device__ __forceinline__ void min_image(const Box<S>& b, S& 
         if (b.flags & 1u)
             x -= b.Lx * rint_(x * b.Lxinv);
         }
+    }
+template<bool FASTBOX, class S> __device__ __forceinline__ void min_image_t(const Box<S>& b, S& x, S& y, S& z)
+    {
+    if (FASTBOX)
+        min_image_ortho(b, x, y, z);
+    else
+        min_image(b, x, y, z);
     }
     } // namespace azb

@@ -3,9 +3,12 @@
 //
 // Work decomposition: TPP lanes of a warp cooperate on one particle. Lane l walks neighbour-row entries
 // l, l+TPP, ...: the row read is a coalesced 4*TPP-byte segment, each entry is followed by one 16 B (float) or
-// 32 B (double) read-only gather of pos[j]. Per-type-pair coefficients (hoisted evaluator-constructor math and
-// the energy shift) live in shared memory. Force, energy and the six virial rows are reduced across the TPP
-// lanes with shuffles; lane 0 writes Scalar4 force (energy in .w) and the virial rows.
+// 32 B (double) read-only gather of pos[j]. Two row entries are in flight per lane and iteration (both index loads,
+// then both position gathers, then the arithmetic) so that gather latency overlaps. Per-type-pair coefficients
+// (hoisted evaluator-constructor math and the energy shift) live in shared memory — or in registers when the system
+// has a single particle type (SINGLE). FASTBOX selects straight-line minimum-image code for the fully periodic
+// orthorhombic box. Force, energy and the six virial rows are reduced across the TPP lanes with shuffles; lane 0
+// writes Scalar4 force (energy in .w) and the virial rows.
 #pragma once
 #include "azb_math.cuh"
 #include "azb_pair_potentials.cuh"
@@ -36,8 +39,80 @@ template<int TPP, class S> __device__ __forceinline__ S group_sum(S v)
     return v;
     }
 
+// per-lane accumulators of one particle
+template<class S, bool VIRIAL> struct PairAccum
+    {
+    S fx = S(0), fy = S(0), fz = S(0), pe = S(0);
+    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    __device__ __forceinline__ void add(S dx, S dy, S dz, S fdivr, S fdivr_virial, S e)
+        {
+        fx += dx * fdivr;
+        fy += dy * fdivr;
+        fz += dz * fdivr;
+        pe += e;
+        if (VIRIAL)
+            {
+            const S h = S(0.5) * fdivr_virial;
+            vxx += h * dx * dx;
+            vxy += h * dx * dy;
+            vxz += h * dx * dz;
+            vyy += h * dy * dy;
+            vyz += h * dy * dz;
+            vzz += h * dz * dz;
+            }
+        }
+    template<int TPP> __device__ __forceinline__ void reduce()
+        {
+        if (TPP > 1)
+            {
+            fx = group_sum<TPP>(fx);
+            fy = group_sum<TPP>(fy);
+            fz = group_sum<TPP>(fz);
+            pe = group_sum<TPP>(pe);
+            if (VIRIAL)
+                {
+                vxx = group_sum<TPP>(vxx);
+                vxy = group_sum<TPP>(vxy);
+                vxz = group_sum<TPP>(vxz);
+                vyy = group_sum<TPP>(vyy);
+                vyz = group_sum<TPP>(vyz);
+                vzz = group_sum<TPP>(vzz);
+                }
+            }
+        }
+    __device__ __forceinline__ void store(const PairArgsDev<S>& a, unsigned int idx) const
+        {
+        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
+        if (VIRIAL)
+            {
+            a.virial[0 * a.virial_pitch + idx] = vxx;
+            a.virial[1 * a.virial_pitch + idx] = vxy;
+            a.virial[2 * a.virial_pitch + idx] = vxz;
+            a.virial[3 * a.virial_pitch + idx] = vyy;
+            a.virial[4 * a.virial_pitch + idx] = vyz;
+            a.virial[5 * a.virial_pitch + idx] = vzz;
+            }
+        }
+    };
+
+// XPLOR smoothing between r_on and r_cut (HOOMD PotentialPair)
+template<class S> __device__ __forceinline__ void xplor(S rsq, S rcutsq, S ronsq, S& fdivr, S& e)
+    {
+    if (rsq >= ronsq && rsq < rcutsq)
+        {
+        const S d = rcutsq - ronsq;
+        const S denom_inv = S(1.0) / (d * d * d);
+        const S q = rsq - rcutsq;
+        const S s = q * q * (rcutsq + S(2.0) * rsq - S(3.0) * ronsq) * denom_inv;
+        const S ds = S(12.0) * (rsq - ronsq) * q * denom_inv;
+        const S old_e = e;
+        e = old_e * s;
+        fdivr = s * fdivr - ds * old_e;
+        }
+    }
+
 // SHIFT: 0 none, 1 shift, 2 xplor (azb_shift_mode)
-template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP>
+template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a, const typename Pot::template Params<S>* __restrict__ params)
     {
     typedef typename Pot::template Coeff<S> coeff_t;
@@ -67,87 +142,60 @@ __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a,
     const unsigned int lane = threadIdx.x % TPP;
     const bool active = idx < a.N;
 
-    S fx = S(0), fy = S(0), fz = S(0), pe = S(0);
-    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    PairAccum<S, VIRIAL> acc;
     if (active)
         {
         const unsigned int nn = __ldg(a.n_neigh + idx);
         const unsigned int* row = a.nlist + __ldg(a.head_list + idx);
         const auto pi = ld4(a.pos + idx);
-        const unsigned int trow = type_of(pi.w) * a.ntypes;
+        const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
+        // single-type systems: the one coefficient set lives in registers for the whole loop
+        const coeff_t c0 = s_coeff[0];
+        const S rc0 = s_rcutsq[0], ron0 = s_ronsq[0];
 
-        for (unsigned int k = lane; k < nn; k += TPP)
-            {
-            const unsigned int j = __ldg(row + k);
-            const auto pj = ld4(a.pos + j);
+        auto visit = [&](const typename vec4<S>::type& pj)
+        {
             S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            min_image(a.box, dx, dy, dz);
+            min_image_t<FASTBOX>(a.box, dx, dy, dz);
             const S rsq = dx * dx + dy * dy + dz * dz;
-            const unsigned int tp = trow + type_of(pj.w);
-            const S rcutsq = s_rcutsq[tp];
             S fdivr = S(0), e = S(0);
-            if (Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
+            if (SINGLE)
                 {
-                if (SHIFT == 2)
+                if (Pot::eval(rsq, rc0, c0, fdivr, e))
                     {
-                    const S ronsq = s_ronsq[tp];
-                    if (rsq >= ronsq && rsq < rcutsq)
-                        {
-                        const S d = rcutsq - ronsq;
-                        const S denom_inv = S(1.0) / (d * d * d);
-                        const S q = rsq - rcutsq;
-                        const S s = q * q * (rcutsq + S(2.0) * rsq - S(3.0) * ronsq) * denom_inv;
-                        const S ds = S(12.0) * (rsq - ronsq) * q * denom_inv;
-                        const S old_e = e;
-                        e = old_e * s;
-                        fdivr = s * fdivr - ds * old_e;
-                        }
-                    }
-                fx += dx * fdivr;
-                fy += dy * fdivr;
-                fz += dz * fdivr;
-                pe += e;
-                if (VIRIAL)
-                    {
-                    const S h = S(0.5) * fdivr;
-                    vxx += h * dx * dx;
-                    vxy += h * dx * dy;
-                    vxz += h * dx * dz;
-                    vyy += h * dy * dy;
-                    vyz += h * dy * dz;
-                    vzz += h * dz * dz;
+                    if (SHIFT == 2)
+                        xplor(rsq, rc0, ron0, fdivr, e);
+                    acc.add(dx, dy, dz, fdivr, fdivr, e);
                     }
                 }
-            }
-        }
-    if (TPP > 1)
-        {
-        fx = group_sum<TPP>(fx);
-        fy = group_sum<TPP>(fy);
-        fz = group_sum<TPP>(fz);
-        pe = group_sum<TPP>(pe);
-        if (VIRIAL)
+            else
+                {
+                const unsigned int tp = trow + type_of(pj.w);
+                const S rcutsq = s_rcutsq[tp];
+                if (Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
+                    {
+                    if (SHIFT == 2)
+                        xplor(rsq, rcutsq, s_ronsq[tp], fdivr, e);
+                    acc.add(dx, dy, dz, fdivr, fdivr, e);
+                    }
+                }
+        };
+
+        unsigned int k = lane;
+        for (; k + TPP < nn; k += 2 * TPP)
             {
-            vxx = group_sum<TPP>(vxx);
-            vxy = group_sum<TPP>(vxy);
-            vxz = group_sum<TPP>(vxz);
-            vyy = group_sum<TPP>(vyy);
-            vyz = group_sum<TPP>(vyz);
-            vzz = group_sum<TPP>(vzz);
+            const unsigned int j0 = __ldg(row + k);
+            const unsigned int j1 = __ldg(row + k + TPP);
+            const auto p0 = ld4(a.pos + j0);
+            const auto p1 = ld4(a.pos + j1);
+            visit(p0);
+            visit(p1);
             }
+        if (k < nn)
+            visit(ld4(a.pos + __ldg(row + k)));
         }
+    acc.template reduce<TPP>();
     if (active && lane == 0)
-        {
-        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
-        if (VIRIAL)
-            {
-            a.virial[0 * a.virial_pitch + idx] = vxx;
-            a.virial[1 * a.virial_pitch + idx] = vxy;
-            a.virial[2 * a.virial_pitch + idx] = vxz;
-            a.virial[3 * a.virial_pitch + idx] = vyy;
-            a.virial[4 * a.virial_pitch + idx] = vyz;
-            a.virial[5 * a.virial_pitch + idx] = vzz;
-            }
-        }
+        acc.store(a, idx);
     }
     } // namespace azb

@@ -21,16 +21,31 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
     const size_t smem = T2 * (sizeof(coeff_t) + 2 * sizeof(S));
     if (smem > 200 * 1024)
         return AZB_ERR_BAD_ARGUMENT;
-#define AZB_CALL(TPP)                                                                                                      \
+    // kernel flavour: fully periodic orthorhombic box -> straight-line minimum image; one particle type -> coefficients
+    // in registers. Anything else takes the general kernel.
+    const bool fastbox = d.box.flags == 7u;
+    const int flavour = fastbox ? (a.ntypes == 1 ? 2 : 1) : 0;
+#define AZB_LAUNCH(TPP, FB, SG)                                                                                            \
     do                                                                                                                     \
         {                                                                                                                  \
-        auto kern = pair_force_kernel<Pot, S, SHIFT, VIRIAL, TPP>;                                                         \
+        auto kern = pair_force_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG>;                                                 \
         if (smem > 48 * 1024)                                                                                              \
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                            \
         kern<<<grid, block, smem, stream>>>(d, (const param_t*)d_params);                                                  \
         } while (0)
+#define AZB_CALL(TPP)                          \
+    do                                         \
+        {                                      \
+        if (flavour == 2)                      \
+            AZB_LAUNCH(TPP, true, true);       \
+        else if (flavour == 1)                 \
+            AZB_LAUNCH(TPP, true, false);      \
+        else                                   \
+            AZB_LAUNCH(TPP, false, false);     \
+        } while (0)
     AZB_DISPATCH_TPP(tpp, AZB_CALL)
 #undef AZB_CALL
+#undef AZB_LAUNCH
     return (int)cudaGetLastError();
     }
 
