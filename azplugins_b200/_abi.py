@@ -137,6 +137,7 @@ EXPORTS = (
     "azb_nlist_workspace_size",
     "azb_nlist_count",
     "azb_nlist_fill",
+    "azb_gather_scalar4",
 )
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
@@ -176,6 +177,8 @@ def load():
     lib.azb_nlist_count.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(C.c_size_t), C.c_void_p]
     lib.azb_nlist_fill.restype = C.c_int
     lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
+    lib.azb_gather_scalar4.restype = C.c_int
+    lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

@@ -1,0 +1,205 @@
+"""Spatial domain decomposition with a ghost-particle halo (SURVEY.md §8 e) — the multi-GPU form of the force path.
+
+One process per GPU on a Cartesian grid (1) / (2,1,1) / (2,2,1) / (2,2,2) of the periodic global box. Every rank owns the
+particles inside its sub-box; copies of neighbours' particles within ``r_ghost`` of a face / edge / corner are stored behind
+the locals at indices ``[N, N + n_ghost)`` — HOOMD's convention: the force kernels read ``pos[j]`` for ``j >= N`` and never
+write there. With the FULL neighbour list there is no reverse (force) communication. The local box is non-periodic along
+decomposed directions; ghosts arriving across the global boundary are shifted by -/+L so they sit next to the sub-box.
+
+Per step ``HaloExchange.update()`` refreshes the dynamic ghost fields (positions; velocities for DPD; orientations for
+anisotropic pairs) with one grouped point-to-point exchange (``torch.distributed`` P2P: NCCL over NVLink on GPUs, gloo in the CPU
+tests). Tags and types are static and travel once at setup. DPD random numbers depend only on (seed, timestep, tag_i, tag_j),
+so forces are independent of the decomposition up to summation order.
+"""
+
+import ctypes as C
+import itertools
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _abi
+from .state import Box, scalar_dtype
+
+GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+DIRECTIONS = [d for d in itertools.product((-1, 0, 1), repeat=3) if d != (0, 0, 0)]
+
+
+class Decomposition:
+    """Cartesian split of a periodic, origin-centred, orthorhombic global box."""
+
+    def __init__(self, world, rank, global_box, grid=None):
+        if grid is None:
+            if world not in GRIDS:
+                raise ValueError(f"no default domain grid for {world} ranks (use 1, 2, 4 or 8)")
+            grid = GRIDS[world]
+        if int(np.prod(grid)) != world:
+            raise ValueError("grid does not match the number of ranks")
+        if global_box.xy or global_box.xz or global_box.yz:
+            raise ValueError("domain decomposition supports orthorhombic boxes only")
+        self.world, self.rank, self.grid, self.global_box = world, rank, tuple(grid), global_box
+        self.coords = self.coords_of(rank)
+        L = global_box.L
+        w = L / np.array(self.grid)
+        self.lo = -L / 2 + w * np.array(self.coords)
+        self.hi = self.lo + w
+        self.width = w
+
+    def coords_of(self, rank):
+        gx, gy, gz = self.grid
+        return (rank % gx, (rank // gx) % gy, rank // (gx * gy))
+
+    def rank_of(self, coords):
+        gx, gy, gz = self.grid
+        return (coords[0] % gx) + gx * ((coords[1] % gy) + gy * (coords[2] % gz))
+
+    def neighbor(self, d):
+        """(rank, shift) of the domain in direction d; shift moves MY particles into the neighbour's frame."""
+        c = [self.coords[k] + d[k] for k in range(3)]
+        shift = np.zeros(3)
+        for k in range(3):
+            if c[k] < 0:
+                shift[k] = +self.global_box.L[k]  # leaving through the low face: reappear above the neighbour's box
+            elif c[k] >= self.grid[k]:
+                shift[k] = -self.global_box.L[k]
+        return self.rank_of(c), shift
+
+    def active_directions(self):
+        return [d for d in DIRECTIONS if all(d[k] == 0 or self.grid[k] > 1 for k in range(3))]
+
+    def local_box(self):
+        """Box handed to the kernels: global extent + periodic where not decomposed, non-periodic where decomposed."""
+        gb = self.global_box
+        return Box(gb.Lx, gb.Ly, gb.Lz, periodic=tuple(self.grid[k] == 1 for k in range(3)))
+
+    def owns(self, pos):
+        pos = np.asarray(pos)
+        m = np.ones(len(pos), dtype=bool)
+        for k in range(3):
+            if self.grid[k] > 1:
+                m &= (pos[:, k] >= self.lo[k]) & (pos[:, k] < self.hi[k])
+        return m
+
+    def send_mask(self, pos, d, r_ghost):
+        """Local particles that the neighbour in direction d needs as ghosts."""
+        m = np.ones(len(pos), dtype=bool)
+        for k in range(3):
+            if d[k] > 0:
+                m &= pos[:, k] >= self.hi[k] - r_ghost
+            elif d[k] < 0:
+                m &= pos[:, k] < self.lo[k] + r_ghost
+        return m
+
+
+def _gather_rows(out, src, idx, shift):
+    """out[e] = src[idx[e]] (+ shift[e] on xyz): CUDA kernel through the C-ABI on device tensors; torch indexing on CPU tensors
+    (the CPU form exists for the gloo tests of the exchange logic, the force path itself has no CPU form)."""
+    n = idx.numel()
+    if n == 0:
+        return
+    if src.is_cuda:
+        lib = _abi.load()
+        bits = 32 if src.dtype == torch.float32 else 64
+        code = lib.azb_gather_scalar4(bits, src.data_ptr(), idx.data_ptr(), shift.data_ptr() if shift is not None else None, out.data_ptr(), n,
+                                      C.c_void_p(torch.cuda.current_stream(src.device).cuda_stream))
+        _abi.check(code, "azb_gather_scalar4")
+    else:
+        torch.index_select(src, 0, idx.long(), out=out)
+        if shift is not None:
+            out[:, :3] += shift[:, :3]
+
+
+class HaloExchange:
+    """Ghost bookkeeping of one rank: builds the send lists, appends ghost storage to the State, refreshes it per step."""
+
+    def __init__(self, decomp, state, r_ghost, fields=("pos",), group=None):
+        self.decomp, self.state, self.group = decomp, state, group
+        self.fields = tuple(fields)
+        self.r_ghost = float(r_ghost)
+        if np.any(decomp.width[np.array(decomp.grid) > 1] < 2 * r_ghost):
+            raise ValueError("sub-domain narrower than 2 r_ghost")
+        dev = state.device
+        ftype = scalar_dtype(state.scalar_bits)[0]
+        pos_h = state.pos[: state.N, :3].double().cpu().numpy()
+        self.dirs = decomp.active_directions()
+        self.send_idx, self.send_shift, self.peers_send, self.peers_recv = [], [], [], []
+        for d in self.dirs:
+            peer, shift = decomp.neighbor(d)
+            idx = np.nonzero(decomp.send_mask(pos_h, d, self.r_ghost))[0].astype(np.int32)
+            sh = np.zeros((len(idx), 4), dtype=ftype)
+            sh[:, :3] = shift
+            self.send_idx.append(torch.from_numpy(idx).to(dev))
+            self.send_shift.append(torch.from_numpy(sh).to(dev))
+            self.peers_send.append(peer)
+            self.peers_recv.append(decomp.neighbor(tuple(-x for x in d))[0])
+        # counts: what I receive for direction k is what the rank behind me (direction -d_k) selected for ITS direction k
+        mine = [len(i) for i in self.send_idx]
+        if decomp.world > 1:
+            everyone = [None] * decomp.world
+            dist.all_gather_object(everyone, mine, group=group)
+        else:
+            everyone = [mine]
+        recv_counts = [everyone[self.peers_recv[k]][k] for k in range(len(self.dirs))]
+        self.recv_counts = [int(c) for c in recv_counts]
+        self.recv_offsets = np.concatenate([[0], np.cumsum(self.recv_counts)]).astype(np.int64)
+        n_ghost = int(self.recv_offsets[-1])
+        # grow the state arrays: locals first, ghosts behind them
+        N = state.N
+        for name in ("pos", "vel", "orientation"):
+            t = getattr(state, name)
+            grown = torch.zeros((N + n_ghost, 4), dtype=t.dtype, device=dev)
+            grown[:N] = t[:N]
+            setattr(state, name, grown)
+        tag = torch.zeros(N + n_ghost, dtype=state.tag.dtype, device=dev)
+        tag[:N] = state.tag[:N]
+        state.tag = tag
+        state.n_ghost = n_ghost
+        state.box = decomp.local_box()
+        self._bufs = {}
+        # static data once: tags (as a 1-column exchange) — types travel inside pos.w with every position update
+        sends, recvs = [], []
+        for k in range(len(self.dirs)):
+            sends.append((state.tag[self.send_idx[k].long()].contiguous(), self.peers_send[k]))
+            o0, o1 = N + int(self.recv_offsets[k]), N + int(self.recv_offsets[k + 1])
+            recvs.append((state.tag[o0:o1], self.peers_recv[k]))
+        self._p2p(sends, recvs)
+        self.update(all_fields=True)
+
+    def _p2p(self, sends, recvs):
+        """One grouped exchange; per peer, sends and receives are posted in direction order on both sides so they match."""
+        ops = []
+        for buf, peer in sends:
+            if buf.numel():
+                ops.append(dist.P2POp(dist.isend, buf, peer, group=self.group))
+        for buf, peer in recvs:
+            if buf.numel():
+                ops.append(dist.P2POp(dist.irecv, buf, peer, group=self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+    def update(self, all_fields=False):
+        """Refresh ghost copies of the dynamic fields (every step, before the force kernels)."""
+        st = self.state
+        N = st.N
+        fields = ("pos", "vel", "orientation") if all_fields else self.fields
+        sends, recvs = [], []
+        for name in fields:
+            arr = getattr(st, name)
+            for k in range(len(self.dirs)):
+                n = self.send_idx[k].numel()
+                key = (name, k)
+                if key not in self._bufs:
+                    self._bufs[key] = torch.empty((n, 4), dtype=arr.dtype, device=arr.device)
+                buf = self._bufs[key]
+                _gather_rows(buf, arr, self.send_idx[k], self.send_shift[k] if name == "pos" else None)
+                sends.append((buf, self.peers_send[k]))
+                o0, o1 = N + int(self.recv_offsets[k]), N + int(self.recv_offsets[k + 1])
+                recvs.append((arr[o0:o1], self.peers_recv[k]))  # contiguous slice: received in place, no unpack kernel
+        self._p2p(sends, recvs)
+
+    def bytes_per_update(self):
+        st = self.state
+        s4 = 4 * (st.scalar_bits // 8)
+        return sum(int(i.numel()) for i in self.send_idx) * s4 * len(self.fields)

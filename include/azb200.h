@@ -239,6 +239,12 @@ AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
 AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
 
+/* ---- halo packing (SURVEY.md §8 e): d_out[e] = d_src[d_idx[e]] (+ d_shift[e].xyz when d_shift != NULL), Scalar4 rows.
+ * Packs the boundary particles a neighbouring domain needs as ghosts into a contiguous send buffer; the periodic image
+ * shift is applied on the sender so the receiver stores the message in place behind its local particles. */
+AZB_API int azb_gather_scalar4(int scalar_bits, const void* d_src, const unsigned int* d_idx, const void* d_shift, void* d_out,
+                               size_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
