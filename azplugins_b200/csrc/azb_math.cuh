@@ -180,11 +180,11 @@ template<class S> __device__ __forceinline__ void min_image(const Box<S>& b, S& 
     else
         {
         if (b.flags & 4u)
-            z -= b.Lz * rint_(z * b.Lzinv);
+            z -= b.Lz * rint_small(z * b.Lzinv);
         if (b.flags & 2u)
-            y -= b.Ly * rint_(y * b.Lyinv);
+            y -= b.Ly * rint_small(y * b.Lyinv);
         if (b.flags & 1u)
-            x -= b.Lx * rint_(x * b.Lxinv);
+            x -= b.Lx * rint_small(x * b.Lxinv);
         }
     }
 template<bool FASTBOX, class S> __device__ __forceinline__ void min_image_t(const Box<S>& b, S& x, S& y, S& z)

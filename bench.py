@@ -288,9 +288,28 @@ def run_b200(args):
     _abi.load()
 
     label, snap, setup, buffer = make_workload(args.workload, args.n, rank)
-    st = az.State(snap, device=dev, scalar_bits=args.bits, seed=42)
     nl = nlist.Cell(buffer=buffer)
     forces = setup(nl)
+    halo = None
+    if world > 1:
+        # weak scaling: every rank generates its own sub-domain (same recipe, rank-dependent seed) of one periodic global
+        # box of grid x sub-box; ghosts within r_cut + buffer are exchanged with the neighbouring domains every step
+        from azplugins_b200.domain import GRIDS, Decomposition, HaloExchange
+
+        if args.workload == "melt":
+            raise SystemExit("melt: bonds across domains are not supported in the multi-GPU bench")
+        grid = GRIDS[world]
+        sub = snap.box
+        gbox = az.Box(sub.Lx * grid[0], sub.Ly * grid[1], sub.Lz * grid[2])
+        dec = Decomposition(world, rank, gbox)
+        snap.position += (dec.lo + dec.hi) / 2
+        snap.tag = (snap.tag.astype(np.uint64) + rank * snap.N).astype(np.uint32)
+        snap.box = gbox
+    st = az.State(snap, device=dev, scalar_bits=args.bits, seed=42)
+    if world > 1:
+        kind = forces[0]._kind
+        fields = ("pos", "vel") if kind == _abi.KIND_DPD else (("pos", "orientation") if kind == _abi.KIND_ANISO else ("pos",))
+        halo = HaloExchange(dec, st, float(nl.r_list(st.types).max()), fields=fields)
     virial = not args.no_virial
     for f in forces:
         f.compute_virial = virial
@@ -306,6 +325,8 @@ def run_b200(args):
     flush = None if args.no_flush else torch.empty(384 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     def step(t):
+        if halo is not None:
+            halo.update()
         for f in forces:
             f.compute(t)
 
@@ -330,6 +351,8 @@ def run_b200(args):
         if flush is not None:
             flush.fill_(k & 0xFF)
         ev[k][0].record()
+        if halo is not None:
+            halo.update()
         for fi, f in enumerate(forces):
             kev[k][fi][0].record()
             f.compute(args.warmup + k)
@@ -376,7 +399,9 @@ def run_b200(args):
         "config": {"workload": label, "particles_per_gpu": st.N, "mean_neighbors": round(nbar, 2), "compute_virial": virial,
                    "threads_per_particle": args.tpp or "auto", "neighbor_list": "full, HOOMD layout, built on GPU (azb_nlist_*)",
                    "l2": "flushed between timed steps (384 MiB fill)" if flush is not None else "not flushed; working set > L2",
-                   "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, independent domains (weak)"},
+                   "parallelism": "1 GPU" if world == 1 else
+                   f"{world} GPUs, spatial domains {GRIDS[world]}, ghost halo over NCCL P2P every step ({halo.bytes_per_update()} B sent/rank/step, "
+                   f"{st.n_ghost} ghosts on rank 0)"},
         "clocks": clocks, "roofline": roofline, "gpu_launches": int(launches),
         "nlist_build_s": nlist_build_s,
     }
