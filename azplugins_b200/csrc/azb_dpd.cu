@@ -1,4 +1,6 @@
 // DPD thermostat launcher (float and double; virial on/off; tpp 1..32).
+#include <cstdlib>
+
 #include "azb_dpd_kernel.cuh"
 #include "azb_launch.cuh"
 
@@ -8,6 +10,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     {
     typedef DPDThermo::Params<S> param_t;
     typedef DPDThermo::Coeff<S> coeff_t;
+    static const bool use_v1 = getenv("AZB_DPD_V1") != nullptr; // A/B switch while the queue kernel is being tuned
     DPDArgsDev<S> d;
     d.pair = make_pair_args<S>(a.pair);
     d.vel = (const typename vec4<S>::type*)a.d_vel;
@@ -16,7 +19,13 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     d.rk = make_round_keys(200, (uint64_t)(uint32_t)a.timestep, a.seed);
     d.deltaT = (S)a.deltaT;
     d.T = (S)a.T;
-    const unsigned int tpp = pick_tpp(a.pair);
+    // the queue kernel balances in-range work inside a group, so narrow groups (less idle tail, cheaper reductions) win
+    unsigned int tpp = a.pair.threads_per_particle;
+    if (tpp == 0)
+        {
+        const double nbar = a.pair.N ? (double)a.pair.size_nlist / (double)a.pair.N : 0.0;
+        tpp = use_v1 ? pick_tpp(a.pair) : (nbar <= 8 ? 1 : (nbar <= 16 ? 2 : (nbar <= 96 ? 4 : (nbar <= 256 ? 8 : 16))));
+        }
     if (!valid_tpp(tpp))
         return AZB_ERR_BAD_ARGUMENT;
     const unsigned int block = pick_block(a.pair.block_size);
@@ -26,6 +35,8 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     const size_t smem = T2 * (sizeof(coeff_t) + sizeof(S));
     if (smem > 48 * 1024)
         return AZB_ERR_BAD_ARGUMENT;
+    if (use_v1)
+        {
 #define AZB_CALL(TPP)                                                                           \
     do                                                                                          \
         {                                                                                       \
@@ -34,8 +45,42 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
         else                                                                                    \
             dpd_force_kernel<S, VIRIAL, TPP, false><<<grid, block, smem, stream>>>(d, (const param_t*)d_params); \
         } while (0)
+        AZB_DISPATCH_TPP(tpp, AZB_CALL)
+#undef AZB_CALL
+        return (int)cudaGetLastError();
+        }
+    // queue kernel: per-group ring of in-range entries + coefficient table in shared memory
+    const bool fastbox = d.pair.box.flags == 7u;
+    const bool single = a.pair.ntypes == 1;
+    const S lmin = fmin(d.pair.box.Lx, fmin(d.pair.box.Ly, d.pair.box.Lz));
+    const S wrap_sq = S(0.25) * lmin * lmin;
+    const size_t smem_q = (size_t)block * 4 * sizeof(typename vec4<S>::type) + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int))
+                          + T2 * sizeof(DPDCoeffQ<S>);
+    if (smem_q > 200 * 1024)
+        return AZB_ERR_BAD_ARGUMENT;
+#define AZB_LAUNCH_Q(TPP, FB, SG)                                                                   \
+    do                                                                                              \
+        {                                                                                           \
+        auto kern = dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG>;                                     \
+        if (smem_q > 48 * 1024)                                                                     \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_q);   \
+        kern<<<grid, block, smem_q, stream>>>(d, (const param_t*)d_params, wrap_sq);                \
+        } while (0)
+#define AZB_CALL(TPP)                            \
+    do                                           \
+        {                                        \
+        if (fastbox && single)                   \
+            AZB_LAUNCH_Q(TPP, true, true);       \
+        else if (fastbox)                        \
+            AZB_LAUNCH_Q(TPP, true, false);      \
+        else if (single)                         \
+            AZB_LAUNCH_Q(TPP, false, true);      \
+        else                                     \
+            AZB_LAUNCH_Q(TPP, false, false);     \
+        } while (0)
     AZB_DISPATCH_TPP(tpp, AZB_CALL)
 #undef AZB_CALL
+#undef AZB_LAUNCH_Q
     return (int)cudaGetLastError();
     }
 
