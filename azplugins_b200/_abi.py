@@ -8,7 +8,7 @@ substituted for it: if it is missing, importing a force class fails loudly.
 import ctypes as C
 import os
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 ERR_BAD_POTENTIAL = 10001
 ERR_BAD_SCALAR = 10002
@@ -35,6 +35,34 @@ class Box(C.Structure):
     ]
 
 
+class TilePlan(C.Structure):
+    _fields_ = [
+        ("tile_size", C.c_uint),
+        ("n_tiles", C.c_uint),
+        ("uniq_capacity", C.c_uint),
+        ("max_uniq", C.c_uint),
+        ("d_uniq_count", C.c_void_p),
+        ("d_uniq", C.c_void_p),
+        ("d_slots", C.c_void_p),
+    ]
+
+
+class TileBuildArgs(C.Structure):
+    _fields_ = [
+        ("d_n_neigh", C.c_void_p),
+        ("d_nlist", C.c_void_p),
+        ("d_head_list", C.c_void_p),
+        ("size_nlist", C.c_size_t),
+        ("N", C.c_uint),
+        ("tile_size", C.c_uint),
+        ("uniq_capacity", C.c_uint),
+        ("d_uniq_count", C.c_void_p),
+        ("d_uniq", C.c_void_p),
+        ("d_slots", C.c_void_p),
+        ("d_status", C.c_void_p),
+    ]
+
+
 class PairArgs(C.Structure):
     _fields_ = [
         ("d_force", C.c_void_p),
@@ -56,6 +84,7 @@ class PairArgs(C.Structure):
         ("shift_mode", C.c_uint),
         ("compute_virial", C.c_uint),
         ("threads_per_particle", C.c_uint),
+        ("tiles", C.POINTER(TilePlan)),
     ]
 
 
@@ -138,6 +167,7 @@ EXPORTS = (
     "azb_nlist_count",
     "azb_nlist_fill",
     "azb_gather_scalar4",
+    "azb_tiles_build",
 )
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
@@ -179,6 +209,8 @@ def load():
     lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
     lib.azb_gather_scalar4.restype = C.c_int
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.azb_tiles_build.restype = C.c_int
+    lib.azb_tiles_build.argtypes = [C.POINTER(TileBuildArgs), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_void_p]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

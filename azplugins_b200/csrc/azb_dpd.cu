@@ -1,6 +1,4 @@
-// DPD thermostat launcher (float and double; virial on/off; tpp 1..32).
-#include <cstdlib>
-
+// DPD thermostat launcher (float and double; virial on/off; tpp 1..32; direct or tile-staged neighbour data).
 #include "azb_dpd_kernel.cuh"
 #include "azb_launch.cuh"
 
@@ -10,77 +8,101 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     {
     typedef DPDThermo::Params<S> param_t;
     typedef DPDThermo::Coeff<S> coeff_t;
-    static const bool use_v1 = getenv("AZB_DPD_V1") != nullptr; // A/B switch while the queue kernel is being tuned
+    typedef typename vec4<S>::type V4;
     DPDArgsDev<S> d;
     d.pair = make_pair_args<S>(a.pair);
-    d.vel = (const typename vec4<S>::type*)a.d_vel;
+    d.vel = (const V4*)a.d_vel;
     d.tag = a.d_tag;
     // the evaluator stores the timestep in an `unsigned int` (DPDPairEvaluatorGeneralWeight.h:122,273)
     d.rk = make_round_keys(200, (uint64_t)(uint32_t)a.timestep, a.seed);
     d.deltaT = (S)a.deltaT;
     d.T = (S)a.T;
-    // the queue kernel balances in-range work inside a group, so narrow groups (less idle tail, cheaper reductions) win
+    // the queue balances in-range work inside a group, so narrow groups (less idle tail, cheaper reductions) win
     unsigned int tpp = a.pair.threads_per_particle;
     if (tpp == 0)
         {
         const double nbar = a.pair.N ? (double)a.pair.size_nlist / (double)a.pair.N : 0.0;
-        tpp = use_v1 ? pick_tpp(a.pair) : (nbar <= 8 ? 1 : (nbar <= 16 ? 2 : (nbar <= 96 ? 4 : (nbar <= 256 ? 8 : 16))));
+        tpp = nbar <= 8 ? 1 : (nbar <= 16 ? 2 : (nbar <= 96 ? 4 : (nbar <= 256 ? 8 : 16)));
         }
+    if (a.pair.tiles && a.pair.threads_per_particle == 0)
+        tpp = tpp < 2 ? 2 : (tpp > 16 ? 16 : tpp); // tile kernels exist for 2..16 lanes per particle
     if (!valid_tpp(tpp))
         return AZB_ERR_BAD_ARGUMENT;
-    const unsigned int block = pick_block(a.pair.block_size);
-    const unsigned int per_block = block / tpp;
-    const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
     const size_t T2 = (size_t)a.pair.ntypes * a.pair.ntypes;
-    const size_t smem = T2 * (sizeof(coeff_t) + sizeof(S));
-    if (smem > 48 * 1024)
-        return AZB_ERR_BAD_ARGUMENT;
-    if (use_v1)
-        {
-#define AZB_CALL(TPP)                                                                           \
-    do                                                                                          \
-        {                                                                                       \
-        if (d.pair.box.flags == 7u)                                                             \
-            dpd_force_kernel<S, VIRIAL, TPP, true><<<grid, block, smem, stream>>>(d, (const param_t*)d_params);  \
-        else                                                                                    \
-            dpd_force_kernel<S, VIRIAL, TPP, false><<<grid, block, smem, stream>>>(d, (const param_t*)d_params); \
-        } while (0)
-        AZB_DISPATCH_TPP(tpp, AZB_CALL)
-#undef AZB_CALL
-        return (int)cudaGetLastError();
-        }
-    // queue kernel: per-group ring of in-range entries + coefficient table in shared memory
     const bool fastbox = d.pair.box.flags == 7u;
     const bool single = a.pair.ntypes == 1;
     const S lmin = fmin(d.pair.box.Lx, fmin(d.pair.box.Ly, d.pair.box.Lz));
     const S wrap_sq = S(0.25) * lmin * lmin;
-    const size_t smem_q = (size_t)block * 4 * sizeof(typename vec4<S>::type) + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int))
-                          + T2 * sizeof(DPDCoeffQ<S>);
-    if (smem_q > 200 * 1024)
+
+#define AZB_BY_FLAVOUR(LAUNCH, TPP)        \
+    do                                     \
+        {                                  \
+        if (fastbox && single)             \
+            LAUNCH(TPP, true, true);       \
+        else if (fastbox)                  \
+            LAUNCH(TPP, true, false);      \
+        else if (single)                   \
+            LAUNCH(TPP, false, true);      \
+        else                               \
+            LAUNCH(TPP, false, false);     \
+        } while (0)
+
+    if (a.pair.tiles)
+        {
+        TilePlanDev plan;
+        unsigned int block = 0;
+        const int bad = make_tile_plan(a.pair, tpp, plan, block);
+        if (bad)
+            return bad;
+        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + (size_t)block * 4 * sizeof(V4)
+                            + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int)) + T2 * sizeof(coeff_t);
+        if (smem > AZB_MAX_SMEM)
+            return AZB_ERR_BAD_ARGUMENT;
+        const unsigned int grid = a.pair.tiles->n_tiles;
+#define AZB_LAUNCH_T(TPP, FB, SG)                                                            \
+    do                                                                                       \
+        {                                                                                    \
+        ensure_smem<dpd_tile_kernel<S, VIRIAL, TPP, FB, SG>>(smem);                          \
+        dpd_tile_kernel<S, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
+        } while (0)
+        switch (tpp)
+            {
+        case 2:
+            AZB_BY_FLAVOUR(AZB_LAUNCH_T, 2);
+            break;
+        case 4:
+            AZB_BY_FLAVOUR(AZB_LAUNCH_T, 4);
+            break;
+        case 8:
+            AZB_BY_FLAVOUR(AZB_LAUNCH_T, 8);
+            break;
+        case 16:
+            AZB_BY_FLAVOUR(AZB_LAUNCH_T, 16);
+            break;
+        default:
+            return AZB_ERR_BAD_ARGUMENT; // tile kernels exist for 2..16 lanes per particle
+            }
+#undef AZB_LAUNCH_T
+        return (int)cudaGetLastError();
+        }
+
+    const unsigned int block = pick_block(a.pair.block_size);
+    const unsigned int per_block = block / tpp;
+    const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
+    const size_t smem = (size_t)block * 4 * sizeof(V4) + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int)) + T2 * sizeof(coeff_t);
+    if (smem > AZB_MAX_SMEM)
         return AZB_ERR_BAD_ARGUMENT;
-#define AZB_LAUNCH_Q(TPP, FB, SG)                                                                   \
-    do                                                                                              \
-        {                                                                                           \
-        auto kern = dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG>;                                     \
-        if (smem_q > 48 * 1024)                                                                     \
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_q);   \
-        kern<<<grid, block, smem_q, stream>>>(d, (const param_t*)d_params, wrap_sq);                \
+#define AZB_LAUNCH_Q(TPP, FB, SG)                                                            \
+    do                                                                                       \
+        {                                                                                    \
+        ensure_smem<dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG>>(smem);                       \
+        dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, (const param_t*)d_params, wrap_sq); \
         } while (0)
-#define AZB_CALL(TPP)                            \
-    do                                           \
-        {                                        \
-        if (fastbox && single)                   \
-            AZB_LAUNCH_Q(TPP, true, true);       \
-        else if (fastbox)                        \
-            AZB_LAUNCH_Q(TPP, true, false);      \
-        else if (single)                         \
-            AZB_LAUNCH_Q(TPP, false, true);      \
-        else                                     \
-            AZB_LAUNCH_Q(TPP, false, false);     \
-        } while (0)
+#define AZB_CALL(TPP) AZB_BY_FLAVOUR(AZB_LAUNCH_Q, TPP)
     AZB_DISPATCH_TPP(tpp, AZB_CALL)
 #undef AZB_CALL
 #undef AZB_LAUNCH_Q
+#undef AZB_BY_FLAVOUR
     return (int)cudaGetLastError();
     }
 

@@ -70,6 +70,41 @@ inline unsigned int pick_block(unsigned int requested)
     return (b / 32) * 32;
     }
 
+// opt-in dynamic shared memory above 48 KB, once per kernel instantiation and size
+#define AZB_MAX_SMEM (227 * 1024)
+template<auto KERNEL> inline void ensure_smem(size_t bytes)
+    {
+    static size_t granted = 48 * 1024;
+    if (bytes > granted)
+        {
+        cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        granted = bytes;
+        }
+    }
+
+// Validates a.tiles against the launch and picks the CTA size: blockDim / tpp groups, each walking
+// tile_size / groups particles (both powers of two, so every warp runs the same number of passes).
+inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, TilePlanDev& plan, unsigned int& block)
+    {
+    const azb_tile_plan& t = *a.tiles;
+    const unsigned int ts = t.tile_size;
+    if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || t.n_tiles != (a.N + ts - 1) / ts || t.max_uniq > t.uniq_capacity
+        || !t.d_uniq_count || !t.d_uniq || !t.d_slots)
+        return AZB_ERR_BAD_ARGUMENT;
+    plan.tile_size = ts;
+    plan.uniq_capacity = t.uniq_capacity;
+    plan.smem_uniq = ((t.max_uniq > 0 ? t.max_uniq : 1u) + 7u) & ~7u;
+    plan.uniq_count = t.d_uniq_count;
+    plan.uniq = t.d_uniq;
+    plan.slots = t.d_slots;
+    block = a.block_size ? pick_block(a.block_size) : 256u;
+    if (block > ts * tpp)
+        block = ts * tpp;
+    if (block < 32 || (block & (block - 1u)))
+        return AZB_ERR_BAD_ARGUMENT;
+    return 0;
+    }
+
 inline int check_pair_args(const azb_pair_args* a)
     {
     if (!a || a->ntypes == 0 || a->shift_mode > 2)

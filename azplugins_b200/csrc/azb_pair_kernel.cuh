@@ -9,7 +9,12 @@
 // has a single particle type (SINGLE). FASTBOX selects straight-line minimum-image code for the fully periodic
 // orthorhombic box. Force, energy and the six virial rows are reduced across the TPP lanes with shuffles; lane 0
 // writes Scalar4 force (energy in .w) and the virial rows.
+//
+// pair_tile_kernel is the same evaluation with the neighbour positions taken from a shared-memory copy of the tile's
+// distinct neighbours (azb_tile_plan): one CTA per tile stages them once with coalesced loads, then addresses them
+// through 16-bit slots read four at a time.
 #pragma once
+#include "azb200.h"
 #include "azb_math.cuh"
 #include "azb_pair_potentials.cuh"
 
@@ -29,6 +34,15 @@ template<class S> struct PairArgsDev
     const S* rcutsq;
     const S* ronsq;
     unsigned int ntypes;
+    };
+
+// device view of azb_tile_plan
+struct TilePlanDev
+    {
+    unsigned int tile_size, uniq_capacity, smem_uniq; // smem_uniq: capacity of the staging arrays (>= max_uniq)
+    const unsigned int* uniq_count;
+    const unsigned int* uniq;
+    const uint16_t* slots;
     };
 
 template<int TPP, class S> __device__ __forceinline__ S group_sum(S v)
@@ -197,5 +211,128 @@ __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a,
     acc.template reduce<TPP>();
     if (active && lane == 0)
         acc.store(a, idx);
+    }
+// Separation of one list entry with the lazy minimum image: in the fully periodic orthorhombic box a pair whose raw
+// separation is inside half the shortest box edge (wrap_sq = (L_min / 2)^2) needs no wrap. Returns r^2.
+template<bool FASTBOX, class S> __device__ __forceinline__ S separation(const Box<S>& box, S wrap_sq, S& dx, S& dy, S& dz)
+    {
+    if (FASTBOX)
+        {
+        S rsq = dx * dx + dy * dy + dz * dz;
+        if (rsq > wrap_sq) // only then can a component exceed half a box edge
+            {
+            min_image_ortho(box, dx, dy, dz);
+            rsq = dx * dx + dy * dy + dz * dz;
+            }
+        return rsq;
+        }
+    min_image(box, dx, dy, dz);
+    return dx * dx + dy * dy + dz * dz;
+    }
+
+// One CTA per tile of consecutive particles. Stage: s_pos[s] = pos[uniq[s]] (ascending indices -> coalesced runs).
+// Walk: blockDim / TPP groups, each taking tile_size / groups particles; a lane reads four 16-bit slots per load.
+template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
+__global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, const TilePlanDev plan,
+                                                        const typename Pot::template Params<S>* __restrict__ params, const S wrap_sq)
+    {
+    typedef typename Pot::template Coeff<S> coeff_t;
+    typedef typename vec4<S>::type V4;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    V4* s_pos = reinterpret_cast<V4*>(smem_raw);
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_pos + plan.smem_uniq);
+    S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
+    S* s_ronsq = s_rcutsq + T2;
+
+    const unsigned int tile = blockIdx.x;
+    const unsigned int U = __ldg(plan.uniq_count + tile);
+    const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
+        s_pos[s] = ld4(a.pos + __ldg(uq + s));
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        {
+        const S rc = a.rcutsq[t];
+        S ron = S(0);
+        bool energy_shift = (SHIFT == 1);
+        if (SHIFT == 2)
+            {
+            ron = a.ronsq[t];
+            energy_shift = ron > rc;
+            }
+        s_coeff[t] = Pot::make(params[t], rc, energy_shift);
+        s_rcutsq[t] = rc;
+        s_ronsq[t] = ron;
+        }
+    __syncthreads();
+    const coeff_t c0 = s_coeff[0];
+    const S rc0 = s_rcutsq[0], ron0 = s_ronsq[0];
+
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    for (unsigned int p = gid; p < plan.tile_size; p += groups) // warp-uniform trip count (host picks blockDim)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        const bool active = idx < a.N;
+        PairAccum<S, VIRIAL> acc;
+        if (active)
+            {
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx));
+            const V4 pi = ld4(a.pos + idx);
+            const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
+
+            auto visit = [&](const unsigned int slot)
+            {
+                const V4 pj = s_pos[slot];
+                S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                const S rsq = separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
+                S fdivr = S(0), e = S(0);
+                if (SINGLE)
+                    {
+                    if (Pot::eval(rsq, rc0, c0, fdivr, e))
+                        {
+                        if (SHIFT == 2)
+                            xplor(rsq, rc0, ron0, fdivr, e);
+                        acc.add(dx, dy, dz, fdivr, fdivr, e);
+                        }
+                    }
+                else
+                    {
+                    const unsigned int tp = trow + type_of(pj.w);
+                    const S rcutsq = s_rcutsq[tp];
+                    if (Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
+                        {
+                        if (SHIFT == 2)
+                            xplor(rsq, rcutsq, s_ronsq[tp], fdivr, e);
+                        acc.add(dx, dy, dz, fdivr, fdivr, e);
+                        }
+                    }
+            };
+
+            unsigned int k = 4 * lane;
+            for (; k + 4 <= nn; k += 4 * TPP)
+                {
+                const uint2 s4 = __ldg(row + (k >> 2));
+                visit(s4.x & 0xffffu);
+                visit(s4.x >> 16);
+                visit(s4.y & 0xffffu);
+                visit(s4.y >> 16);
+                }
+            if (k < nn) // the row's ragged end: 1..3 entries (padding slots are never evaluated)
+                {
+                const uint2 s4 = __ldg(row + (k >> 2));
+                visit(s4.x & 0xffffu);
+                if (k + 1 < nn)
+                    visit(s4.x >> 16);
+                if (k + 2 < nn)
+                    visit(s4.y & 0xffffu);
+                }
+            }
+        acc.template reduce<TPP>();
+        if (active && lane == 0)
+            acc.store(a, idx);
+        }
     }
     } // namespace azb

@@ -11,19 +11,77 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
     typedef typename Pot::template Params<S> param_t;
     typedef typename Pot::template Coeff<S> coeff_t;
     const PairArgsDev<S> d = make_pair_args<S>(a);
+    const size_t T2 = (size_t)a.ntypes * a.ntypes;
+    const bool fastbox = d.box.flags == 7u;
+    if (a.tiles)
+        {
+        // tile-staged flavour: neighbour positions come from shared memory, so narrow groups lose nothing on
+        // coalescing and save on the reduction
+        unsigned int tpp = a.threads_per_particle;
+        if (tpp == 0)
+            {
+            const double nbar = a.N ? (double)a.size_nlist / (double)a.N : 0.0;
+            tpp = nbar <= 48 ? 2 : (nbar <= 160 ? 4 : 8);
+            }
+        if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16))
+            return AZB_ERR_BAD_ARGUMENT;
+        TilePlanDev plan;
+        unsigned int block = 0;
+        const int bad = make_tile_plan(a, tpp, plan, block);
+        if (bad)
+            return bad;
+        const size_t smem = (size_t)plan.smem_uniq * sizeof(typename vec4<S>::type) + T2 * (sizeof(coeff_t) + 2 * sizeof(S));
+        if (smem > AZB_MAX_SMEM)
+            return AZB_ERR_BAD_ARGUMENT;
+        const S lmin = fmin(d.box.Lx, fmin(d.box.Ly, d.box.Lz));
+        const S wrap_sq = S(0.25) * lmin * lmin;
+        const bool single = a.ntypes == 1;
+#define AZB_LAUNCH_T(TPP, FB, SG)                                                                                         \
+    do                                                                                                                    \
+        {                                                                                                                 \
+        ensure_smem<pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG>>(smem);                                          \
+        pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG><<<a.tiles->n_tiles, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
+        } while (0)
+#define AZB_CALL_T(TPP)                         \
+    do                                          \
+        {                                       \
+        if (fastbox && single)                  \
+            AZB_LAUNCH_T(TPP, true, true);      \
+        else if (fastbox)                       \
+            AZB_LAUNCH_T(TPP, true, false);     \
+        else                                    \
+            AZB_LAUNCH_T(TPP, false, false);    \
+        } while (0)
+        switch (tpp)
+            {
+        case 2:
+            AZB_CALL_T(2);
+            break;
+        case 4:
+            AZB_CALL_T(4);
+            break;
+        case 8:
+            AZB_CALL_T(8);
+            break;
+        default:
+            AZB_CALL_T(16);
+            break;
+            }
+#undef AZB_CALL_T
+#undef AZB_LAUNCH_T
+        return (int)cudaGetLastError();
+        }
     const unsigned int tpp = pick_tpp(a);
     if (!valid_tpp(tpp))
         return AZB_ERR_BAD_ARGUMENT;
     const unsigned int block = pick_block(a.block_size);
     const unsigned int per_block = block / tpp;
     const unsigned int grid = (a.N + per_block - 1) / per_block;
-    const size_t T2 = (size_t)a.ntypes * a.ntypes;
     const size_t smem = T2 * (sizeof(coeff_t) + 2 * sizeof(S));
     if (smem > 200 * 1024)
         return AZB_ERR_BAD_ARGUMENT;
     // kernel flavour: fully periodic orthorhombic box -> straight-line minimum image; one particle type -> coefficients
     // in registers. Anything else takes the general kernel.
-    const bool fastbox = d.box.flags == 7u;
     const int flavour = fastbox ? (a.ntypes == 1 ? 2 : 1) : 0;
 #define AZB_LAUNCH(TPP, FB, SG)                                                                                            \
     do                                                                                                                     \

@@ -1,0 +1,218 @@
+// azb_tiles.cu — tile plan builder (include/azb200.h, azb_tiles_build).
+//
+// The force kernels are bound by the L1 data pipe when every list entry costs a scattered 16 B gather from global
+// memory (one 128 B line per lane in the worst case). A tile of consecutive particles shares most of its neighbours,
+// so the kernels stage each tile's distinct neighbours in shared memory once (coalesced runs) and then address them
+// with 16-bit slots. This file derives that view from the HOOMD-layout list: one CTA per tile,
+//   1. insert every list entry of the tile into a shared-memory hash set (open addressing, atomicCAS),
+//   2. compact the set, bitonic-sort it ascending (runs of consecutive indices -> coalesced staging loads),
+//   3. record each key's rank in the table, and 4. rewrite every list entry as its rank (u16).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "azb200.h"
+
+namespace azb
+    {
+constexpr unsigned int EMPTY_KEY = 0xffffffffu;
+
+__device__ __forceinline__ unsigned int tile_hash(unsigned int j, unsigned int shift)
+    {
+    return (j * 2654435761u) >> shift;
+    }
+
+// dynamic shared memory: keys[hcap] u32 | list[ucap] u32 | vals[hcap] u16
+__global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __restrict__ n_neigh,
+                                                          const unsigned int* __restrict__ nlist,
+                                                          const size_t* __restrict__ head_list,
+                                                          const unsigned int N,
+                                                          const unsigned int tile_size,
+                                                          const unsigned int ucap,
+                                                          const unsigned int hcap_log2,
+                                                          unsigned int* __restrict__ uniq_count,
+                                                          unsigned int* __restrict__ uniq,
+                                                          uint16_t* __restrict__ slots,
+                                                          unsigned int* __restrict__ status)
+    {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const unsigned int hcap = 1u << hcap_log2;
+    const unsigned int hmask = hcap - 1u;
+    const unsigned int hshift = 32u - hcap_log2;
+    unsigned int* keys = reinterpret_cast<unsigned int*>(smem_raw);
+    unsigned int* list = keys + hcap;
+    uint16_t* vals = reinterpret_cast<uint16_t*>(list + ucap);
+    __shared__ unsigned int s_count, s_fill;
+
+    const unsigned int tile = blockIdx.x;
+    const unsigned int first = tile * tile_size;
+    const unsigned int last = min(first + tile_size, N);
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
+
+    for (unsigned int h = threadIdx.x; h < hcap; h += blockDim.x)
+        keys[h] = EMPTY_KEY;
+    if (threadIdx.x == 0)
+        {
+        s_count = 0;
+        s_fill = 0;
+        }
+    __syncthreads();
+
+    // 1. hash-set insert (a warp walks one row at a time: coalesced index reads)
+    for (unsigned int i = first + warp; i < last; i += nwarps)
+        {
+        const unsigned int nn = n_neigh[i];
+        const unsigned int* row = nlist + head_list[i];
+        for (unsigned int k = lane; k < nn; k += 32)
+            {
+            const unsigned int j = row[k];
+            unsigned int h = tile_hash(j, hshift);
+            while (*(volatile unsigned int*)&s_count <= ucap)
+                {
+                const unsigned int old = atomicCAS(&keys[h], EMPTY_KEY, j);
+                if (old == EMPTY_KEY)
+                    {
+                    atomicAdd(&s_count, 1u);
+                    break;
+                    }
+                if (old == j)
+                    break;
+                h = (h + 1u) & hmask;
+                }
+            }
+        }
+    __syncthreads();
+    const unsigned int U = s_count;
+    if (U > ucap)
+        {
+        if (threadIdx.x == 0)
+            {
+            uniq_count[tile] = EMPTY_KEY;
+            atomicMax(status + 0, U);
+            atomicExch(status + 1, 1u);
+            }
+        return;
+        }
+
+    // 2. compact + sort ascending
+    for (unsigned int h = threadIdx.x; h < hcap; h += blockDim.x)
+        {
+        const unsigned int key = keys[h];
+        if (key != EMPTY_KEY)
+            list[atomicAdd(&s_fill, 1u)] = key;
+        }
+    unsigned int P = 1;
+    while (P < U)
+        P <<= 1;
+    __syncthreads();
+    for (unsigned int s = U + threadIdx.x; s < P; s += blockDim.x)
+        list[s] = EMPTY_KEY; // P <= ucap because ucap is a power of two
+    __syncthreads();
+    for (unsigned int size = 2; size <= P; size <<= 1)
+        for (unsigned int stride = size >> 1; stride > 0; stride >>= 1)
+            {
+            for (unsigned int t = threadIdx.x; t < (P >> 1); t += blockDim.x)
+                {
+                const unsigned int lo = 2 * t - (t & (stride - 1u));
+                const unsigned int hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const unsigned int a = list[lo], b = list[hi];
+                if ((a > b) == up)
+                    {
+                    list[lo] = b;
+                    list[hi] = a;
+                    }
+                }
+            __syncthreads();
+            }
+
+    // 3. publish the list; remember each key's rank next to its table position
+    unsigned int* out = uniq + (size_t)tile * ucap;
+    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
+        {
+        const unsigned int key = list[s];
+        out[s] = key;
+        unsigned int h = tile_hash(key, hshift);
+        while (keys[h] != key)
+            h = (h + 1u) & hmask;
+        vals[h] = (uint16_t)s;
+        }
+    if (threadIdx.x == 0)
+        {
+        uniq_count[tile] = U;
+        atomicMax(status + 0, U);
+        }
+    __syncthreads();
+
+    // 4. list entry -> slot. Slot rows start at azb_slot_head(i) (8-byte aligned: four slots per vector load) and
+    // are padded to a multiple of four entries with slot 0.
+    for (unsigned int i = first + warp; i < last; i += nwarps)
+        {
+        const unsigned int nn = n_neigh[i];
+        const size_t head = head_list[i];
+        const size_t shead = (head + 4 * (size_t)i) & ~(size_t)3;
+        const unsigned int nn4 = (nn + 3u) & ~3u;
+        for (unsigned int k = lane; k < nn4; k += 32)
+            {
+            uint16_t v = 0;
+            if (k < nn)
+                {
+                const unsigned int j = nlist[head + k];
+                unsigned int h = tile_hash(j, hshift);
+                while (keys[h] != j)
+                    h = (h + 1u) & hmask;
+                v = vals[h];
+                }
+            slots[shead + k] = v;
+            }
+        // rows must be disjoint and ordered by particle for the padded layout to be collision-free
+        if (lane == 0 && i + 1 < N && head_list[i + 1] < head + nn)
+            atomicExch(status + 1, 2u);
+        }
+    }
+    } // namespace azb
+
+extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max_uniq, unsigned int* h_overflow, void* stream)
+    {
+    if (!a || !h_max_uniq || !h_overflow)
+        return AZB_ERR_BAD_ARGUMENT;
+    const unsigned int ts = a->tile_size, ucap = a->uniq_capacity;
+    if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u)))
+        return AZB_ERR_BAD_ARGUMENT;
+    *h_max_uniq = 0;
+    *h_overflow = 0;
+    if (a->N == 0)
+        return 0;
+    if (!a->d_n_neigh || !a->d_nlist || !a->d_head_list || !a->d_uniq_count || !a->d_uniq || !a->d_slots || !a->d_status)
+        return AZB_ERR_BAD_ARGUMENT;
+    cudaStream_t s = (cudaStream_t)stream;
+    unsigned int hcap_log2 = 0;
+    while ((1u << hcap_log2) < 2u * ucap)
+        ++hcap_log2;
+    const size_t hcap = (size_t)1 << hcap_log2;
+    const size_t smem = hcap * sizeof(unsigned int) + ucap * sizeof(unsigned int) + hcap * sizeof(uint16_t);
+    cudaError_t err = cudaMemsetAsync(a->d_status, 0, 2 * sizeof(unsigned int), s);
+    if (err != cudaSuccess)
+        return (int)err;
+    if (smem > 48 * 1024)
+        {
+        err = cudaFuncSetAttribute(azb::tiles_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess)
+            return (int)err;
+        }
+    const unsigned int n_tiles = (a->N + ts - 1) / ts;
+    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, a->d_uniq_count,
+                                                      a->d_uniq, a->d_slots, a->d_status);
+    err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return (int)err;
+    unsigned int h[2] = {0, 0};
+    err = cudaMemcpyAsync(h, a->d_status, sizeof(h), cudaMemcpyDeviceToHost, s);
+    if (err != cudaSuccess)
+        return (int)err;
+    err = cudaStreamSynchronize(s);
+    if (err != cudaSuccess)
+        return (int)err;
+    *h_max_uniq = h[0];
+    *h_overflow = h[1];
+    return 0;
+    }

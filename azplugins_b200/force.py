@@ -57,6 +57,10 @@ class Force:
         self.block_size = 0
         self.threads_per_particle = 0
         self.launches = 0
+        # neighbour data staged per tile in shared memory (azb_tile_plan) or gathered straight from global memory
+        self.use_tiles = True
+        self.tile_size = 128
+        self._plan = None
 
     def _attach(self, state):
         if state.device.type != "cuda":
@@ -101,6 +105,7 @@ class Pair(Force):
     _spec = None
     _accepted_modes = ("none", "shift", "xplor")
     _kind = _abi.KIND_PAIR
+    _tiled_kernels = True  # which kernel families have a tile-staged flavour
 
     def __init__(self, nlist, default_r_cut=None, default_r_on=0.0, mode="none"):
         super().__init__()
@@ -177,6 +182,8 @@ class Pair(Force):
         a.shift_mode = {"none": _abi.SHIFT_NONE, "shift": _abi.SHIFT_SHIFT, "xplor": _abi.SHIFT_XPLOR}[self.mode]
         a.compute_virial = 1 if self.compute_virial else 0
         a.threads_per_particle = self.threads_per_particle
+        self._plan = nl.tile_plan(st.N, self.tile_size) if (self.use_tiles and self._tiled_kernels) else None
+        a.tiles = self._plan.pointer() if self._plan is not None else None
 
     def compute(self, timestep=0):
         if self._state is None:
@@ -197,6 +204,7 @@ class DPDThermoPair(Pair):
 
     _accepted_modes = ("none",)
     _kind = _abi.KIND_DPD
+    _tiled_kernels = True
 
     def __init__(self, nlist, kT, default_r_cut=None):
         super().__init__(nlist, default_r_cut, 0.0, "none")
@@ -231,6 +239,7 @@ class AnisotropicPair(Pair):
 
     _accepted_modes = ("none", "shift")
     _kind = _abi.KIND_ANISO
+    _tiled_kernels = False
 
     def __init__(self, nlist, default_r_cut=None, mode="none"):
         super().__init__(nlist, default_r_cut, 0.0, mode)

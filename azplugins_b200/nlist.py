@@ -21,6 +21,7 @@ class NeighborList:
         self.nlist = None
         self.size_nlist = 0
         self._state = None
+        self._tiles = {}
 
     # consumers (pair forces) register so the list covers max r_cut per type pair, like hoomd's nlist subscribers
     def _subscribe(self, force):
@@ -30,6 +31,22 @@ class NeighborList:
 
     def invalidate(self):
         self.n_neigh = None
+        self._tiles = {}
+
+    def tile_plan(self, N, tile_size=128, uniq_capacity=2048):
+        """Tile plan of the current arrays (``azb_tiles_build``), built once per list rebuild and cached; ``None`` when a
+        tile holds more than ``uniq_capacity`` distinct neighbours even at the smallest tile size."""
+        key = (int(tile_size), int(uniq_capacity))
+        if key not in self._tiles:
+            from . import _nlist_gpu
+
+            plan = None
+            ts = int(tile_size)
+            while plan is None and ts >= 32:
+                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity))
+                ts //= 2
+            self._tiles[key] = plan
+        return self._tiles[key]
 
     def r_list(self, types):
         """(T,T) matrix of r_cut_max + buffer over all consumers; 0 where no consumer interacts."""
@@ -48,6 +65,7 @@ class NeighborList:
         self.head_list = torch.from_numpy(head_list.view(np.int64)).to(device)
         self.nlist = torch.from_numpy(nlist.view(np.int32) if nlist.size else np.zeros(1, np.int32)).to(device)
         self.size_nlist = int(nlist.size)
+        self._tiles = {}
         return self
 
     def compute(self, state):

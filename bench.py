@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--bits", type=int, default=32, choices=[32, 64])
     ap.add_argument("--tpp", type=int, default=0)
     ap.add_argument("--block", type=int, default=0)
+    ap.add_argument("--no-tiles", action="store_true", help="gather neighbour data from global memory instead of per-tile shared-memory staging")
+    ap.add_argument("--tile-size", type=int, default=128)
     ap.add_argument("--no-virial", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -315,6 +317,8 @@ def run_b200(args):
         f.compute_virial = virial
         f.threads_per_particle = args.tpp
         f.block_size = args.block
+        f.use_tiles = not args.no_tiles
+        f.tile_size = args.tile_size
         f._attach(st)
     t0 = time.perf_counter()
     nl.compute(st)

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define AZB200_ABI_VERSION 1
+#define AZB200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define AZB_API __attribute__((visibility("default")))
@@ -100,6 +100,28 @@ typedef struct azb_box
     unsigned char pad_[5];
     } azb_box;
 
+/* Tile plan (optional, azb_tiles_build below): a derived view of one neighbour list that lets the force kernels stage
+ * neighbour data in shared memory. Particles [t*tile_size, (t+1)*tile_size) form tile t; d_uniq holds, per tile, the
+ * ascending list of distinct particle indices appearing in its rows; d_slots holds, entry for entry, the position of
+ * each neighbour inside its tile's list: the slot of d_nlist[d_head_list[i] + k] is d_slots[AZB_SLOT_HEAD(head, i) + k].
+ * Slot rows are 8-byte aligned and padded to a multiple of four entries (kernels read four slots per load); this
+ * needs rows that are disjoint and ordered by particle (head_list[i+1] >= head_list[i] + n_neigh[i], as HOOMD's
+ * prefix-sum head list is), which azb_tiles_build verifies. The pair set is exactly the neighbour list's; only where
+ * pos[j] is read from changes. The plan is valid for as long as the neighbour-list arrays it was built from are
+ * unchanged (HOOMD: until the next rebuild). */
+#define AZB_SLOT_HEAD(head, i) (((size_t)(head) + 4 * (size_t)(i)) & ~(size_t)3)
+#define AZB_SLOTS_SIZE(size_nlist, N) ((size_t)(size_nlist) + 4 * (size_t)(N) + 4)
+typedef struct azb_tile_plan
+    {
+    unsigned int tile_size;           /* particles per tile: 32, 64, 128 or 256 */
+    unsigned int n_tiles;             /* ceil(N / tile_size) */
+    unsigned int uniq_capacity;       /* stride of d_uniq per tile; power of two, <= 4096 */
+    unsigned int max_uniq;            /* max over tiles of d_uniq_count (returned by azb_tiles_build) */
+    const unsigned int* d_uniq_count; /* [n_tiles] */
+    const unsigned int* d_uniq;       /* [n_tiles * uniq_capacity] */
+    const uint16_t* d_slots;          /* [AZB_SLOTS_SIZE(size_nlist, N)] */
+    } azb_tile_plan;
+
 /* mirrors HOOMD pair_args_t */
 typedef struct azb_pair_args
     {
@@ -122,6 +144,7 @@ typedef struct azb_pair_args
     unsigned int shift_mode;           /* azb_shift_mode */
     unsigned int compute_virial;       /* 0/1 */
     unsigned int threads_per_particle; /* 0 = engine picks; else power of two <= 32 */
+    const azb_tile_plan* tiles;        /* host pointer; NULL = gather neighbour data straight from global memory */
     } azb_pair_args;
 
 /* mirrors HOOMD dpd_pair_args_t: pair args + velocities, tags, RNG key material, dt and kT */
@@ -238,6 +261,29 @@ typedef struct azb_nlist_args
 AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
 AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
+
+/* ---- tile plan builder: one call per neighbour-list rebuild (the host class calls it when HOOMD's
+ * NeighborList::hasBeenUpdated(timestep) reports a rebuild). Writes d_uniq_count / d_uniq / d_slots and returns the
+ * largest per-tile unique count in *h_max_uniq. *h_overflow is set non-zero when some tile has more than uniq_capacity
+ * distinct neighbours (1) or the rows are not disjoint and ordered by particle (2): the plan is then unusable (retry
+ * with a smaller tile_size or pass tiles = NULL). Synchronises
+ * the stream. Rows may reference ghosts (indices in [N, n_max)). */
+typedef struct azb_tile_build_args
+    {
+    const unsigned int* d_n_neigh;   /* [N] */
+    const unsigned int* d_nlist;     /* [size_nlist] */
+    const size_t* d_head_list;       /* [N] */
+    size_t size_nlist;
+    unsigned int N;
+    unsigned int tile_size;
+    unsigned int uniq_capacity;
+    unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
+    unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
+    uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N)] */
+    unsigned int* d_status;          /* scratch, 2 x u32 on the device */
+    } azb_tile_build_args;
+
+AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_overflow, void* stream);
 
 /* ---- halo packing (SURVEY.md §8 e): d_out[e] = d_src[d_idx[e]] (+ d_shift[e].xyz when d_shift != NULL), Scalar4 rows.
  * Packs the boundary particles a neighbouring domain needs as ghosts into a contiguous send buffer; the periodic image

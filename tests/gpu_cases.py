@@ -39,7 +39,7 @@ def attach_with_oracle_nlist(force, state, hs):
 
 
 def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", ron_by=None, seed=101, tpp=0, virial=True, which=None,
-             buffer=0.3, system=None):
+             buffer=0.3, system=None, use_tiles=True, tile_size=128):
     spec = cases.SPEC_BY_API[api]
     box, pos, typeid = system if system is not None else cases.random_fluid(n, rho, ntypes, seed)
     par, rcsq, ronsq, rc = cases.pair_tables(spec, par_by, rc_by, ntypes, bits, ron_by)
@@ -69,12 +69,15 @@ def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", r
             f.r_on[key] = ron_by[(i, j)]
     f.threads_per_particle = tpp
     f.compute_virial = virial
+    f.use_tiles, f.tile_size = use_tiles, tile_size
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(0)
+    assert (f._plan is not None) == bool(use_tiles)
     return f, hs_b
 
 
-def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0, sim_seed=42, dt=0.01, kT=1.0, tpp=0, buffer=0.4):
+def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0, sim_seed=42, dt=0.01, kT=1.0, tpp=0, buffer=0.4,
+            use_tiles=True, tile_size=128):
     spec = cases.SPEC_BY_API["DPDGeneralWeight"]
     box, pos, typeid = cases.random_fluid(n, rho, ntypes, seed, jitter=0.5)
     rng = np.random.default_rng(seed + 1)
@@ -98,8 +101,10 @@ def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0
         f.params[key] = p
         f.r_cut[key] = rc_by[(i, j)]
     f.threads_per_particle = tpp
+    f.use_tiles, f.tile_size = use_tiles, tile_size
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(timestep)
+    assert (f._plan is not None) == bool(use_tiles)
     hs_b.hs64 = hs
     return f, hs_b, hs
 

@@ -188,21 +188,30 @@ cases.SPEC_BY_API["DPDConservativeGeneralWeight"] = __import__("azplugins_b200")
 @pytest.mark.parametrize("bits", [32, 64])
 @pytest.mark.parametrize("mode", ["none", "shift", "xplor"])
 @pytest.mark.parametrize("api", list(PAIRS))
-def test_pair_random_system(api, mode, bits):
+@pytest.mark.parametrize("tiles", [False, True], ids=["direct", "tiles"])
+def test_pair_random_system(tiles, api, mode, bits):
     par_by, rc_by = PAIRS[api]
     if api == "DPDConservativeGeneralWeight" and mode != "none":
         pytest.skip("mode none only")
     ron_by = {k: 0.8 * v for k, v in rc_by.items()}
     ron_by[(0, 1)] = rc_by[(0, 1)] + 0.5
-    f, hs = GC.run_pair(api, par_by, rc_by, bits, mode=mode, ron_by=ron_by)
-    _check(f"pair/{api}/{mode}/{bits}", f, hs, bits)
+    f, hs = GC.run_pair(api, par_by, rc_by, bits, mode=mode, ron_by=ron_by, use_tiles=tiles)
+    _check(f"pair/{'tiles' if tiles else 'direct'}/{api}/{mode}/{bits}", f, hs, bits)
 
 
 @pytest.mark.parametrize("tpp", [1, 2, 4, 8, 16, 32])
-def test_pair_threads_per_particle_variants(tpp):
+@pytest.mark.parametrize("tiles", [False, 32, 128, 256], ids=lambda t: f"tiles{t}")
+def test_pair_threads_per_particle_variants(tiles, tpp):
+    """Every lanes-per-particle width, neighbour positions gathered from global memory or staged per tile of 32 / 128 /
+    256 particles; one and two particle types (register / shared-memory coefficient flavours)."""
+    if tiles and tpp in (1, 32):
+        pytest.skip("tile kernels exist for 2..16 lanes per particle")
     par_by, rc_by = PAIRS["PerturbedLennardJones"]
-    f, hs = GC.run_pair("PerturbedLennardJones", par_by, rc_by, 32, n=3000, tpp=tpp)
-    _check(f"pair/plj/tpp{tpp}", f, hs, 32)
+    for ntypes in (1, 2):
+        pb = {k: v for k, v in par_by.items() if max(k) < ntypes}
+        rb = {k: v for k, v in rc_by.items() if max(k) < ntypes}
+        f, hs = GC.run_pair("PerturbedLennardJones", pb, rb, 32, n=3000, tpp=tpp, ntypes=ntypes, use_tiles=bool(tiles), tile_size=tiles or 128)
+        _check(f"pair/plj/tiles{tiles}/tpp{tpp}/T{ntypes}", f, hs, 32)
 
 
 def test_pair_without_virial_leaves_virial_untouched():
@@ -228,12 +237,28 @@ DPD_PARAMS = ({(0, 0): dict(A=25.0, gamma=4.5, s=2.0), (0, 1): dict(A=50.0, gamm
 @pytest.mark.parametrize("bits", [32, 64])
 @pytest.mark.parametrize("s_exp", [2.0, 0.5])
 @pytest.mark.parametrize("timestep", [0, 1, 2**32 - 1, 2**32])
-def test_dpd_random_system(timestep, s_exp, bits):
+@pytest.mark.parametrize("tiles", [False, True], ids=["direct", "tiles"])
+def test_dpd_random_system(tiles, timestep, s_exp, bits):
     par_by = {k: dict(v, s=s_exp) for k, v in DPD_PARAMS[0].items()}
-    f, hs, _ = GC.run_dpd(par_by, DPD_PARAMS[1], bits, timestep=timestep)
+    f, hs, _ = GC.run_dpd(par_by, DPD_PARAMS[1], bits, timestep=timestep, use_tiles=tiles)
     # w^(s/2) with s < 2 has an infinite slope at r_cut: pairs within 1e-4 of the cutoff are ill-conditioned in float
     # (one ulp of r moves the weight by percents) for the reference as much as for the kernel, so they are skipped
-    _check(f"dpd/s{s_exp}/t{timestep}/{bits}", f, hs, bits, ambiguous_rel=2e-6 if s_exp >= 2.0 else 2e-4)
+    _check(f"dpd/{'tiles' if tiles else 'direct'}/s{s_exp}/t{timestep}/{bits}", f, hs, bits, ambiguous_rel=2e-6 if s_exp >= 2.0 else 2e-4)
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("tpp", [1, 2, 4, 8, 16, 32])
+@pytest.mark.parametrize("tiles", [False, 32, 128, 256], ids=lambda t: f"tiles{t}")
+def test_dpd_lane_group_and_tile_variants(tiles, tpp, bits):
+    """Every lanes-per-particle width of the queue kernel, with neighbour data gathered from global memory or staged
+    per tile of 32 / 128 / 256 particles; one and two particle types (register / shared-memory coefficient flavours)."""
+    if tiles and tpp in (1, 32):
+        pytest.skip("tile kernels exist for 2..16 lanes per particle")
+    for ntypes in (1, 2):
+        par_by = {k: v for k, v in DPD_PARAMS[0].items() if max(k) < ntypes}
+        rc_by = {k: v for k, v in DPD_PARAMS[1].items() if max(k) < ntypes}
+        f, hs, _ = GC.run_dpd(par_by, rc_by, bits, n=3000, ntypes=ntypes, timestep=7, tpp=tpp, use_tiles=bool(tiles), tile_size=tiles or 128)
+        _check(f"dpd/variants/tiles{tiles}/tpp{tpp}/T{ntypes}/{bits}", f, hs, bits)
 
 
 def test_dpd_timestep_truncation_and_stream_change():

@@ -1,2 +1,8 @@
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-extras --tpp 4"
-$CMD > gpurun_out/plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:dpd_force_kernel -s 3 -c 2 -o gpurun_out/prof_dpd_q1 $CMD > gpurun_out/ncu.log 2>&1
+python -m pytest tests/test_gpu_tiles.py tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r1e_pytest.log
+run() { python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-extras "$@" 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$*', d['roofline']['kernel_ms'], d['value'], d['roofline']['frac'])" >> gpurun_out/r1e_sweep.log 2>&1; }
+for tpp in 2 4 8; do run --workload plj4m --tpp $tpp; done
+run --workload plj4m --tpp 4 --tile-size 256
+run --workload plj4m --tpp 4 --tile-size 64
+run --workload plj4m --no-tiles
+run --workload plj4m --tpp 4 --no-virial
+run --workload dpd
