@@ -41,6 +41,8 @@ class TilePlan(C.Structure):
         ("n_tiles", C.c_uint),
         ("uniq_capacity", C.c_uint),
         ("max_uniq", C.c_uint),
+        ("lane_width", C.c_uint),
+        ("max_slot_span", C.c_uint),
         ("d_uniq_count", C.c_void_p),
         ("d_uniq", C.c_void_p),
         ("d_slots", C.c_void_p),
@@ -56,6 +58,7 @@ class TileBuildArgs(C.Structure):
         ("N", C.c_uint),
         ("tile_size", C.c_uint),
         ("uniq_capacity", C.c_uint),
+        ("lane_width", C.c_uint),
         ("d_uniq_count", C.c_void_p),
         ("d_uniq", C.c_void_p),
         ("d_slots", C.c_void_p),
@@ -210,7 +213,7 @@ def load():
     lib.azb_gather_scalar4.restype = C.c_int
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.azb_tiles_build.restype = C.c_int
-    lib.azb_tiles_build.argtypes = [C.POINTER(TileBuildArgs), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_void_p]
+    lib.azb_tiles_build.argtypes = [C.POINTER(TileBuildArgs), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_void_p]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

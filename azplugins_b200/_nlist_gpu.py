@@ -64,23 +64,26 @@ def build_cell_nlist(nl, state, row_align=1):
 class TilePlanHandle:
     """Device arrays of one ``azb_tile_plan`` plus the C struct that points at them (kept alive together)."""
 
-    def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, uniq_count, uniq, slots, build_ms):
+    def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, lane_width, max_slot_span, uniq_count, uniq, slots, build_ms):
         self.uniq_count, self.uniq, self.slots = uniq_count, uniq, slots
         self.build_ms = build_ms
         self.c = _abi.TilePlan()
         self.c.tile_size, self.c.n_tiles, self.c.uniq_capacity, self.c.max_uniq = tile_size, n_tiles, uniq_capacity, max_uniq
+        self.c.lane_width, self.c.max_slot_span = lane_width, max_slot_span
         self.c.d_uniq_count, self.c.d_uniq, self.c.d_slots = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr()
 
     tile_size = property(lambda self: self.c.tile_size)
     n_tiles = property(lambda self: self.c.n_tiles)
     uniq_capacity = property(lambda self: self.c.uniq_capacity)
     max_uniq = property(lambda self: self.c.max_uniq)
+    lane_width = property(lambda self: self.c.lane_width)
+    max_slot_span = property(lambda self: self.c.max_slot_span)
 
     def pointer(self):
         return C.pointer(self.c)
 
 
-def build_tile_plan(nl, N, tile_size, uniq_capacity):
+def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1):
     """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles)."""
     dev = nl.n_neigh.device
     if dev.type != "cuda":
@@ -91,19 +94,20 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity):
     n_tiles = (N + tile_size - 1) // tile_size
     uniq_count = torch.zeros(n_tiles, dtype=torch.int32, device=dev)
     uniq = torch.empty(n_tiles * uniq_capacity, dtype=torch.int32, device=dev)
-    slots = torch.zeros(nl.size_nlist + 4 * N + 4, dtype=torch.int16, device=dev)  # AZB_SLOTS_SIZE
-    status = torch.zeros(2, dtype=torch.int32, device=dev)
+    slots = torch.zeros(nl.size_nlist + max(4 * lane_width, 8) * (N + 1), dtype=torch.int16, device=dev)  # AZB_SLOTS_SIZE
+    status = torch.zeros(4, dtype=torch.int32, device=dev)
     a = _abi.TileBuildArgs()
     a.d_n_neigh, a.d_nlist, a.d_head_list = nl.n_neigh.data_ptr(), nl.nlist.data_ptr(), nl.head_list.data_ptr()
-    a.size_nlist, a.N, a.tile_size, a.uniq_capacity = nl.size_nlist, N, tile_size, uniq_capacity
+    a.size_nlist, a.N, a.tile_size, a.uniq_capacity, a.lane_width = nl.size_nlist, N, tile_size, uniq_capacity, lane_width
     a.d_uniq_count, a.d_uniq, a.d_slots, a.d_status = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr(), status.data_ptr()
-    max_uniq, overflow = C.c_uint(0), C.c_uint(0)
+    max_uniq, max_span, overflow = C.c_uint(0), C.c_uint(0), C.c_uint(0)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    _abi.check(lib.azb_tiles_build(C.byref(a), C.byref(max_uniq), C.byref(overflow), stream), "azb_tiles_build")
+    _abi.check(lib.azb_tiles_build(C.byref(a), C.byref(max_uniq), C.byref(max_span), C.byref(overflow), stream), "azb_tiles_build")
     e1.record()
     e1.synchronize()
     if overflow.value:
         return None
-    return TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, uniq_count, uniq, slots, e0.elapsed_time(e1))
+    return TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, lane_width, max_span.value, uniq_count, uniq, slots,
+                          e0.elapsed_time(e1))

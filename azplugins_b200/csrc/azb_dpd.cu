@@ -51,11 +51,13 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
         {
         TilePlanDev plan;
         unsigned int block = 0;
-        const int bad = make_tile_plan(a.pair, tpp, plan, block);
+        const int bad = make_tile_plan(a.pair, tpp, 1u, plan, block);
         if (bad)
             return bad;
-        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + (size_t)block * 4 * sizeof(V4)
-                            + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int)) + T2 * sizeof(coeff_t);
+        if (a.pair.ntypes > 255)
+            return AZB_ERR_BAD_ARGUMENT; // the ring packs slot | type pair << 16
+        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + (size_t)(block / tpp) * (4 * tpp + 1) * sizeof(V4)
+                            + T2 * sizeof(coeff_t);
         if (smem > AZB_MAX_SMEM)
             return AZB_ERR_BAD_ARGUMENT;
         const unsigned int grid = a.pair.tiles->n_tiles;
@@ -89,7 +91,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     const unsigned int block = pick_block(a.pair.block_size);
     const unsigned int per_block = block / tpp;
     const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
-    const size_t smem = (size_t)block * 4 * sizeof(V4) + (single ? 0 : (size_t)block * 4 * sizeof(unsigned int)) + T2 * sizeof(coeff_t);
+    const size_t smem = (size_t)(block / tpp) * (4 * tpp + 1) * (sizeof(V4) + sizeof(unsigned int)) + T2 * sizeof(coeff_t);
     if (smem > AZB_MAX_SMEM)
         return AZB_ERR_BAD_ARGUMENT;
 #define AZB_LAUNCH_Q(TPP, FB, SG)                                                            \

@@ -113,15 +113,18 @@ __device__ __forceinline__ void dpd_pair(const V4& e, const V4& vi, const V4& vj
     }
 
 // The two-phase walk of one particle's row by a group of TPP lanes. `Src` supplies the neighbour data:
-//   Src::index(k)      list entry k of this particle's row (global index or tile slot)
-//   Src::pos(j), Src::vel(j), Src::tag(j)
+//   index(k)                list entry k of this particle's row (global particle index, or tile slot)
+//   pos(j), vel(j), tag(j)  the neighbour's data (global memory, or the tile's shared-memory copy)
+//   push / pop              how the neighbour index and the type pair travel through the ring
 // All 32 lanes of the warp must call this together (warp votes inside); lanes of idle groups pass nn = 0.
+// The ring of a group holds QCAP = 4 TPP entries at shared address q_addr (group rings are QCAP + 1 entries apart so
+// that equal positions of different groups fall into different banks).
 template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE, class Src>
 __device__ __forceinline__ void dpd_walk_row(const Src& src, const unsigned int nn, const typename vec4<S>::type& pi,
                                              const typename vec4<S>::type& vi, const unsigned int tag_i, const unsigned int trow,
-                                             const Box<S>& box, const S wrap_sq, const DPDThermo::Coeff<S>* __restrict__ s_coeff,
-                                             const DPDThermo::Coeff<S>& c0, typename vec4<S>::type* __restrict__ q,
-                                             unsigned int* __restrict__ qtp, const PhiloxRoundKeys& rk, PairAccum<S, VIRIAL>& acc)
+                                             const Box<S>& box, const S wrap_sq, const unsigned int coeff_addr,
+                                             const DPDThermo::Coeff<S>& c0, const unsigned int q_addr, const unsigned int qtp_addr,
+                                             const PhiloxRoundKeys& rk, PairAccum<S, VIRIAL>& acc)
     {
     typedef typename vec4<S>::type V4;
     typedef DPDThermo::Coeff<S> coeff_t;
@@ -129,81 +132,89 @@ __device__ __forceinline__ void dpd_walk_row(const Src& src, const unsigned int 
     constexpr unsigned int FULL = 0xffffffffu;
     const unsigned int lane = threadIdx.x % TPP;
     const unsigned int gshift = (threadIdx.x & 31u) & ~(unsigned int)(TPP - 1);
-    const unsigned int gmask = ((TPP == 32) ? FULL : ((1u << TPP) - 1u)) << gshift; // my group's lanes
-    const unsigned int ltmask = ((1u << lane) - 1u) << gshift;                      // ... below me
+    // lane masks of my group / of the lanes below me in it; pinned in registers (the compiler otherwise rebuilds them
+    // from %tid inside the loop)
+    unsigned int gmask, ltmask;
+    asm volatile("mov.u32 %0, %1;" : "=r"(gmask) : "r"(((TPP == 32) ? FULL : ((1u << TPP) - 1u)) << gshift));
+    asm volatile("mov.u32 %0, %1;" : "=r"(ltmask) : "r"(((1u << lane) - 1u) << gshift));
+    const unsigned int nn_warp = __reduce_max_sync(FULL, nn); // longest row among the warp's groups
 
-    unsigned int q_head = 0, q_cnt = 0; // group-uniform ring state
+    unsigned int q_head = 0, q_tail = 0; // group-uniform ring state (monotonic; position = counter mod QCAP)
     unsigned int k = lane;
-    unsigned int j_next = (k < nn) ? src.index(k) : 0u;
+    unsigned int j = 0;
+    if (k < nn)
+        j = src.index(k);
     for (;;)
         {
-        // ---- light phase: one list entry per lane ----------------------------------------------------------------
-        const unsigned int j = j_next;
-        const bool have = k < nn;
-        k += TPP;
-        if (k < nn)
-            j_next = src.index(k);
-        bool in = false;
-        S dx = S(0), dy = S(0), dz = S(0);
-        unsigned int tp = 0;
-        if (have)
+        // ---- light phase: one list entry per lane, skipped by the whole warp once its longest row is exhausted.
+        // Straight-line: a lane without an entry re-reads the last valid index (or 0) and is masked out of the cutoff
+        // test.
+        if (k - lane < nn_warp)
             {
-            const V4 pj = src.pos(j);
-            dx = pi.x - pj.x;
-            dy = pi.y - pj.y;
-            dz = pi.z - pj.z;
+            const bool have = k < nn;
+            const unsigned int jc = j;
+            k += TPP;
+            if (k < nn)
+                j = src.index(k);
+            const V4 pj = src.pos(jc);
+            S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+            unsigned int tp = 0;
             S rc = c0.rcutsq;
             if (!SINGLE)
                 {
                 tp = trow + type_of(pj.w);
-                rc = s_coeff[tp].rcutsq;
+                rc = lds_scalar(coeff_addr + tp * (unsigned int)sizeof(coeff_t) + 7u * (unsigned int)sizeof(S), S());
                 }
-            in = separation<FASTBOX>(box, wrap_sq, dx, dy, dz) < rc;
+            const bool in = have & (separation<FASTBOX>(box, wrap_sq, dx, dy, dz) < rc);
+            const unsigned int b = __ballot_sync(FULL, in);
+            // branch-free push: every lane computes its ring position, the store is predicated on `in`
+            const unsigned int at = (q_tail + __popc(b & ltmask)) & (QCAP - 1u);
+            sts4_if(in, q_addr + at * (unsigned int)sizeof(V4), pack_entry<S>(dx, dy, dz, Src::pack(jc, tp)));
+            if (!SINGLE && !Src::kPackedTypePair)
+                sts32_if(in, qtp_addr + at * 4u, tp);
+            q_tail += __popc(b & gmask);
             }
-        const unsigned int b = __ballot_sync(FULL, in);
-        if (in)
-            {
-            const unsigned int slot = (q_head + q_cnt + __popc(b & ltmask)) & (QCAP - 1u);
-            q[slot] = pack_entry<S>(dx, dy, dz, j);
-            if (!SINGLE)
-                qtp[slot] = tp;
-            }
-        q_cnt += __popc(b & gmask);
         const bool light_done = (k - lane) >= nn;
-        const bool all_ready = __all_sync(FULL, q_cnt >= TPP || light_done);
+        const unsigned int cnt = q_tail - q_head;
+        const bool all_ready = __all_sync(FULL, (cnt >= TPP) | light_done);
 
         // ---- heavy phase: one queued in-range pair per lane ------------------------------------------------------
-        if (all_ready || __any_sync(FULL, q_cnt > QCAP - TPP))
+        if (all_ready || __any_sync(FULL, cnt > QCAP - TPP))
             {
             __syncwarp();
-            if (lane < q_cnt)
+            if (lane < cnt)
                 {
-                const unsigned int slot = (q_head + lane) & (QCAP - 1u);
-                const V4 e = q[slot];
-                const unsigned int jj = entry_index(e.w);
+                const unsigned int at = (q_head + lane) & (QCAP - 1u);
+                const V4 e = lds4_at(q_addr + at * (unsigned int)sizeof(V4), S());
+                const unsigned int packed = entry_index(e.w);
+                const unsigned int jj = Src::index_of(packed);
                 const V4 vj = src.vel(jj);
                 const unsigned int tag_j = src.tag(jj);
                 if (SINGLE)
                     dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c0, rk, acc);
                 else
                     {
-                    const coeff_t c = s_coeff[qtp[slot]];
+                    const unsigned int tq = Src::kPackedTypePair ? Src::type_pair_of(packed) : lds32_at(qtp_addr + at * 4u);
+                    const unsigned int ca = coeff_addr + tq * (unsigned int)sizeof(coeff_t);
+                    const V4 c_lo = lds4_at(ca, S()), c_hi = lds4_at(ca + (unsigned int)sizeof(V4), S());
+                    coeff_t c;
+                    c.A = c_lo.x, c.gamma = c_lo.y, c.sigma = c_lo.z, c.rcutinv = c_lo.w;
+                    c.rcut = c_hi.x, c.half_s = c_hi.y, c.hA = c_hi.z, c.rcutsq = c_hi.w;
                     dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c, rk, acc);
                     }
                 }
-            const unsigned int n = min(q_cnt, (unsigned int)TPP);
-            q_head += n;
-            q_cnt -= n;
-            if (all_ready && __all_sync(FULL, light_done && q_cnt == 0u))
+            q_head += min(cnt, (unsigned int)TPP);
+            if (all_ready && __all_sync(FULL, light_done & (q_head == q_tail)))
                 break;
             }
         }
     }
 
-// neighbour data straight from global memory
+// neighbour data straight from global memory; the ring carries the global index, the type pair rides in a side ring
 template<class S> struct GlobalSource
     {
     typedef typename vec4<S>::type V4;
+    static constexpr bool kPackedTypePair = false;
     const unsigned int* row;
     const V4* pos_;
     const V4* vel_;
@@ -224,33 +235,62 @@ template<class S> struct GlobalSource
         {
         return __ldg(tag_ + j);
         }
+    __device__ __forceinline__ static unsigned int pack(unsigned int j, unsigned int)
+        {
+        return j;
+        }
+    __device__ __forceinline__ static unsigned int index_of(unsigned int packed)
+        {
+        return packed;
+        }
+    __device__ __forceinline__ static unsigned int type_pair_of(unsigned int)
+        {
+        return 0u;
+        }
     };
 
-// neighbour data from the tile's shared-memory copy, addressed by 16-bit slots
+// neighbour data from the tile's shared-memory copy, addressed by 16-bit slots; the ring carries slot | type pair << 16
 template<class S> struct TileSource
     {
     typedef typename vec4<S>::type V4;
+    static constexpr bool kPackedTypePair = true;
     const uint16_t* row;
-    const V4* pos_;
-    const V4* vel_;
-    const unsigned int* tag_;
+    unsigned int pos_addr, vel_addr, tag_addr; // shared addresses of the staged arrays
     __device__ __forceinline__ unsigned int index(unsigned int k) const
         {
         return __ldg(row + k);
         }
     __device__ __forceinline__ V4 pos(unsigned int j) const
         {
-        return pos_[j];
+        return lds4(pos_addr, j, S());
         }
     __device__ __forceinline__ V4 vel(unsigned int j) const
         {
-        return vel_[j];
+        return lds4(vel_addr, j, S());
         }
     __device__ __forceinline__ unsigned int tag(unsigned int j) const
         {
-        return tag_[j];
+        return lds32_at(tag_addr + j * 4u);
+        }
+    __device__ __forceinline__ static unsigned int pack(unsigned int j, unsigned int tp)
+        {
+        return j | (tp << 16);
+        }
+    __device__ __forceinline__ static unsigned int index_of(unsigned int packed)
+        {
+        return packed & 0xffffu;
+        }
+    __device__ __forceinline__ static unsigned int type_pair_of(unsigned int packed)
+        {
+        return packed >> 16;
         }
     };
+
+// shared-memory footprint of the rings of a CTA: one ring of QCAP + 1 entries per group (+ the type-pair side ring)
+template<class S, int TPP> __host__ __device__ constexpr unsigned int dpd_ring_stride()
+    {
+    return (4u * TPP + 1u) * (unsigned int)sizeof(typename vec4<S>::type);
+    }
 
 template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256)
@@ -262,15 +302,17 @@ __global__ void __launch_bounds__(256)
     const PairArgsDev<S>& a = d.pair;
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const unsigned int T2 = a.ntypes * a.ntypes;
-    V4* s_queue = reinterpret_cast<V4*>(smem_raw);
-    unsigned int* s_qtp = reinterpret_cast<unsigned int*>(s_queue + 4 * blockDim.x);
-    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_qtp + (SINGLE ? 0u : 4u * blockDim.x));
+    const unsigned int groups = blockDim.x / TPP;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(smem_raw);
+    V4* s_queue = reinterpret_cast<V4*>(s_coeff + T2);
+    unsigned int* s_qtp = reinterpret_cast<unsigned int*>(s_queue + groups * (QCAP + 1u));
     for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
         s_coeff[t] = DPDThermo::make(params[t], a.rcutsq[t], d.deltaT, d.T);
     __syncthreads();
 
     const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned int idx = gtid / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
     const bool active = idx < a.N;
 
     unsigned int nn = 0;
@@ -288,15 +330,16 @@ __global__ void __launch_bounds__(256)
         }
     const coeff_t c0 = s_coeff[0]; // single-type systems keep the one coefficient set in registers
     PairAccum<S, VIRIAL> acc;
-    dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, s_coeff, c0,
-                                                  s_queue + (threadIdx.x / TPP) * QCAP, s_qtp + (threadIdx.x / TPP) * QCAP, d.rk, acc);
+    dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, smem_addr(s_coeff), c0,
+                                                  smem_addr(s_queue) + gid * dpd_ring_stride<S, TPP>(),
+                                                  smem_addr(s_qtp) + gid * (QCAP + 1u) * 4u, d.rk, acc);
     acc.template reduce<TPP>();
     if (active && threadIdx.x % TPP == 0)
         acc.store(a, idx);
     }
 
-// One CTA per tile: stage pos/vel/tag of the tile's distinct neighbours (ascending indices -> coalesced runs), then
-// every group walks tile_size / (blockDim / TPP) particles against the staged copy.
+// One CTA per tile: stage pos/vel/tag of the tile's distinct neighbours (ascending indices -> coalesced runs; four
+// gathers per thread in flight), then every group walks tile_size / (blockDim / TPP) particles against the staged copy.
 template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256)
     dpd_tile_kernel(const DPDArgsDev<S> d, const TilePlanDev plan, const DPDThermo::Params<S>* __restrict__ params, const S wrap_sq)
@@ -307,31 +350,51 @@ __global__ void __launch_bounds__(256)
     const PairArgsDev<S>& a = d.pair;
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const unsigned int T2 = a.ntypes * a.ntypes;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
     V4* s_pos = reinterpret_cast<V4*>(smem_raw);
     V4* s_vel = s_pos + plan.smem_uniq;
-    V4* s_queue = s_vel + plan.smem_uniq;
-    unsigned int* s_tag = reinterpret_cast<unsigned int*>(s_queue + 4 * blockDim.x);
-    unsigned int* s_qtp = s_tag + plan.smem_uniq;
-    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_qtp + (SINGLE ? 0u : 4u * blockDim.x));
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_vel + plan.smem_uniq);
+    V4* s_queue = reinterpret_cast<V4*>(s_coeff + T2);
+    unsigned int* s_tag = reinterpret_cast<unsigned int*>(s_queue + groups * (QCAP + 1u));
 
     const unsigned int tile = blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
-    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
+    for (unsigned int s0 = threadIdx.x; s0 < U; s0 += 4 * blockDim.x)
         {
-        const unsigned int g = __ldg(uq + s);
-        s_pos[s] = ld4(a.pos + g);
-        s_vel[s] = ld4(d.vel + g);
-        s_tag[s] = __ldg(d.tag + g);
+        unsigned int g[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            g[u] = (s0 + u * blockDim.x < U) ? __ldg(uq + s0 + u * blockDim.x) : 0xffffffffu;
+        V4 pv[4], vv[4];
+        unsigned int tv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                pv[u] = ld4(a.pos + g[u]);
+                vv[u] = ld4(d.vel + g[u]);
+                tv[u] = __ldg(d.tag + g[u]);
+                }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                const unsigned int s = s0 + u * blockDim.x;
+                s_pos[s] = pv[u];
+                s_vel[s] = vv[u];
+                s_tag[s] = tv[u];
+                }
         }
     for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
         s_coeff[t] = DPDThermo::make(params[t], a.rcutsq[t], d.deltaT, d.T);
     __syncthreads();
     const coeff_t c0 = s_coeff[0];
+    const unsigned int coeff_addr = smem_addr(s_coeff);
+    const unsigned int q_addr = smem_addr(s_queue) + gid * dpd_ring_stride<S, TPP>();
 
-    const unsigned int groups = blockDim.x / TPP;
-    const unsigned int gid = threadIdx.x / TPP;
-    TileSource<S> src = {plan.slots, s_pos, s_vel, s_tag};
+    TileSource<S> src = {plan.slots, smem_addr(s_pos), smem_addr(s_vel), smem_addr(s_tag)};
     for (unsigned int p = gid; p < plan.tile_size; p += groups) // warp-uniform trip count (host picks blockDim)
         {
         const unsigned int idx = tile * plan.tile_size + p;
@@ -342,15 +405,14 @@ __global__ void __launch_bounds__(256)
         if (active)
             {
             nn = __ldg(a.n_neigh + idx);
-            src.row = plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx);
+            src.row = plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, 1);
             pi = ld4(a.pos + idx);
             vi = ld4(d.vel + idx);
             tag_i = __ldg(d.tag + idx);
             trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
             }
         PairAccum<S, VIRIAL> acc;
-        dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, s_coeff, c0, s_queue + gid * QCAP,
-                                                      s_qtp + gid * QCAP, d.rk, acc);
+        dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, coeff_addr, c0, q_addr, 0u, d.rk, acc);
         acc.template reduce<TPP>();
         if (active && threadIdx.x % TPP == 0)
             acc.store(a, idx);

@@ -84,16 +84,17 @@ template<auto KERNEL> inline void ensure_smem(size_t bytes)
 
 // Validates a.tiles against the launch and picks the CTA size: blockDim / tpp groups, each walking
 // tile_size / groups particles (both powers of two, so every warp runs the same number of passes).
-inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, TilePlanDev& plan, unsigned int& block)
+inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int slot_lane_width, TilePlanDev& plan, unsigned int& block)
     {
     const azb_tile_plan& t = *a.tiles;
     const unsigned int ts = t.tile_size;
     if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || t.n_tiles != (a.N + ts - 1) / ts || t.max_uniq > t.uniq_capacity
-        || !t.d_uniq_count || !t.d_uniq || !t.d_slots)
+        || !t.d_uniq_count || !t.d_uniq || !t.d_slots || t.lane_width != slot_lane_width)
         return AZB_ERR_BAD_ARGUMENT;
     plan.tile_size = ts;
     plan.uniq_capacity = t.uniq_capacity;
     plan.smem_uniq = ((t.max_uniq > 0 ? t.max_uniq : 1u) + 7u) & ~7u;
+    plan.smem_span = (t.max_slot_span + 15u) & ~15u;
     plan.uniq_count = t.d_uniq_count;
     plan.uniq = t.d_uniq;
     plan.slots = t.d_slots;

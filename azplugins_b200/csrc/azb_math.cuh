@@ -43,6 +43,84 @@ __device__ __forceinline__ void st4(vec4<double>::type* p, double x, double y, d
     asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(x), "d"(y), "d"(z), "d"(w) : "memory");
     }
 
+// ---- explicit shared-memory accesses at 32-bit shared addresses -----------------------------------------------------
+// (the address stays a plain register add instead of a generic-pointer reconstruction per access)
+__device__ __forceinline__ unsigned int smem_addr(const void* p)
+    {
+    // volatile: computed once where written, never rematerialised inside a loop
+    unsigned int r;
+    asm volatile("{ .reg .u64 t; cvta.to.shared.u64 t, %1; cvt.u32.u64 %0, t; }" : "=r"(r) : "l"(p));
+    return r;
+    }
+__device__ __forceinline__ float4 lds4_at(unsigned int addr, float)
+    {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+    return r;
+    }
+__device__ __forceinline__ vec4<double>::type lds4_at(unsigned int addr, double)
+    {
+    vec4<double>::type r;
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "r"(addr));
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2+16];" : "=d"(r.z), "=d"(r.w) : "r"(addr));
+    return r;
+    }
+__device__ __forceinline__ void sts4_at(unsigned int addr, const float4& v)
+    {
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+__device__ __forceinline__ void sts4_at(unsigned int addr, const vec4<double>::type& v)
+    {
+    asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(addr), "d"(v.x), "d"(v.y) : "memory");
+    asm volatile("st.shared.v2.f64 [%0+16], {%1,%2};" ::"r"(addr), "d"(v.z), "d"(v.w) : "memory");
+    }
+// predicated stores (no branch: lanes with p == false issue nothing to memory)
+__device__ __forceinline__ void sts4_if(bool p, unsigned int addr, const float4& v)
+    {
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %5, 0; @q st.shared.v4.f32 [%0], {%1,%2,%3,%4}; }" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w), "r"((unsigned int)p)
+                 : "memory");
+    }
+__device__ __forceinline__ void sts4_if(bool p, unsigned int addr, const vec4<double>::type& v)
+    {
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %5, 0; @q st.shared.v2.f64 [%0], {%1,%2}; @q st.shared.v2.f64 [%0+16], {%3,%4}; }" ::"r"(addr),
+                 "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w), "r"((unsigned int)p)
+                 : "memory");
+    }
+__device__ __forceinline__ void sts32_if(bool p, unsigned int addr, unsigned int v)
+    {
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.shared.u32 [%0], %1; }" ::"r"(addr), "r"(v), "r"((unsigned int)p) : "memory");
+    }
+__device__ __forceinline__ unsigned int lds32_at(unsigned int addr)
+    {
+    unsigned int r;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(addr));
+    return r;
+    }
+__device__ __forceinline__ void sts32_at(unsigned int addr, unsigned int v)
+    {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+    }
+__device__ __forceinline__ float lds_scalar(unsigned int addr, float)
+    {
+    return __uint_as_float(lds32_at(addr));
+    }
+__device__ __forceinline__ double lds_scalar(unsigned int addr, double)
+    {
+    double r;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(r) : "r"(addr));
+    return r;
+    }
+// Scalar4 element `slot` of a shared-memory array at shared address `base`
+__device__ __forceinline__ float4 lds4(unsigned int base, unsigned int slot, float)
+    {
+    return lds4_at(base + slot * 16u, float());
+    }
+__device__ __forceinline__ vec4<double>::type lds4(unsigned int base, unsigned int slot, double)
+    {
+    return lds4_at(base + slot * 32u, double());
+    }
+
 __device__ __forceinline__ unsigned int type_of(float w)
     {
     return (unsigned int)__float_as_int(w);

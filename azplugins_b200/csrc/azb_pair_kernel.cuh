@@ -40,6 +40,7 @@ template<class S> struct PairArgsDev
 struct TilePlanDev
     {
     unsigned int tile_size, uniq_capacity, smem_uniq; // smem_uniq: capacity of the staging arrays (>= max_uniq)
+    unsigned int smem_span;                           // capacity of the staged slot rows, entries (>= max_slot_span)
     const unsigned int* uniq_count;
     const unsigned int* uniq;
     const uint16_t* slots;
@@ -213,7 +214,22 @@ __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a,
         acc.store(a, idx);
     }
 // Separation of one list entry with the lazy minimum image: in the fully periodic orthorhombic box a pair whose raw
-// separation is inside half the shortest box edge (wrap_sq = (L_min / 2)^2) needs no wrap. Returns r^2.
+// separation is inside half the shortest box edge (wrap_sq = (L_min / 2)^2) needs no wrap. Returns r^2. The wrap
+// itself is a real (not inlined) call so that the compiler cannot turn the rare path into predicated straight-line code
+// that every list entry would pay for.
+template<class S> struct Sep
+    {
+    S dx, dy, dz, rsq;
+    };
+template<class S> __device__ __noinline__ Sep<S> wrapped_separation(S Lx, S Ly, S Lz, S Lxinv, S Lyinv, S Lzinv, S dx, S dy, S dz)
+    {
+    Sep<S> r;
+    r.dx = dx - Lx * rint_small(dx * Lxinv);
+    r.dy = dy - Ly * rint_small(dy * Lyinv);
+    r.dz = dz - Lz * rint_small(dz * Lzinv);
+    r.rsq = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz;
+    return r;
+    }
 template<bool FASTBOX, class S> __device__ __forceinline__ S separation(const Box<S>& box, S wrap_sq, S& dx, S& dy, S& dz)
     {
     if (FASTBOX)
@@ -221,8 +237,11 @@ template<bool FASTBOX, class S> __device__ __forceinline__ S separation(const Bo
         S rsq = dx * dx + dy * dy + dz * dz;
         if (rsq > wrap_sq) // only then can a component exceed half a box edge
             {
-            min_image_ortho(box, dx, dy, dz);
-            rsq = dx * dx + dy * dy + dz * dz;
+            const Sep<S> w = wrapped_separation(box.Lx, box.Ly, box.Lz, box.Lxinv, box.Lyinv, box.Lzinv, dx, dy, dz);
+            dx = w.dx;
+            dy = w.dy;
+            dz = w.dz;
+            rsq = w.rsq;
             }
         return rsq;
         }
@@ -231,7 +250,9 @@ template<bool FASTBOX, class S> __device__ __forceinline__ S separation(const Bo
     }
 
 // One CTA per tile of consecutive particles. Stage: s_pos[s] = pos[uniq[s]] (ascending indices -> coalesced runs).
-// Walk: blockDim / TPP groups, each taking tile_size / groups particles; a lane reads four 16-bit slots per load.
+// Walk: blockDim / TPP groups, each taking tile_size / groups particles. A row is read in blocks of 4 TPP entries:
+// every lane fetches its four slots of a block with one 8-byte load (the next block's load is issued before the
+// current block is evaluated) and the lanes of a group visit consecutive list entries together (azb200.h, slot rows).
 template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, const TilePlanDev plan,
                                                         const typename Pot::template Params<S>* __restrict__ params, const S wrap_sq)
@@ -267,7 +288,9 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
     __syncthreads();
     const coeff_t c0 = s_coeff[0];
     const S rc0 = s_rcutsq[0], ron0 = s_ronsq[0];
+    const unsigned int pos_base = smem_addr(s_pos);
 
+    constexpr unsigned int M = 4 * TPP; // entries per block of a row
     const unsigned int groups = blockDim.x / TPP;
     const unsigned int gid = threadIdx.x / TPP;
     const unsigned int lane = threadIdx.x % TPP;
@@ -279,19 +302,19 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
         if (active)
             {
             const unsigned int nn = __ldg(a.n_neigh + idx);
-            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx));
+            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
             const V4 pi = ld4(a.pos + idx);
             const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
 
-            auto visit = [&](const unsigned int slot)
+            auto visit = [&](const unsigned int slot, const bool valid)
             {
-                const V4 pj = s_pos[slot];
+                const V4 pj = lds4(pos_base, slot, S());
                 S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
                 const S rsq = separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
                 S fdivr = S(0), e = S(0);
                 if (SINGLE)
                     {
-                    if (Pot::eval(rsq, rc0, c0, fdivr, e))
+                    if (valid && Pot::eval(rsq, rc0, c0, fdivr, e))
                         {
                         if (SHIFT == 2)
                             xplor(rsq, rc0, ron0, fdivr, e);
@@ -302,7 +325,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
                     {
                     const unsigned int tp = trow + type_of(pj.w);
                     const S rcutsq = s_rcutsq[tp];
-                    if (Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
+                    if (valid && Pot::eval(rsq, rcutsq, s_coeff[tp], fdivr, e))
                         {
                         if (SHIFT == 2)
                             xplor(rsq, rcutsq, s_ronsq[tp], fdivr, e);
@@ -311,23 +334,28 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
                     }
             };
 
-            unsigned int k = 4 * lane;
-            for (; k + 4 <= nn; k += 4 * TPP)
+            const unsigned int full = nn / M;             // blocks whose 4 TPP entries all exist
+            const unsigned int nblk = (nn + M - 1u) / M;  // ... plus the ragged last one
+            uint2 next = make_uint2(0u, 0u);
+            if (nblk)
+                next = __ldg(row);
+            for (unsigned int b = 0; b < full; ++b)
                 {
-                const uint2 s4 = __ldg(row + (k >> 2));
-                visit(s4.x & 0xffffu);
-                visit(s4.x >> 16);
-                visit(s4.y & 0xffffu);
-                visit(s4.y >> 16);
+                const uint2 s4 = next;
+                if (b + 1 < nblk)
+                    next = __ldg(row + (b + 1) * TPP);
+                visit(s4.x & 0xffffu, true);
+                visit(s4.x >> 16, true);
+                visit(s4.y & 0xffffu, true);
+                visit(s4.y >> 16, true);
                 }
-            if (k < nn) // the row's ragged end: 1..3 entries (padding slots are never evaluated)
+            if (full < nblk) // entries full*M + u*TPP + lane, u = 0..3, that exist (padding slots are never evaluated)
                 {
-                const uint2 s4 = __ldg(row + (k >> 2));
-                visit(s4.x & 0xffffu);
-                if (k + 1 < nn)
-                    visit(s4.x >> 16);
-                if (k + 2 < nn)
-                    visit(s4.y & 0xffffu);
+                const unsigned int e0 = full * M + lane;
+                visit(next.x & 0xffffu, e0 < nn);
+                visit(next.x >> 16, e0 + TPP < nn);
+                visit(next.y & 0xffffu, e0 + 2 * TPP < nn);
+                visit(next.y >> 16, e0 + 3 * TPP < nn);
                 }
             }
         acc.template reduce<TPP>();

@@ -16,18 +16,13 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
     if (a.tiles)
         {
         // tile-staged flavour: neighbour positions come from shared memory, so narrow groups lose nothing on
-        // coalescing and save on the reduction
-        unsigned int tpp = a.threads_per_particle;
-        if (tpp == 0)
-            {
-            const double nbar = a.N ? (double)a.size_nlist / (double)a.N : 0.0;
-            tpp = nbar <= 48 ? 2 : (nbar <= 160 ? 4 : 8);
-            }
-        if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16))
+        // coalescing and save on the reduction. The slot rows are laid out for one group width: that is the width.
+        const unsigned int tpp = a.tiles->lane_width;
+        if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16) || (a.threads_per_particle && a.threads_per_particle != tpp))
             return AZB_ERR_BAD_ARGUMENT;
         TilePlanDev plan;
         unsigned int block = 0;
-        const int bad = make_tile_plan(a, tpp, plan, block);
+        const int bad = make_tile_plan(a, tpp, tpp, plan, block);
         if (bad)
             return bad;
         const size_t smem = (size_t)plan.smem_uniq * sizeof(typename vec4<S>::type) + T2 * (sizeof(coeff_t) + 2 * sizeof(S));

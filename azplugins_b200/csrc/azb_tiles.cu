@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
                                                           const unsigned int tile_size,
                                                           const unsigned int ucap,
                                                           const unsigned int hcap_log2,
+                                                          const unsigned int W,
                                                           unsigned int* __restrict__ uniq_count,
                                                           unsigned int* __restrict__ uniq,
                                                           uint16_t* __restrict__ slots,
@@ -143,42 +144,49 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         }
     __syncthreads();
 
-    // 4. list entry -> slot. Slot rows start at azb_slot_head(i) (8-byte aligned: four slots per vector load) and
-    // are padded to a multiple of four entries with slot 0.
+    // 4. list entry -> slot, stored in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD)
+    const unsigned int M = 4u * W;
     for (unsigned int i = first + warp; i < last; i += nwarps)
         {
         const unsigned int nn = n_neigh[i];
         const size_t head = head_list[i];
-        const size_t shead = (head + 4 * (size_t)i) & ~(size_t)3;
-        const unsigned int nn4 = (nn + 3u) & ~3u;
-        for (unsigned int k = lane; k < nn4; k += 32)
+        const size_t shead = AZB_SLOT_HEAD(head, i, W);
+        const unsigned int nnp = (nn + M - 1u) / M * M;
+        for (unsigned int e = lane; e < nnp; e += 32)
             {
             uint16_t v = 0;
-            if (k < nn)
+            if (e < nn)
                 {
-                const unsigned int j = nlist[head + k];
+                const unsigned int j = nlist[head + e];
                 unsigned int h = tile_hash(j, hshift);
                 while (keys[h] != j)
                     h = (h + 1u) & hmask;
                 v = vals[h];
                 }
-            slots[shead + k] = v;
+            const unsigned int r = e % M;
+            slots[shead + (e - r) + 4u * (r % W) + r / W] = v;
             }
         // rows must be disjoint and ordered by particle for the padded layout to be collision-free
         if (lane == 0 && i + 1 < N && head_list[i + 1] < head + nn)
             atomicExch(status + 1, 2u);
+        if (lane == 0 && i + 1 == last) // extent of the tile's slot rows (kernels that stage them size their buffer by it)
+            atomicMax(status + 2, (unsigned int)(shead + nnp - AZB_SLOT_HEAD(head_list[first], first, W)));
         }
     }
     } // namespace azb
 
-extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max_uniq, unsigned int* h_overflow, void* stream)
+extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,
+                               void* stream)
     {
-    if (!a || !h_max_uniq || !h_overflow)
+    if (!a || !h_max_uniq || !h_max_slot_span || !h_overflow)
         return AZB_ERR_BAD_ARGUMENT;
     const unsigned int ts = a->tile_size, ucap = a->uniq_capacity;
-    if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u)))
+    const unsigned int W = a->lane_width;
+    if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u))
+        || !(W == 1 || W == 2 || W == 4 || W == 8 || W == 16))
         return AZB_ERR_BAD_ARGUMENT;
     *h_max_uniq = 0;
+    *h_max_slot_span = 0;
     *h_overflow = 0;
     if (a->N == 0)
         return 0;
@@ -190,7 +198,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         ++hcap_log2;
     const size_t hcap = (size_t)1 << hcap_log2;
     const size_t smem = hcap * sizeof(unsigned int) + ucap * sizeof(unsigned int) + hcap * sizeof(uint16_t);
-    cudaError_t err = cudaMemsetAsync(a->d_status, 0, 2 * sizeof(unsigned int), s);
+    cudaError_t err = cudaMemsetAsync(a->d_status, 0, 4 * sizeof(unsigned int), s);
     if (err != cudaSuccess)
         return (int)err;
     if (smem > 48 * 1024)
@@ -200,12 +208,12 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
             return (int)err;
         }
     const unsigned int n_tiles = (a->N + ts - 1) / ts;
-    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, a->d_uniq_count,
+    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, W, a->d_uniq_count,
                                                       a->d_uniq, a->d_slots, a->d_status);
     err = cudaGetLastError();
     if (err != cudaSuccess)
         return (int)err;
-    unsigned int h[2] = {0, 0};
+    unsigned int h[4] = {0, 0, 0, 0};
     err = cudaMemcpyAsync(h, a->d_status, sizeof(h), cudaMemcpyDeviceToHost, s);
     if (err != cudaSuccess)
         return (int)err;
@@ -214,5 +222,6 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         return (int)err;
     *h_max_uniq = h[0];
     *h_overflow = h[1];
+    *h_max_slot_span = h[2];
     return 0;
     }

@@ -124,6 +124,13 @@ class Pair(Force):
     def _cpp_class_name(self):
         return self._spec.cpp_class
 
+    def _slot_lane_width(self, nbar):
+        """Slot-row layout of the tile plan = lanes per particle of the tile kernel: narrow groups (positions come from
+        shared memory, so nothing is lost on coalescing) unless rows are long."""
+        if self.threads_per_particle:
+            return self.threads_per_particle
+        return 2 if nbar <= 200 else 4
+
     def _pair_value(self, store, a, b, default):
         key = tuple(sorted((a, b)))
         if dict.__contains__(store, key):
@@ -182,7 +189,9 @@ class Pair(Force):
         a.shift_mode = {"none": _abi.SHIFT_NONE, "shift": _abi.SHIFT_SHIFT, "xplor": _abi.SHIFT_XPLOR}[self.mode]
         a.compute_virial = 1 if self.compute_virial else 0
         a.threads_per_particle = self.threads_per_particle
-        self._plan = nl.tile_plan(st.N, self.tile_size) if (self.use_tiles and self._tiled_kernels) else None
+        self._plan = None
+        if self.use_tiles and self._tiled_kernels:
+            self._plan = nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nl.mean_neighbors(st.N)))
         a.tiles = self._plan.pointer() if self._plan is not None else None
 
     def compute(self, timestep=0):
@@ -210,6 +219,9 @@ class DPDThermoPair(Pair):
         super().__init__(nlist, default_r_cut, 0.0, "none")
         self.kT = kT
         self.dt = 0.005  # set by the integrator (hoomd passes m_deltaT to the force)
+
+    def _slot_lane_width(self, nbar):
+        return 1  # the DPD queue kernels read slots one at a time in list order
 
     def _kT_at(self, timestep):
         return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)

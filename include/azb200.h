@@ -103,23 +103,31 @@ typedef struct azb_box
 /* Tile plan (optional, azb_tiles_build below): a derived view of one neighbour list that lets the force kernels stage
  * neighbour data in shared memory. Particles [t*tile_size, (t+1)*tile_size) form tile t; d_uniq holds, per tile, the
  * ascending list of distinct particle indices appearing in its rows; d_slots holds, entry for entry, the position of
- * each neighbour inside its tile's list: the slot of d_nlist[d_head_list[i] + k] is d_slots[AZB_SLOT_HEAD(head, i) + k].
- * Slot rows are 8-byte aligned and padded to a multiple of four entries (kernels read four slots per load); this
- * needs rows that are disjoint and ordered by particle (head_list[i+1] >= head_list[i] + n_neigh[i], as HOOMD's
- * prefix-sum head list is), which azb_tiles_build verifies. The pair set is exactly the neighbour list's; only where
- * pos[j] is read from changes. The plan is valid for as long as the neighbour-list arrays it was built from are
- * unchanged (HOOMD: until the next rebuild). */
-#define AZB_SLOT_HEAD(head, i) (((size_t)(head) + 4 * (size_t)(i)) & ~(size_t)3)
-#define AZB_SLOTS_SIZE(size_nlist, N) ((size_t)(size_nlist) + 4 * (size_t)(N) + 4)
+ * each neighbour inside its tile's list. Slot rows are laid out for the kernel that reads them: a group of W =
+ * lane_width lanes walks a row in blocks of 4W entries, each lane fetching its four entries of a block with one 8-byte
+ * load, and the lanes of a group touching consecutive list entries at the same time (consecutive entries are mostly
+ * consecutive slots, i.e. distinct shared-memory banks). So the slot of list entry e = b*4W + u*W + l of particle i
+ * (d_nlist[d_head_list[i] + e]) is stored at d_slots[AZB_SLOT_HEAD(head, i, W) + b*4W + 4*l + u], rows are padded with
+ * slot 0 to a multiple of 4W entries and start on a multiple of max(4W, 8) entries, i.e. 16 bytes (W = 1 is the plain
+ * order). This needs rows that
+ * are disjoint and ordered by particle (head_list[i+1] >= head_list[i] + n_neigh[i], as HOOMD's prefix-sum head list
+ * is), which azb_tiles_build verifies. The pair set is exactly the neighbour list's; only where pos[j] is read from
+ * changes. The plan is valid for as long as the neighbour-list arrays it was built from are unchanged (HOOMD: until
+ * the next rebuild). */
+#define AZB_SLOT_ROW_ALIGN(W) ((size_t)((W) < 2 ? 8 : 4 * (W))) /* entries; rows are padded to a multiple of 4W, 16-byte aligned */
+#define AZB_SLOT_HEAD(head, i, W) (((size_t)(head) + AZB_SLOT_ROW_ALIGN(W) * (size_t)(i)) & ~(AZB_SLOT_ROW_ALIGN(W) - 1))
+#define AZB_SLOTS_SIZE(size_nlist, N, W) ((size_t)(size_nlist) + AZB_SLOT_ROW_ALIGN(W) * ((size_t)(N) + 1))
 typedef struct azb_tile_plan
     {
     unsigned int tile_size;           /* particles per tile: 32, 64, 128 or 256 */
     unsigned int n_tiles;             /* ceil(N / tile_size) */
     unsigned int uniq_capacity;       /* stride of d_uniq per tile; power of two, <= 4096 */
     unsigned int max_uniq;            /* max over tiles of d_uniq_count (returned by azb_tiles_build) */
+    unsigned int lane_width;          /* W of the slot-row layout: 1 (DPD kernels), or the pair kernel's lanes per particle */
+    unsigned int max_slot_span;       /* max over tiles of the tile's slot-row range, in entries (returned by azb_tiles_build) */
     const unsigned int* d_uniq_count; /* [n_tiles] */
     const unsigned int* d_uniq;       /* [n_tiles * uniq_capacity] */
-    const uint16_t* d_slots;          /* [AZB_SLOTS_SIZE(size_nlist, N)] */
+    const uint16_t* d_slots;          /* [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */
     } azb_tile_plan;
 
 /* mirrors HOOMD pair_args_t */
@@ -264,7 +272,7 @@ AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* st
 
 /* ---- tile plan builder: one call per neighbour-list rebuild (the host class calls it when HOOMD's
  * NeighborList::hasBeenUpdated(timestep) reports a rebuild). Writes d_uniq_count / d_uniq / d_slots and returns the
- * largest per-tile unique count in *h_max_uniq. *h_overflow is set non-zero when some tile has more than uniq_capacity
+ * largest per-tile unique count in *h_max_uniq and the largest per-tile slot-row range in *h_max_slot_span. *h_overflow is set non-zero when some tile has more than uniq_capacity
  * distinct neighbours (1) or the rows are not disjoint and ordered by particle (2): the plan is then unusable (retry
  * with a smaller tile_size or pass tiles = NULL). Synchronises
  * the stream. Rows may reference ghosts (indices in [N, n_max)). */
@@ -277,13 +285,15 @@ typedef struct azb_tile_build_args
     unsigned int N;
     unsigned int tile_size;
     unsigned int uniq_capacity;
+    unsigned int lane_width;         /* 1, 2, 4, 8 or 16 */
     unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
     unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
-    uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N)] */
-    unsigned int* d_status;          /* scratch, 2 x u32 on the device */
+    uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */
+    unsigned int* d_status;          /* scratch, 4 x u32 on the device */
     } azb_tile_build_args;
 
-AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_overflow, void* stream);
+AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,
+                            void* stream);
 
 /* ---- halo packing (SURVEY.md §8 e): d_out[e] = d_src[d_idx[e]] (+ d_shift[e].xyz when d_shift != NULL), Scalar4 rows.
  * Packs the boundary particles a neighbouring domain needs as ghosts into a contiguous send buffer; the periodic image

@@ -20,11 +20,14 @@ def _list_on_device(n, rho, r_list, seed, shuffle=False):
     return hs, nl
 
 
+@pytest.mark.parametrize("lane_width", [1, 2, 4, 8, 16])
 @pytest.mark.parametrize("tile_size", [32, 64, 128, 256])
-def test_tile_plan_matches_numpy(tile_size):
+def test_tile_plan_matches_numpy(tile_size, lane_width):
     n = 5000
     hs, nl = _list_on_device(n, 3.0, 1.4, 11)
-    plan = nl.tile_plan(n, tile_size, 2048)
+    plan = nl.tile_plan(n, tile_size, 2048, lane_width)
+    W, M = lane_width, 4 * lane_width
+    A = max(M, 8)  # AZB_SLOT_ROW_ALIGN
     assert plan is not None and plan.tile_size == tile_size and plan.n_tiles == (n + tile_size - 1) // tile_size
     count = plan.uniq_count.cpu().numpy().view(np.uint32)
     uniq = plan.uniq.cpu().numpy().view(np.uint32).reshape(plan.n_tiles, plan.uniq_capacity)
@@ -38,12 +41,19 @@ def test_tile_plan_matches_numpy(tile_size):
         assert count[t] == len(want)
         assert np.array_equal(uniq[t, : len(want)], want)  # ascending, no duplicates
         for i in rows:
-            sh = (head[i] + 4 * i) & ~3  # AZB_SLOT_HEAD
-            s = slots[sh : sh + nn[i]]
-            assert np.array_equal(want[s], lst[head[i] : head[i] + nn[i]])  # slot -> the listed neighbour, entry for entry
-            assert np.all(slots[sh + nn[i] : sh + ((nn[i] + 3) & ~3)] == 0)  # padding
+            sh = (head[i] + A * i) & ~(A - 1)  # AZB_SLOT_HEAD
+            e = np.arange((nn[i] + M - 1) // M * M)
+            r = e % M
+            stored = slots[sh + (e - r) + 4 * (r % W) + r // W]  # entry e of the row in the lane-transposed layout
+            assert np.array_equal(want[stored[: nn[i]]], lst[head[i] : head[i] + nn[i]])  # slot -> the listed neighbour
+            assert np.all(stored[nn[i] :] == 0)  # padding
         worst = max(worst, len(want))
     assert plan.max_uniq == worst
+    spans = []
+    for t in range(plan.n_tiles):
+        i0, i1 = t * tile_size, min((t + 1) * tile_size, n) - 1
+        spans.append(((head[i1] + A * i1) & ~(A - 1)) + (nn[i1] + M - 1) // M * M - ((head[i0] + A * i0) & ~(A - 1)))
+    assert plan.max_slot_span == max(spans)
 
 
 def test_tile_plan_overflow_falls_back_to_smaller_tiles():
