@@ -88,6 +88,8 @@ class PairArgs(C.Structure):
         ("compute_virial", C.c_uint),
         ("threads_per_particle", C.c_uint),
         ("tiles", C.POINTER(TilePlan)),
+        ("tile_begin", C.c_uint),
+        ("tile_count", C.c_uint),
     ]
 
 

@@ -50,8 +50,8 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     if (a.pair.tiles)
         {
         TilePlanDev plan;
-        unsigned int block = 0;
-        const int bad = make_tile_plan(a.pair, tpp, 1u, plan, block);
+        unsigned int block = 0, grid = 0;
+        const int bad = make_tile_plan(a.pair, tpp, 1u, plan, block, grid);
         if (bad)
             return bad;
         if (a.pair.ntypes > 255)
@@ -60,7 +60,6 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
                             + T2 * sizeof(coeff_t);
         if (smem > AZB_MAX_SMEM)
             return AZB_ERR_BAD_ARGUMENT;
-        const unsigned int grid = a.pair.tiles->n_tiles;
 #define AZB_LAUNCH_T(TPP, FB, SG)                                                            \
     do                                                                                       \
         {                                                                                    \

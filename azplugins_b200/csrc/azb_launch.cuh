@@ -84,7 +84,8 @@ template<auto KERNEL> inline void ensure_smem(size_t bytes)
 
 // Validates a.tiles against the launch and picks the CTA size: blockDim / tpp groups, each walking
 // tile_size / groups particles (both powers of two, so every warp runs the same number of passes).
-inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int slot_lane_width, TilePlanDev& plan, unsigned int& block)
+inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int slot_lane_width, TilePlanDev& plan, unsigned int& block,
+                          unsigned int& grid)
     {
     const azb_tile_plan& t = *a.tiles;
     const unsigned int ts = t.tile_size;
@@ -95,6 +96,10 @@ inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int
     plan.uniq_capacity = t.uniq_capacity;
     plan.smem_uniq = ((t.max_uniq > 0 ? t.max_uniq : 1u) + 7u) & ~7u;
     plan.smem_span = (t.max_slot_span + 15u) & ~15u;
+    plan.tile_begin = a.tile_count ? a.tile_begin : 0u;
+    grid = a.tile_count ? a.tile_count : t.n_tiles;
+    if (plan.tile_begin >= t.n_tiles || grid > t.n_tiles - plan.tile_begin)
+        return AZB_ERR_BAD_ARGUMENT;
     plan.uniq_count = t.d_uniq_count;
     plan.uniq = t.d_uniq;
     plan.slots = t.d_slots;

@@ -41,6 +41,7 @@ struct TilePlanDev
     {
     unsigned int tile_size, uniq_capacity, smem_uniq; // smem_uniq: capacity of the staging arrays (>= max_uniq)
     unsigned int smem_span;                           // capacity of the staged slot rows, entries (>= max_slot_span)
+    unsigned int tile_begin;                          // first tile of this launch (blockIdx.x = 0)
     const unsigned int* uniq_count;
     const unsigned int* uniq;
     const uint16_t* slots;
@@ -65,15 +66,15 @@ template<class S, bool VIRIAL> struct PairAccum
         fy += dy * fdivr;
         fz += dz * fdivr;
         pe += e;
-        if (VIRIAL)
+        if (VIRIAL) // sums f/r dx_a dx_b; the virial's factor 1/2 is applied once, in store()
             {
-            const S h = S(0.5) * fdivr_virial;
-            vxx += h * dx * dx;
-            vxy += h * dx * dy;
-            vxz += h * dx * dz;
-            vyy += h * dy * dy;
-            vyz += h * dy * dz;
-            vzz += h * dz * dz;
+            const S hx = fdivr_virial * dx, hy = fdivr_virial * dy, hz = fdivr_virial * dz;
+            vxx += hx * dx;
+            vxy += hx * dy;
+            vxz += hx * dz;
+            vyy += hy * dy;
+            vyz += hy * dz;
+            vzz += hz * dz;
             }
         }
     template<int TPP> __device__ __forceinline__ void reduce()
@@ -100,12 +101,12 @@ template<class S, bool VIRIAL> struct PairAccum
         st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
         if (VIRIAL)
             {
-            a.virial[0 * a.virial_pitch + idx] = vxx;
-            a.virial[1 * a.virial_pitch + idx] = vxy;
-            a.virial[2 * a.virial_pitch + idx] = vxz;
-            a.virial[3 * a.virial_pitch + idx] = vyy;
-            a.virial[4 * a.virial_pitch + idx] = vyz;
-            a.virial[5 * a.virial_pitch + idx] = vzz;
+            a.virial[0 * a.virial_pitch + idx] = S(0.5) * vxx;
+            a.virial[1 * a.virial_pitch + idx] = S(0.5) * vxy;
+            a.virial[2 * a.virial_pitch + idx] = S(0.5) * vxz;
+            a.virial[3 * a.virial_pitch + idx] = S(0.5) * vyy;
+            a.virial[4 * a.virial_pitch + idx] = S(0.5) * vyz;
+            a.virial[5 * a.virial_pitch + idx] = S(0.5) * vzz;
             }
         }
     };
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a,
             energy_shift = ron > rc;
             }
         s_coeff[t] = Pot::make(params[t], rc, energy_shift);
-        s_rcutsq[t] = rc;
+        s_rcutsq[t] = Pot::active(s_coeff[t]) ? rc : S(-1); // inactive type pair: no distance passes the cutoff test
         s_ronsq[t] = ron;
         }
     __syncthreads();
@@ -266,7 +267,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
     S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
     S* s_ronsq = s_rcutsq + T2;
 
-    const unsigned int tile = blockIdx.x;
+    const unsigned int tile = plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
     for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
             energy_shift = ron > rc;
             }
         s_coeff[t] = Pot::make(params[t], rc, energy_shift);
-        s_rcutsq[t] = rc;
+        s_rcutsq[t] = Pot::active(s_coeff[t]) ? rc : S(-1); // inactive type pair: no distance passes the cutoff test
         s_ronsq[t] = ron;
         }
     __syncthreads();

@@ -21,8 +21,8 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
         if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16) || (a.threads_per_particle && a.threads_per_particle != tpp))
             return AZB_ERR_BAD_ARGUMENT;
         TilePlanDev plan;
-        unsigned int block = 0;
-        const int bad = make_tile_plan(a, tpp, tpp, plan, block);
+        unsigned int block = 0, grid = 0;
+        const int bad = make_tile_plan(a, tpp, tpp, plan, block, grid);
         if (bad)
             return bad;
         const size_t smem = (size_t)plan.smem_uniq * sizeof(typename vec4<S>::type) + T2 * (sizeof(coeff_t) + 2 * sizeof(S));
@@ -35,7 +35,7 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
     do                                                                                                                    \
         {                                                                                                                 \
         ensure_smem<pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG>>(smem);                                          \
-        pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG><<<a.tiles->n_tiles, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
+        pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
         } while (0)
 #define AZB_CALL_T(TPP)                         \
     do                                          \

@@ -49,9 +49,15 @@ struct PerturbedLJ
             }
         return c;
         }
+    // The reference's evaluators return false for a type pair with a vanishing prefactor; the kernels fold that into the
+    // cutoff they test against (r_cut^2 = -1 for such pairs), so eval() itself only tests the distance.
+    template<class S> __device__ __forceinline__ static bool active(const Coeff<S>& c)
+        {
+        return c.lj1 != S(0);
+        }
     template<class S> __device__ __forceinline__ static bool eval(S rsq, S rcutsq, const Coeff<S>& c, S& fdivr, S& e)
         {
-        if (rsq < rcutsq && c.lj1 != S(0))
+        if (rsq < rcutsq)
             {
             const S r2inv = rcp(rsq);
             const S r6inv = r2inv * r2inv * r2inv;
@@ -183,9 +189,15 @@ struct Colloid
             }
         return c;
         }
+    // The reference's evaluators return false for a type pair with a vanishing prefactor; the kernels fold that into the
+    // cutoff they test against (r_cut^2 = -1 for such pairs), so eval() itself only tests the distance.
+    template<class S> __device__ __forceinline__ static bool active(const Coeff<S>& c)
+        {
+        return c.A != S(0);
+        }
     template<class S> __device__ __forceinline__ static bool eval(S rsq, S rcutsq, const Coeff<S>& c, S& fdivr, S& e)
         {
-        if (rsq < rcutsq && c.A != S(0))
+        if (rsq < rcutsq)
             {
             e = branch<true>(c, fdivr, rsq) - c.e_shift;
             return true;
@@ -222,9 +234,15 @@ struct ExpandedYukawa
             }
         return c;
         }
+    // The reference's evaluators return false for a type pair with a vanishing prefactor; the kernels fold that into the
+    // cutoff they test against (r_cut^2 = -1 for such pairs), so eval() itself only tests the distance.
+    template<class S> __device__ __forceinline__ static bool active(const Coeff<S>& c)
+        {
+        return c.epsilon != S(0);
+        }
     template<class S> __device__ __forceinline__ static bool eval(S rsq, S rcutsq, const Coeff<S>& c, S& fdivr, S& e)
         {
-        if (rsq < rcutsq && c.epsilon != S(0))
+        if (rsq < rcutsq)
             {
             const S rinv = rsqrt_(rsq);
             const S r = rsq * rinv;
@@ -259,9 +277,15 @@ struct Hertz
         c.rcutinv = S(1.0) / sqrt_(rcutsq);
         return c;
         }
+    // The reference's evaluators return false for a type pair with a vanishing prefactor; the kernels fold that into the
+    // cutoff they test against (r_cut^2 = -1 for such pairs), so eval() itself only tests the distance.
+    template<class S> __device__ __forceinline__ static bool active(const Coeff<S>& c)
+        {
+        return c.epsilon != S(0);
+        }
     template<class S> __device__ __forceinline__ static bool eval(S rsq, S rcutsq, const Coeff<S>& c, S& fdivr, S& e)
         {
-        if (rsq < rcutsq && c.epsilon != S(0))
+        if (rsq < rcutsq)
             {
             const S rinv = rsqrt_(rsq);
             const S r = rsq * rinv;
@@ -297,6 +321,12 @@ struct DPDConservative
         c.rcutinv = S(1.0) / sqrt_(rcutsq);
         c.rcut = S(1.0) / c.rcutinv;
         return c;
+        }
+    // The reference's evaluators return false for a type pair with a vanishing prefactor; the kernels fold that into the
+    // cutoff they test against (r_cut^2 = -1 for such pairs), so eval() itself only tests the distance.
+    template<class S> __device__ __forceinline__ static bool active(const Coeff<S>& c)
+        {
+        return true;
         }
     template<class S> __device__ __forceinline__ static bool eval(S rsq, S rcutsq, const Coeff<S>& c, S& fdivr, S& e)
         {

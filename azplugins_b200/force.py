@@ -61,6 +61,7 @@ class Force:
         self.use_tiles = True
         self.tile_size = 128
         self._plan = None
+        self._tile_range = None
 
     def _attach(self, state):
         if state.device.type != "cuda":
@@ -131,6 +132,13 @@ class Pair(Force):
             return self.threads_per_particle
         return 2 if nbar <= 200 else 4
 
+    def _current_plan(self):
+        """Tile plan of the current neighbour list for this force's kernel (None: gather from global memory)."""
+        if not (self.use_tiles and self._tiled_kernels) or self._state is None:
+            return None
+        st, nl = self._state, self.nlist
+        return nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nl.mean_neighbors(st.N)))
+
     def _pair_value(self, store, a, b, default):
         key = tuple(sorted((a, b)))
         if dict.__contains__(store, key):
@@ -189,23 +197,38 @@ class Pair(Force):
         a.shift_mode = {"none": _abi.SHIFT_NONE, "shift": _abi.SHIFT_SHIFT, "xplor": _abi.SHIFT_XPLOR}[self.mode]
         a.compute_virial = 1 if self.compute_virial else 0
         a.threads_per_particle = self.threads_per_particle
-        self._plan = None
-        if self.use_tiles and self._tiled_kernels:
-            self._plan = nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nl.mean_neighbors(st.N)))
+        self._plan = self._current_plan()
         a.tiles = self._plan.pointer() if self._plan is not None else None
+        a.tile_begin, a.tile_count = self._tile_range if (self._plan is not None and self._tile_range) else (0, 0)
 
-    def compute(self, timestep=0):
+    def _prepare(self):
         if self._state is None:
             raise RuntimeError("force is not attached to a state")
         self.nlist.compute(self._state)
         if self._dirty:
             self._tables()
+
+    def _build_args(self, timestep, tile_range=None):
+        """The C-ABI argument struct of one launch (kept alive by the caller until the launch is issued)."""
+        self._tile_range = tile_range
         args = _abi.PairArgs()
         self._fill_pair_args(args)
+        return args
+
+    def _set_timestep(self, args, timestep):
+        pass
+
+    def _launch(self, args):
         code = self._lib.azb_pair_forces(self._spec.potential_id, self._state.scalar_bits, C.byref(args),
                                          self._d_params.data_ptr(), self._stream())
         _abi.check(code, f"azb_pair_forces[{self._spec.name}]")
         self.launches += 1
+
+    def compute(self, timestep=0, tile_range=None):
+        """One evaluation (one kernel launch). ``tile_range=(first_tile, n_tiles)`` restricts a tile-staged launch to
+        those tiles and leaves the outputs of all other particles untouched (used to pipeline a step against copies)."""
+        self._prepare()
+        self._launch(self._build_args(timestep, tile_range))
 
 
 class DPDThermoPair(Pair):
@@ -226,22 +249,24 @@ class DPDThermoPair(Pair):
     def _kT_at(self, timestep):
         return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)
 
-    def compute(self, timestep=0):
-        if self._state is None:
-            raise RuntimeError("force is not attached to a state")
+    def _build_args(self, timestep, tile_range=None):
         st = self._state
-        self.nlist.compute(st)
-        if self._dirty:
-            self._tables()
+        self._tile_range = tile_range
         args = _abi.DPDArgs()
         self._fill_pair_args(args.pair)
         args.d_vel = st.vel.data_ptr()
         args.d_tag = st.tag.data_ptr()
         args.seed = st.seed
-        args.timestep = int(timestep)
         args.deltaT = float(self.dt)
+        self._set_timestep(args, timestep)
+        return args
+
+    def _set_timestep(self, args, timestep):
+        args.timestep = int(timestep)
         args.T = self._kT_at(timestep)
-        code = self._lib.azb_dpd_forces(self._spec.potential_id, st.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
+
+    def _launch(self, args):
+        code = self._lib.azb_dpd_forces(self._spec.potential_id, self._state.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
         _abi.check(code, f"azb_dpd_forces[{self._spec.name}]")
         self.launches += 1
 
@@ -260,19 +285,18 @@ class AnisotropicPair(Pair):
         super()._attach(state)
         self._torque = torch.zeros((state.N, 4), dtype=self._force.dtype, device=state.device)
 
-    def compute(self, timestep=0):
-        if self._state is None:
-            raise RuntimeError("force is not attached to a state")
+    def _build_args(self, timestep, tile_range=None):
         st = self._state
-        self.nlist.compute(st)
-        if self._dirty:
-            self._tables()
+        self._tile_range = tile_range
         args = _abi.AnisoArgs()
         self._fill_pair_args(args.pair)
         args.d_orientation = st.orientation.data_ptr()
         args.d_torque = self._torque.data_ptr()
         args.d_shape_params = None
-        code = self._lib.azb_aniso_forces(self._spec.potential_id, st.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
+        return args
+
+    def _launch(self, args):
+        code = self._lib.azb_aniso_forces(self._spec.potential_id, self._state.scalar_bits, C.byref(args), self._d_params.data_ptr(), self._stream())
         _abi.check(code, f"azb_aniso_forces[{self._spec.name}]")
         self.launches += 1
 

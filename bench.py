@@ -22,6 +22,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+ALL_CPUS = os.sched_getaffinity(0)  # the CPU baseline always runs on every core the process was given
 METRIC = "force-compute particle-steps/s"
 UNIT = "particle-steps/s"
 
@@ -44,7 +45,35 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--e2e-chunks", type=int, default=8, help="chunks of the pipelined host step (1 = copy, compute, copy)")
     return ap.parse_args()
+
+
+def bind_to_gpu_numa_node(index):
+    """Run this process (and so first-touch its pinned host buffers) on the CPUs local to GPU `index`: host<->device
+    copies from the far NUMA node lose a third or more of the PCIe bandwidth. Best effort; returns a note for the JSON line."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        path = f"/sys/bus/pci/devices/{dom[-4:].lower()}:{rest.lower()}"
+        cpus = open(path + "/local_cpulist").read().strip()
+        node = open(path + "/numa_node").read().strip()
+        ids = set()
+        for part in cpus.split(","):
+            lo, _, hi = part.partition("-")
+            ids.update(range(int(lo), int(hi or lo) + 1))
+        ids &= os.sched_getaffinity(0)
+        if ids:
+            os.sched_setaffinity(0, ids)
+            return f"process bound to NUMA node {node} (cpus {cpus}) of GPU {bus}"
+        return f"GPU {bus}: no usable local cpus ({cpus})"
+    except Exception as exc:  # noqa: BLE001 - affinity is an optimisation, never a failure
+        return f"not bound ({type(exc).__name__})"
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -199,7 +228,8 @@ def time_reference_cpu(workload, snap, bits, nl_arrays, seconds, steps=None, war
 
     hs, _ = host_arrays_for_oracle(snap, bits, *nl_arrays)
     which = "ref" if O.have_ref() else "port"
-    cores = os.cpu_count() or 1
+    os.sched_setaffinity(0, ALL_CPUS)  # undo the GPU-local binding of the copy path: the reference gets all host cores
+    cores = len(ALL_CPUS)
     T = len(snap.types)
     names = snap.types
 
@@ -283,6 +313,7 @@ def run_b200(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device; the force path has no CPU fallback")
+    numa_note = bind_to_gpu_numa_node(local_rank)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -396,52 +427,81 @@ def run_b200(args):
     if os.path.exists(traffic_path):
         roofline["traffic"] = json.load(open(traffic_path)).get("dram_bytes_per_launch")
 
+    plan = dom._plan
+    tile_note = ("gathered from global memory" if plan is None else
+                 f"staged per tile in shared memory (azb_tile_plan: {plan.tile_size} particles/tile, <= {plan.max_uniq} distinct neighbours, "
+                 f"built in {plan.build_ms:.2f} ms per neighbour-list rebuild, outside the timed region like the list itself)")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.bits == 32 else "f64", "data": "synthetic",
         "config": {"workload": label, "particles_per_gpu": st.N, "mean_neighbors": round(nbar, 2), "compute_virial": virial,
                    "threads_per_particle": args.tpp or "auto", "neighbor_list": "full, HOOMD layout, built on GPU (azb_nlist_*)",
+                   "neighbor_data": tile_note,
                    "l2": "flushed between timed steps (384 MiB fill)" if flush is not None else "not flushed; working set > L2",
                    "parallelism": "1 GPU" if world == 1 else
                    f"{world} GPUs, spatial domains {GRIDS[world]}, ghost halo over NCCL P2P every step ({halo.bytes_per_update()} B sent/rank/step, "
                    f"{st.n_ghost} ghosts on rank 0)"},
         "clocks": clocks, "roofline": roofline, "gpu_launches": int(launches),
-        "nlist_build_s": nlist_build_s,
+        "nlist_build_s": nlist_build_s, "host_affinity": numa_note,
     }
 
+    # ---- e2e: the same metric through the public API with HOST buffers; every step copies this step's positions
+    # (+ velocities / orientations) from pinned host memory and reads the forces (+ torques) back into pinned host memory.
+    # Neighbour list, tile plan, tags and parameter tables stay resident between list rebuilds, as they do in HOOMD.
+    # 1 GPU, one force: the step is pipelined (azplugins_b200/hostio.py: chunked H2D, tile-range launches as their inputs
+    # arrive, D2H of finished chunks). Several forces or several GPUs (ghost exchange needs all local positions first):
+    # copy, exchange, compute, copy.
+    from azplugins_b200.hostio import HostStep
+
+    hs = HostStep(dom, chunks=args.e2e_chunks)
+    extra_out = [f._force for f in forces[1:]]
+    pinned_in = hs.pinned_inputs()
+    pinned_out = hs.pinned_outputs()
+    pinned_extra = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in extra_out]
+    h2d = hs.h2d_bytes
+    d2h = hs.d2h_bytes + sum(t.numel() * t.element_size() for t in extra_out)
+    pipelined = world == 1 and len(forces) == 1 and args.e2e_chunks > 1
+
+    def e2e_step(t):
+        if pipelined:
+            hs.run(t, pinned_in, pinned_out)
+            return
+        for dst, src in zip(hs.inputs, pinned_in):
+            dst.copy_(src, non_blocking=True)
+        step(t)
+        for dst, src in zip(pinned_out + pinned_extra, hs.outputs + extra_out):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the host consumes the forces every step
+
+    for t in range(3):
+        e2e_step(t)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for k in range(K):
+        e2e_step(args.warmup + k)
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    if world > 1:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
+    if pipelined:
+        # the pipelined step must deliver the same forces as the plain launch
+        step(args.warmup + K - 1)
+        torch.cuda.synchronize()
+        same = all(torch.equal(o.cpu(), p) for o, p in zip(hs.outputs, pinned_out))
+        if not same:
+            raise RuntimeError("pipelined host step and plain launch disagree")
+    line["e2e"] = {"value": n_total * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "ms_per_step": e2e_ms / K,
+                   "note": (f"pipelined in {args.e2e_chunks} chunks: pinned host pos(+vel/orientation) -> device, tile-range launches as inputs arrive, "
+                            "force(+torque) -> pinned host" if pipelined else
+                            "pinned host pos(+vel/orientation) -> device, (ghost exchange,) kernel(s), force(+torque) -> pinned host, every step")}
+
     if rank == 0 and world == 1:
-        # ---- e2e: the same metric through the public API with HOST buffers; per-step H2D of positions + velocities
-        # from pinned memory and D2H of the force array (neighbour list / tags / params stay resident between rebuilds,
-        # as they do in HOOMD) ---------------------------------------------------------------------------------------
-        dom_inputs = [st.pos, st.vel] if dom._kind == _abi.KIND_DPD else ([st.pos, st.orientation] if dom._kind == _abi.KIND_ANISO else [st.pos])
-        pinned_in = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t.cpu()) for t in dom_inputs]
-        outs = [f._force for f in forces] + ([dom._torque] if dom._torque is not None else [])
-        pinned_out = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in outs]
-        h2d = sum(t.numel() * t.element_size() for t in pinned_in)
-        d2h = sum(t.numel() * t.element_size() for t in pinned_out)
-
-        def e2e_step(t):
-            for dst, src in zip(dom_inputs, pinned_in):
-                dst.copy_(src, non_blocking=True)
-            step(t)
-            for dst, src in zip(pinned_out, outs):
-                dst.copy_(src, non_blocking=True)
-            torch.cuda.current_stream().synchronize()  # the host consumes the forces every step
-
-        for t in range(3):
-            e2e_step(t)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        e0.record()
-        for k in range(K):
-            e2e_step(k)
-        e1.record()
-        torch.cuda.synchronize()
-        e2e_ms = e0.elapsed_time(e1)
-        line["e2e"] = {"value": st.N * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                       "ms_per_step": e2e_ms / K, "note": "pinned host pos(+vel/orientation) -> device, kernel, force(+torque) -> pinned host, every step"}
-
         if not args.no_extras and flush is not None:
             # back-to-back (no L2 flush) figure for context
             torch.cuda.synchronize()
@@ -463,8 +523,6 @@ def run_b200(args):
                                                   f"{sec * 1e3:.1f} ms each, OpenMP over particles, Scalar={'float' if args.bits == 32 else 'double'}"}
             except Exception as exc:  # the baseline is a report, never a reason to lose the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
-    elif rank == 0:
-        line["e2e"] = None
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

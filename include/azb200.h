@@ -153,6 +153,8 @@ typedef struct azb_pair_args
     unsigned int compute_virial;       /* 0/1 */
     unsigned int threads_per_particle; /* 0 = engine picks; else power of two <= 32 */
     const azb_tile_plan* tiles;        /* host pointer; NULL = gather neighbour data straight from global memory */
+    unsigned int tile_begin;           /* with tiles: evaluate only tiles [tile_begin, tile_begin + tile_count) and leave the */
+    unsigned int tile_count;           /* outputs of all other particles untouched; tile_count == 0 = every tile */
     } azb_pair_args;
 
 /* mirrors HOOMD dpd_pair_args_t: pair args + velocities, tags, RNG key material, dt and kT */

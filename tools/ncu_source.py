@@ -6,7 +6,8 @@ rep = sys.argv[1]
 txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 lines = txt.splitlines()
 start = next(i for i, l in enumerate(lines) if l.startswith('"Address"'))
-rows = list(csv.reader(io.StringIO("\n".join(lines[start:]))))
+end = next((i for i in range(start + 1, len(lines)) if lines[i].startswith('"Kernel Name"')), len(lines))  # first launch only
+rows = list(csv.reader(io.StringIO("\n".join(lines[start:end]))))
 hdr = rows[0]
 ix = {h: i for i, h in enumerate(hdr)}
 tot_s = sum(int(r[ix["# Samples"]] or 0) for r in rows[1:] if len(r) == len(hdr))
