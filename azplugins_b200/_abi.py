@@ -59,6 +59,7 @@ class TileBuildArgs(C.Structure):
         ("tile_size", C.c_uint),
         ("uniq_capacity", C.c_uint),
         ("lane_width", C.c_uint),
+        ("group_width", C.c_uint),
         ("d_uniq_count", C.c_void_p),
         ("d_uniq", C.c_void_p),
         ("d_slots", C.c_void_p),
@@ -90,6 +91,7 @@ class PairArgs(C.Structure):
         ("tiles", C.POINTER(TilePlan)),
         ("tile_begin", C.c_uint),
         ("tile_count", C.c_uint),
+        ("d_tile_order", C.c_void_p),
     ]
 
 

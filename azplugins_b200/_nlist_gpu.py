@@ -83,7 +83,7 @@ class TilePlanHandle:
         return C.pointer(self.c)
 
 
-def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1):
+def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0):
     """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles)."""
     dev = nl.n_neigh.device
     if dev.type != "cuda":
@@ -99,6 +99,7 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1):
     a = _abi.TileBuildArgs()
     a.d_n_neigh, a.d_nlist, a.d_head_list = nl.n_neigh.data_ptr(), nl.nlist.data_ptr(), nl.head_list.data_ptr()
     a.size_nlist, a.N, a.tile_size, a.uniq_capacity, a.lane_width = nl.size_nlist, N, tile_size, uniq_capacity, lane_width
+    a.group_width = group_width
     a.d_uniq_count, a.d_uniq, a.d_slots, a.d_status = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr(), status.data_ptr()
     max_uniq, max_span, overflow = C.c_uint(0), C.c_uint(0), C.c_uint(0)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)

@@ -12,6 +12,54 @@ template<class S, int SHIFT, bool VIRIAL> static int launch_aniso_variant(const 
     d.pair = make_pair_args<S>(a.pair);
     d.orientation = (const typename vec4<S>::type*)a.d_orientation;
     d.torque = (typename vec4<S>::type*)a.d_torque;
+    const size_t T2t = (size_t)a.pair.ntypes * a.pair.ntypes;
+    if (a.pair.tiles)
+        {
+        const unsigned int tpp = a.pair.tiles->lane_width; // the slot rows are laid out for one group width
+        if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16) || (a.pair.threads_per_particle && a.pair.threads_per_particle != tpp))
+            return AZB_ERR_BAD_ARGUMENT;
+        TilePlanDev plan;
+        unsigned int block = 0, grid = 0;
+        const int bad = make_tile_plan(a.pair, tpp, tpp, plan, block, grid);
+        if (bad)
+            return bad;
+        const size_t smem = (size_t)plan.smem_uniq * 2 * sizeof(typename vec4<S>::type) + T2t * (sizeof(coeff_t) + sizeof(S));
+        if (smem > AZB_MAX_SMEM)
+            return AZB_ERR_BAD_ARGUMENT;
+        S wrap_sq;
+        const bool lazy = lazy_wrap(d.pair.box, wrap_sq);
+#define AZB_CALL_T(TPP)                                                                                                        \
+    do                                                                                                                         \
+        {                                                                                                                      \
+        if (lazy)                                                                                                              \
+            {                                                                                                                  \
+            ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, true>>(smem);                                                 \
+            aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, true><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq);  \
+            }                                                                                                                  \
+        else                                                                                                                   \
+            {                                                                                                                  \
+            ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, false>>(smem);                                                \
+            aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, false><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
+            }                                                                                                                  \
+        } while (0)
+        switch (tpp)
+            {
+        case 2:
+            AZB_CALL_T(2);
+            break;
+        case 4:
+            AZB_CALL_T(4);
+            break;
+        case 8:
+            AZB_CALL_T(8);
+            break;
+        default:
+            AZB_CALL_T(16);
+            break;
+            }
+#undef AZB_CALL_T
+        return (int)cudaGetLastError();
+        }
     const unsigned int tpp = pick_tpp(a.pair);
     if (!valid_tpp(tpp))
         return AZB_ERR_BAD_ARGUMENT;

@@ -60,6 +60,104 @@ template<class S, class Q> __device__ __forceinline__ void patch_director(const 
     nz = S(2) * (vx * vz - s * vy);
     }
 
+// per-lane accumulators of one particle: force, energy, torque, virial
+template<class S, bool VIRIAL> struct AnisoAccum
+    {
+    S fx = S(0), fy = S(0), fz = S(0), pe = S(0), tx = S(0), ty = S(0), tz = S(0);
+    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    template<int TPP> __device__ __forceinline__ void reduce()
+        {
+        if (TPP > 1)
+            {
+            fx = group_sum<TPP>(fx);
+            fy = group_sum<TPP>(fy);
+            fz = group_sum<TPP>(fz);
+            pe = group_sum<TPP>(pe);
+            tx = group_sum<TPP>(tx);
+            ty = group_sum<TPP>(ty);
+            tz = group_sum<TPP>(tz);
+            if (VIRIAL)
+                {
+                vxx = group_sum<TPP>(vxx);
+                vxy = group_sum<TPP>(vxy);
+                vxz = group_sum<TPP>(vxz);
+                vyy = group_sum<TPP>(vyy);
+                vyz = group_sum<TPP>(vyz);
+                vzz = group_sum<TPP>(vzz);
+                }
+            }
+        }
+    __device__ __forceinline__ void store(const AnisoArgsDev<S>& d, unsigned int idx) const
+        {
+        const PairArgsDev<S>& a = d.pair;
+        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
+        st4(d.torque + idx, tx, ty, tz, S(0));
+        if (VIRIAL)
+            {
+            a.virial[0 * a.virial_pitch + idx] = vxx;
+            a.virial[1 * a.virial_pitch + idx] = vxy;
+            a.virial[2 * a.virial_pitch + idx] = vxz;
+            a.virial[3 * a.virial_pitch + idx] = vyy;
+            a.virial[4 * a.virial_pitch + idx] = vyz;
+            a.virial[5 * a.virial_pitch + idx] = vzz;
+            }
+        }
+    };
+
+// One in-range pair (AnisoPairEvaluatorTwoPatchMorse.h:127-216): separation d = r_i - r_j, patch directors n_i, n_j.
+template<class S, bool VIRIAL>
+__device__ __forceinline__ void tpm_pair(S dx, S dy, S dz, S rsq, S nix, S niy, S niz, S njx, S njy, S njz, const TwoPatchMorse::Coeff<S>& c,
+                                         AnisoAccum<S, VIRIAL>& acc)
+    {
+    const S rinv = rsqrt_(rsq);
+    const S r = rsq * rinv;
+    const S ux = dx * rinv, uy = dy * rinv, uz = dz * rinv;
+
+    S UMorse = -c.M_d, dUMorse_dr = S(0);
+    if (r > c.r_eq || c.repulsion)
+        {
+        const S ex = exp_(-(r - c.r_eq) * c.M_rinv);
+        const S om = S(1.0) - ex;
+        UMorse = c.M_d * (om * om - S(1.0));
+        dUMorse_dr = S(2.0) * c.M_d * c.M_rinv * ex * om;
+        }
+    const S gi = ux * nix + uy * niy + uz * niz;
+    const S gi_exp = exp_(-c.omega * (gi * gi - c.alpha));
+    const S Oi = rcp(S(1.0) + gi_exp);
+    const S gj = ux * njx + uy * njy + uz * njz;
+    const S gj_exp = exp_(-c.omega * (gj * gj - c.alpha));
+    const S Oj = rcp(S(1.0) + gj_exp);
+
+    const S e = (UMorse - c.U_shift) * Oi * Oj;
+    const S dU_dr = dUMorse_dr * Oi * Oj;
+    const S dU_dgi = S(2.0) * c.omega * gi * gi_exp * Oi * Oi * UMorse * Oj;
+    const S dU_dgj = S(2.0) * c.omega * gj * gj_exp * Oj * Oj * UMorse * Oi;
+
+    // n_perp = -u x (u x n) = n - (u.n) u   (|u| = 1)
+    const S pix = nix - gi * ux, piy = niy - gi * uy, piz = niz - gi * uz;
+    const S pjx = njx - gj * ux, pjy = njy - gj * uy, pjz = njz - gj * uz;
+    const S Fx = -dU_dr * ux - rinv * (dU_dgi * pix + dU_dgj * pjx);
+    const S Fy = -dU_dr * uy - rinv * (dU_dgi * piy + dU_dgj * pjy);
+    const S Fz = -dU_dr * uz - rinv * (dU_dgi * piz + dU_dgj * pjz);
+    // t_i = dU_dgi (u x n_i)
+    acc.tx += dU_dgi * (uy * niz - uz * niy);
+    acc.ty += dU_dgi * (uz * nix - ux * niz);
+    acc.tz += dU_dgi * (ux * niy - uy * nix);
+    acc.fx += Fx;
+    acc.fy += Fy;
+    acc.fz += Fz;
+    acc.pe += e;
+    if (VIRIAL)
+        {
+        acc.vxx += S(0.5) * dx * Fx;
+        acc.vxy += S(0.5) * dy * Fx;
+        acc.vxz += S(0.5) * dz * Fx;
+        acc.vyy += S(0.5) * dy * Fy;
+        acc.vyz += S(0.5) * dz * Fy;
+        acc.vzz += S(0.5) * dz * Fz;
+        }
+    }
+
 template<class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX>
 __global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> d, const TwoPatchMorse::Params<S>* __restrict__ params)
     {
@@ -82,8 +180,7 @@ __global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> 
     const unsigned int lane = threadIdx.x % TPP;
     const bool active = idx < a.N;
 
-    S fx = S(0), fy = S(0), fz = S(0), pe = S(0), tx = S(0), ty = S(0), tz = S(0);
-    S vxx = S(0), vxy = S(0), vxz = S(0), vyy = S(0), vyz = S(0), vzz = S(0);
+    AnisoAccum<S, VIRIAL> acc;
     if (active)
         {
         const unsigned int nn = __ldg(a.n_neigh + idx);
@@ -105,91 +202,114 @@ __global__ void __launch_bounds__(256) aniso_force_kernel(const AnisoArgsDev<S> 
             if (!(rsq > s_rcutsq[tp])) // the evaluator rejects only rsq > rcutsq (strict), :135
                 {
                 const auto qj = ld4(d.orientation + j);
-                const coeff_t c = s_coeff[tp];
                 S njx, njy, njz;
                 patch_director<S>(qj, njx, njy, njz);
-                const S rinv = rsqrt_(rsq);
-                const S r = rsq * rinv;
-                const S ux = dx * rinv, uy = dy * rinv, uz = dz * rinv;
-
-                S UMorse = -c.M_d, dUMorse_dr = S(0);
-                if (r > c.r_eq || c.repulsion)
-                    {
-                    const S ex = exp_(-(r - c.r_eq) * c.M_rinv);
-                    const S om = S(1.0) - ex;
-                    UMorse = c.M_d * (om * om - S(1.0));
-                    dUMorse_dr = S(2.0) * c.M_d * c.M_rinv * ex * om;
-                    }
-                const S gi = ux * nix + uy * niy + uz * niz;
-                const S gi_exp = exp_(-c.omega * (gi * gi - c.alpha));
-                const S Oi = rcp(S(1.0) + gi_exp);
-                const S gj = ux * njx + uy * njy + uz * njz;
-                const S gj_exp = exp_(-c.omega * (gj * gj - c.alpha));
-                const S Oj = rcp(S(1.0) + gj_exp);
-
-                const S e = (UMorse - c.U_shift) * Oi * Oj;
-                const S dU_dr = dUMorse_dr * Oi * Oj;
-                const S dU_dgi = S(2.0) * c.omega * gi * gi_exp * Oi * Oi * UMorse * Oj;
-                const S dU_dgj = S(2.0) * c.omega * gj * gj_exp * Oj * Oj * UMorse * Oi;
-
-                // n_perp = -u x (u x n) = n - (u.n) u   (|u| = 1)
-                const S pix = nix - gi * ux, piy = niy - gi * uy, piz = niz - gi * uz;
-                const S pjx = njx - gj * ux, pjy = njy - gj * uy, pjz = njz - gj * uz;
-                const S Fx = -dU_dr * ux - rinv * (dU_dgi * pix + dU_dgj * pjx);
-                const S Fy = -dU_dr * uy - rinv * (dU_dgi * piy + dU_dgj * pjy);
-                const S Fz = -dU_dr * uz - rinv * (dU_dgi * piz + dU_dgj * pjz);
-                // t_i = dU_dgi (u x n_i)
-                tx += dU_dgi * (uy * niz - uz * niy);
-                ty += dU_dgi * (uz * nix - ux * niz);
-                tz += dU_dgi * (ux * niy - uy * nix);
-                fx += Fx;
-                fy += Fy;
-                fz += Fz;
-                pe += e;
-                if (VIRIAL)
-                    {
-                    vxx += S(0.5) * dx * Fx;
-                    vxy += S(0.5) * dy * Fx;
-                    vxz += S(0.5) * dz * Fx;
-                    vyy += S(0.5) * dy * Fy;
-                    vyz += S(0.5) * dz * Fy;
-                    vzz += S(0.5) * dz * Fz;
-                    }
+                tpm_pair<S, VIRIAL>(dx, dy, dz, rsq, nix, niy, niz, njx, njy, njz, s_coeff[tp], acc);
                 }
             }
         }
-    if (TPP > 1)
-        {
-        fx = group_sum<TPP>(fx);
-        fy = group_sum<TPP>(fy);
-        fz = group_sum<TPP>(fz);
-        pe = group_sum<TPP>(pe);
-        tx = group_sum<TPP>(tx);
-        ty = group_sum<TPP>(ty);
-        tz = group_sum<TPP>(tz);
-        if (VIRIAL)
-            {
-            vxx = group_sum<TPP>(vxx);
-            vxy = group_sum<TPP>(vxy);
-            vxz = group_sum<TPP>(vxz);
-            vyy = group_sum<TPP>(vyy);
-            vyz = group_sum<TPP>(vyz);
-            vzz = group_sum<TPP>(vzz);
-            }
-        }
+    acc.template reduce<TPP>();
     if (active && lane == 0)
+        acc.store(d, idx);
+    }
+
+// Tile-staged flavour: one CTA per tile stages, per distinct neighbour, the position and the patch director
+// n_j = rotate(q_j, e_x) (computed once per tile instead of once per pair); rows are walked through the lane-transposed
+// 16-bit slots like the isotropic tile kernel.
+template<class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX>
+__global__ void __launch_bounds__(256)
+    aniso_tile_kernel(const AnisoArgsDev<S> d, const TilePlanDev plan, const TwoPatchMorse::Params<S>* __restrict__ params, const S wrap_sq)
+    {
+    typedef TwoPatchMorse::Coeff<S> coeff_t;
+    typedef typename vec4<S>::type V4;
+    const PairArgsDev<S>& a = d.pair;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    V4* s_pos = reinterpret_cast<V4*>(smem_raw);
+    V4* s_dir = s_pos + plan.smem_uniq;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_dir + plan.smem_uniq);
+    S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
+
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
+    const unsigned int U = __ldg(plan.uniq_count + tile);
+    const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
         {
-        st4(a.force + idx, fx, fy, fz, S(0.5) * pe);
-        st4(d.torque + idx, tx, ty, tz, S(0));
-        if (VIRIAL)
+        const unsigned int g = __ldg(uq + s);
+        s_pos[s] = ld4(a.pos + g);
+        const V4 q = ld4(d.orientation + g);
+        V4 n = q;
+        patch_director<S>(q, n.x, n.y, n.z);
+        s_dir[s] = n;
+        }
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        {
+        const S rc = a.rcutsq[t];
+        s_coeff[t] = TwoPatchMorse::make(params[t], rc, SHIFT == 1);
+        s_rcutsq[t] = rc;
+        }
+    __syncthreads();
+    const unsigned int pos_base = smem_addr(s_pos), dir_base = smem_addr(s_dir);
+
+    constexpr unsigned int M = 4 * TPP;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    for (unsigned int p = gid; p < plan.tile_size; p += groups)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        const bool active = idx < a.N;
+        AnisoAccum<S, VIRIAL> acc;
+        if (active)
             {
-            a.virial[0 * a.virial_pitch + idx] = vxx;
-            a.virial[1 * a.virial_pitch + idx] = vxy;
-            a.virial[2 * a.virial_pitch + idx] = vxz;
-            a.virial[3 * a.virial_pitch + idx] = vyy;
-            a.virial[4 * a.virial_pitch + idx] = vyz;
-            a.virial[5 * a.virial_pitch + idx] = vzz;
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
+            const V4 pi = ld4(a.pos + idx);
+            const V4 qi = ld4(d.orientation + idx);
+            S nix, niy, niz;
+            patch_director<S>(qi, nix, niy, niz);
+            const unsigned int trow = type_of(pi.w) * a.ntypes;
+
+            auto visit = [&](const unsigned int slot, const bool valid)
+            {
+                const V4 pj = lds4(pos_base, slot, S());
+                S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                const S rsq = separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
+                const unsigned int tp = trow + type_of(pj.w);
+                if (valid && !(rsq > s_rcutsq[tp]))
+                    {
+                    const V4 nj = lds4(dir_base, slot, S());
+                    tpm_pair<S, VIRIAL>(dx, dy, dz, rsq, nix, niy, niz, nj.x, nj.y, nj.z, s_coeff[tp], acc);
+                    }
+            };
+
+            const unsigned int full = nn / M;
+            const unsigned int nblk = (nn + M - 1u) / M;
+            uint2 next = make_uint2(0u, 0u);
+            if (nblk)
+                next = __ldg(row);
+            for (unsigned int b = 0; b < full; ++b)
+                {
+                const uint2 s4 = next;
+                if (b + 1 < nblk)
+                    next = __ldg(row + (b + 1) * TPP);
+                visit(s4.x & 0xffffu, true);
+                visit(s4.x >> 16, true);
+                visit(s4.y & 0xffffu, true);
+                visit(s4.y >> 16, true);
+                }
+            if (full < nblk)
+                {
+                const unsigned int e0 = full * M + lane;
+                visit(next.x & 0xffffu, e0 < nn);
+                visit(next.x >> 16, e0 + TPP < nn);
+                visit(next.y & 0xffffu, e0 + 2 * TPP < nn);
+                visit(next.y >> 16, e0 + 3 * TPP < nn);
+                }
             }
+        acc.template reduce<TPP>();
+        if (active && lane == 0)
+            acc.store(d, idx);
         }
     }
     } // namespace azb

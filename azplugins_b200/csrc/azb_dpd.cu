@@ -29,10 +29,9 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     if (!valid_tpp(tpp))
         return AZB_ERR_BAD_ARGUMENT;
     const size_t T2 = (size_t)a.pair.ntypes * a.pair.ntypes;
-    const bool fastbox = d.pair.box.flags == 7u;
+    S wrap_sq;
+    const bool fastbox = lazy_wrap(d.pair.box, wrap_sq);
     const bool single = a.pair.ntypes == 1;
-    const S lmin = fmin(d.pair.box.Lx, fmin(d.pair.box.Ly, d.pair.box.Lz));
-    const S wrap_sq = S(0.25) * lmin * lmin;
 
 #define AZB_BY_FLAVOUR(LAUNCH, TPP)        \
     do                                     \

@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(256)
     V4* s_queue = reinterpret_cast<V4*>(s_coeff + T2);
     unsigned int* s_tag = reinterpret_cast<unsigned int*>(s_queue + groups * (QCAP + 1u));
 
-    const unsigned int tile = plan.tile_begin + blockIdx.x;
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
     for (unsigned int s0 = threadIdx.x; s0 < U; s0 += 4 * blockDim.x)

@@ -97,6 +97,7 @@ inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int
     plan.smem_uniq = ((t.max_uniq > 0 ? t.max_uniq : 1u) + 7u) & ~7u;
     plan.smem_span = (t.max_slot_span + 15u) & ~15u;
     plan.tile_begin = a.tile_count ? a.tile_begin : 0u;
+    plan.tile_order = a.d_tile_order;
     grid = a.tile_count ? a.tile_count : t.n_tiles;
     if (plan.tile_begin >= t.n_tiles || grid > t.n_tiles - plan.tile_begin)
         return AZB_ERR_BAD_ARGUMENT;
@@ -109,6 +110,21 @@ inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int
     if (block < 32 || (block & (block - 1u)))
         return AZB_ERR_BAD_ARGUMENT;
     return 0;
+    }
+
+// Lazy minimum image (azb_pair_kernel.cuh, separation()): usable in every orthorhombic box; the threshold is half the
+// shortest periodic edge, squared (a value no r^2 exceeds when no direction is periodic).
+template<class S> inline bool lazy_wrap(const Box<S>& box, S& wrap_sq)
+    {
+    S lmin = S(1e18);
+    if (box.flags & 1u)
+        lmin = box.Lx < lmin ? box.Lx : lmin;
+    if (box.flags & 2u)
+        lmin = box.Ly < lmin ? box.Ly : lmin;
+    if (box.flags & 4u)
+        lmin = box.Lz < lmin ? box.Lz : lmin;
+    wrap_sq = S(0.25) * lmin * lmin;
+    return (box.flags & 8u) == 0u;
     }
 
 inline int check_pair_args(const azb_pair_args* a)

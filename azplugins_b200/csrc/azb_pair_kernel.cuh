@@ -42,6 +42,7 @@ struct TilePlanDev
     unsigned int tile_size, uniq_capacity, smem_uniq; // smem_uniq: capacity of the staging arrays (>= max_uniq)
     unsigned int smem_span;                           // capacity of the staged slot rows, entries (>= max_slot_span)
     unsigned int tile_begin;                          // first tile of this launch (blockIdx.x = 0)
+    const unsigned int* tile_order;                   // optional permutation: tile = tile_order[tile_begin + blockIdx.x]
     const unsigned int* uniq_count;
     const unsigned int* uniq;
     const uint16_t* slots;
@@ -214,31 +215,32 @@ __global__ void __launch_bounds__(256) pair_force_kernel(const PairArgsDev<S> a,
     if (active && lane == 0)
         acc.store(a, idx);
     }
-// Separation of one list entry with the lazy minimum image: in the fully periodic orthorhombic box a pair whose raw
-// separation is inside half the shortest box edge (wrap_sq = (L_min / 2)^2) needs no wrap. Returns r^2. The wrap
-// itself is a real (not inlined) call so that the compiler cannot turn the rare path into predicated straight-line code
-// that every list entry would pay for.
+// Separation of one list entry with the lazy minimum image. In an orthorhombic box (any mix of periodic and
+// non-periodic directions — the latter is what a domain-decomposed rank sees) a pair whose raw separation is inside half
+// the shortest PERIODIC box edge (wrap_sq = (L_min / 2)^2; +inf when nothing is periodic) needs no wrap. Returns r^2. The
+// wrap itself is a real (not inlined) call so that the compiler cannot turn the rare path into predicated straight-line
+// code that every list entry would pay for. LAZY = false (triclinic box): BoxDim::minImage for every entry.
 template<class S> struct Sep
     {
     S dx, dy, dz, rsq;
     };
-template<class S> __device__ __noinline__ Sep<S> wrapped_separation(S Lx, S Ly, S Lz, S Lxinv, S Lyinv, S Lzinv, S dx, S dy, S dz)
+template<class S> __device__ __noinline__ Sep<S> wrapped_separation(S Lx, S Ly, S Lz, S Lxinv, S Lyinv, S Lzinv, unsigned int flags, S dx, S dy, S dz)
     {
     Sep<S> r;
-    r.dx = dx - Lx * rint_small(dx * Lxinv);
-    r.dy = dy - Ly * rint_small(dy * Lyinv);
-    r.dz = dz - Lz * rint_small(dz * Lzinv);
+    r.dx = (flags & 1u) ? dx - Lx * rint_small(dx * Lxinv) : dx;
+    r.dy = (flags & 2u) ? dy - Ly * rint_small(dy * Lyinv) : dy;
+    r.dz = (flags & 4u) ? dz - Lz * rint_small(dz * Lzinv) : dz;
     r.rsq = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz;
     return r;
     }
-template<bool FASTBOX, class S> __device__ __forceinline__ S separation(const Box<S>& box, S wrap_sq, S& dx, S& dy, S& dz)
+template<bool LAZY, class S> __device__ __forceinline__ S separation(const Box<S>& box, S wrap_sq, S& dx, S& dy, S& dz)
     {
-    if (FASTBOX)
+    if (LAZY)
         {
         S rsq = dx * dx + dy * dy + dz * dz;
-        if (rsq > wrap_sq) // only then can a component exceed half a box edge
+        if (rsq > wrap_sq) // only then can a component exceed half a periodic box edge
             {
-            const Sep<S> w = wrapped_separation(box.Lx, box.Ly, box.Lz, box.Lxinv, box.Lyinv, box.Lzinv, dx, dy, dz);
+            const Sep<S> w = wrapped_separation(box.Lx, box.Ly, box.Lz, box.Lxinv, box.Lyinv, box.Lzinv, box.flags, dx, dy, dz);
             dx = w.dx;
             dy = w.dy;
             dz = w.dz;
@@ -267,7 +269,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
     S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
     S* s_ronsq = s_rcutsq + T2;
 
-    const unsigned int tile = plan.tile_begin + blockIdx.x;
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
     for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)

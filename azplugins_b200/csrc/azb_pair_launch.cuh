@@ -5,6 +5,17 @@
 
 namespace azb
     {
+// Hook for potential-specific tile kernels (e.g. the packed-FP32 PerturbedLJ kernel, azb_plj_packed.cuh): a translation unit
+// specialises this before it instantiates launch_pair. try_launch returns true when it has issued the launch.
+template<class Pot, class S, int SHIFT, bool VIRIAL> struct SpecialTileKernel
+    {
+    static bool try_launch(const PairArgsDev<S>&, const TilePlanDev&, const void*, S, bool, bool, unsigned int, unsigned int, unsigned int,
+                           cudaStream_t)
+        {
+        return false;
+        }
+    };
+
 template<class Pot, class S, int SHIFT, bool VIRIAL>
 static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cudaStream_t stream)
     {
@@ -12,7 +23,7 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
     typedef typename Pot::template Coeff<S> coeff_t;
     const PairArgsDev<S> d = make_pair_args<S>(a);
     const size_t T2 = (size_t)a.ntypes * a.ntypes;
-    const bool fastbox = d.box.flags == 7u;
+    const bool fastbox = d.box.flags == 7u; // direct kernels: straight-line minimum image in the fully periodic box
     if (a.tiles)
         {
         // tile-staged flavour: neighbour positions come from shared memory, so narrow groups lose nothing on
@@ -28,9 +39,11 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
         const size_t smem = (size_t)plan.smem_uniq * sizeof(typename vec4<S>::type) + T2 * (sizeof(coeff_t) + 2 * sizeof(S));
         if (smem > AZB_MAX_SMEM)
             return AZB_ERR_BAD_ARGUMENT;
-        const S lmin = fmin(d.box.Lx, fmin(d.box.Ly, d.box.Lz));
-        const S wrap_sq = S(0.25) * lmin * lmin;
+        S wrap_sq;
+        const bool lazy = lazy_wrap(d.box, wrap_sq);
         const bool single = a.ntypes == 1;
+        if (SpecialTileKernel<Pot, S, SHIFT, VIRIAL>::try_launch(d, plan, d_params, wrap_sq, lazy, single, tpp, grid, block, stream))
+            return (int)cudaGetLastError();
 #define AZB_LAUNCH_T(TPP, FB, SG)                                                                                         \
     do                                                                                                                    \
         {                                                                                                                 \
@@ -40,9 +53,9 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
 #define AZB_CALL_T(TPP)                         \
     do                                          \
         {                                       \
-        if (fastbox && single)                  \
+        if (lazy && single)                     \
             AZB_LAUNCH_T(TPP, true, true);      \
-        else if (fastbox)                       \
+        else if (lazy)                          \
             AZB_LAUNCH_T(TPP, true, false);     \
         else                                    \
             AZB_LAUNCH_T(TPP, false, false);    \

@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
                                                           const unsigned int ucap,
                                                           const unsigned int hcap_log2,
                                                           const unsigned int W,
+                                                          const unsigned int G,
                                                           unsigned int* __restrict__ uniq_count,
                                                           unsigned int* __restrict__ uniq,
                                                           uint16_t* __restrict__ slots,
@@ -144,7 +145,14 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         }
     __syncthreads();
 
-    // 4. list entry -> slot, stored in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD)
+    // 4. list entry -> slot, stored in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD).
+    // The entries of a row are emitted in BANK-ROTATED order: bucket the row's slots by shared-memory bank group
+    // (slot mod 8: the 16-byte Scalar4 of slot s lives in bank group s mod 8) and deal the buckets round-robin, starting
+    // at bucket (particle * G) mod 8 for a kernel that walks rows with groups of G lanes. Emitted position e then holds
+    // bank group (start + e) mod 8 while no bucket has run dry, so the 8 lanes of a quarter-warp — 8/G particles x G
+    // lanes, lane (q, l) reading position t*G + l at step t — touch 8 different bank groups: the neighbour reads of the
+    // force kernels become conflict-free except in the tail of a row. Deterministic (ranks come from ballots, not
+    // atomics), and only the order inside a row changes: the set of pairs is the list's.
     const unsigned int M = 4u * W;
     for (unsigned int i = first + warp; i < last; i += nwarps)
         {
@@ -152,9 +160,15 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         const size_t head = head_list[i];
         const size_t shead = AZB_SLOT_HEAD(head, i, W);
         const unsigned int nnp = (nn + M - 1u) / M * M;
-        for (unsigned int e = lane; e < nnp; e += 32)
+        // pass 1: bucket sizes
+        unsigned int cnt[8];
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+            cnt[g] = 0;
+        for (unsigned int e0 = 0; e0 < nn; e0 += 32)
             {
-            uint16_t v = 0;
+            const unsigned int e = e0 + lane;
+            unsigned int v = 0xffffffffu;
             if (e < nn)
                 {
                 const unsigned int j = nlist[head + e];
@@ -163,8 +177,56 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
                     h = (h + 1u) & hmask;
                 v = vals[h];
                 }
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+                cnt[g] += __popc(__ballot_sync(0xffffffffu, v != 0xffffffffu && (v & 7u) == (unsigned int)g));
+            }
+        // pass 2: rank inside the bucket -> position in the round-robin deal -> position in the lane-transposed row
+        const unsigned int start = (i * G) & 7u;
+        unsigned int base[8];
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+            base[g] = 0;
+        for (unsigned int e0 = 0; e0 < nn; e0 += 32)
+            {
+            const unsigned int e = e0 + lane;
+            unsigned int v = 0xffffffffu;
+            if (e < nn)
+                {
+                const unsigned int j = nlist[head + e];
+                unsigned int h = tile_hash(j, hshift);
+                while (keys[h] != j)
+                    h = (h + 1u) & hmask;
+                v = vals[h];
+                }
+            unsigned int rank = 0;
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+                {
+                const unsigned int mask = __ballot_sync(0xffffffffu, v != 0xffffffffu && (v & 7u) == (unsigned int)g);
+                if (v != 0xffffffffu && (v & 7u) == (unsigned int)g)
+                    rank = base[g] + __popc(mask & ((1u << lane) - 1u));
+                base[g] += __popc(mask);
+                }
+            if (v != 0xffffffffu)
+                {
+                // round r = rank deals one entry from every bucket that still has one, in rotated bucket order
+                const unsigned int mine = ((v & 7u) - start) & 7u; // my bucket's place in the rotation
+                unsigned int pos = 0;
+#pragma unroll
+                for (int g = 0; g < 8; ++g)
+                    {
+                    const unsigned int place = ((unsigned int)g - start) & 7u;
+                    pos += min(cnt[g], rank) + ((place < mine && cnt[g] > rank) ? 1u : 0u);
+                    }
+                const unsigned int r = pos % M;
+                slots[shead + (pos - r) + 4u * (r % W) + r / W] = (uint16_t)v;
+                }
+            }
+        for (unsigned int e = nn + lane; e < nnp; e += 32) // padding
+            {
             const unsigned int r = e % M;
-            slots[shead + (e - r) + 4u * (r % W) + r / W] = v;
+            slots[shead + (e - r) + 4u * (r % W) + r / W] = 0;
             }
         // rows must be disjoint and ordered by particle for the padded layout to be collision-free
         if (lane == 0 && i + 1 < N && head_list[i + 1] < head + nn)
@@ -182,8 +244,9 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         return AZB_ERR_BAD_ARGUMENT;
     const unsigned int ts = a->tile_size, ucap = a->uniq_capacity;
     const unsigned int W = a->lane_width;
+    const unsigned int G = a->group_width ? a->group_width : W;
     if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u))
-        || !(W == 1 || W == 2 || W == 4 || W == 8 || W == 16))
+        || !(W == 1 || W == 2 || W == 4 || W == 8 || W == 16) || G > 32 || (G & (G - 1u)))
         return AZB_ERR_BAD_ARGUMENT;
     *h_max_uniq = 0;
     *h_max_slot_span = 0;
@@ -208,7 +271,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
             return (int)err;
         }
     const unsigned int n_tiles = (a->N + ts - 1) / ts;
-    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, W, a->d_uniq_count,
+    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, W, G, a->d_uniq_count,
                                                       a->d_uniq, a->d_slots, a->d_status);
     err = cudaGetLastError();
     if (err != cudaSuccess)

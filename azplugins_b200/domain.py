@@ -117,6 +117,7 @@ class HaloExchange:
         self.decomp, self.state, self.group = decomp, state, group
         self.fields = tuple(fields)
         self.r_ghost = float(r_ghost)
+        self.launches = 0  # pack kernels issued (azb_gather_scalar4)
         if np.any(decomp.width[np.array(decomp.grid) > 1] < 2 * r_ghost):
             raise ValueError("sub-domain narrower than 2 r_ghost")
         dev = state.device
@@ -194,10 +195,52 @@ class HaloExchange:
                     self._bufs[key] = torch.empty((n, 4), dtype=arr.dtype, device=arr.device)
                 buf = self._bufs[key]
                 _gather_rows(buf, arr, self.send_idx[k], self.send_shift[k] if name == "pos" else None)
+                self.launches += 1 if (n and arr.is_cuda) else 0
                 sends.append((buf, self.peers_send[k]))
                 o0, o1 = N + int(self.recv_offsets[k]), N + int(self.recv_offsets[k + 1])
                 recvs.append((arr[o0:o1], self.peers_recv[k]))  # contiguous slice: received in place, no unpack kernel
         self._p2p(sends, recvs)
+
+    # ---- ghost exchange overlapped with the ghost-free part of the force evaluation ---------------------------------
+    def tile_order(self, plan):
+        """(order, n_interior): launch order of the plan's tiles with the ghost-free ones first. A tile reads a ghost iff
+        the last (largest) entry of its ascending distinct-neighbour list is >= N. Cached per plan."""
+        cached = getattr(self, "_order_cache", None)
+        if cached is not None and cached[0] is plan:
+            return cached[1], cached[2]
+        N = self.state.N
+        count = plan.uniq_count.long()
+        t = torch.arange(plan.n_tiles, device=count.device, dtype=torch.int64)
+        last = plan.uniq[t * plan.uniq_capacity + torch.clamp(count - 1, min=0)].long()
+        boundary = (count > 0) & (last >= N)
+        order = torch.cat([torch.nonzero(~boundary).flatten(), torch.nonzero(boundary).flatten()]).to(torch.int32).contiguous()
+        n_interior = int((~boundary).sum().item())
+        self._order_cache = (plan, order, n_interior)
+        return order, n_interior
+
+    def step(self, force, timestep):
+        """One force evaluation of a decomposed system: the ghost refresh runs on a side stream while the tiles that read
+        no ghost are evaluated; the tiles on the domain boundary follow once the halo has arrived. Without a tile plan:
+        exchange, then evaluate."""
+        force._prepare()
+        plan = force._current_plan()
+        if plan is None or not self.state.device.type == "cuda":
+            self.update()
+            force.compute(timestep)
+            return
+        order, n_interior = self.tile_order(plan)
+        cur = torch.cuda.current_stream(self.state.device)
+        if getattr(self, "_comm_stream", None) is None:
+            # high priority: the pack and NCCL kernels must get SM slots ahead of the queued CTAs of the force kernel
+            self._comm_stream = torch.cuda.Stream(self.state.device, priority=-1)
+        comm = self._comm_stream
+        comm.wait_stream(cur)  # the previous step's boundary tiles still read the old ghosts
+        # ghost-free tiles first: whatever the exchange does on the host side (torch's P2P wait may block), the GPU is busy
+        force.compute(timestep, tile_range=(0, n_interior), tile_order=order)
+        with torch.cuda.stream(comm):
+            self.update()
+        cur.wait_stream(comm)
+        force.compute(timestep, tile_range=(n_interior, plan.n_tiles - n_interior), tile_order=order)
 
     def bytes_per_update(self):
         st = self.state

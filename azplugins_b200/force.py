@@ -62,6 +62,7 @@ class Force:
         self.tile_size = 128
         self._plan = None
         self._tile_range = None
+        self._tile_order = None
 
     def _attach(self, state):
         if state.device.type != "cuda":
@@ -137,7 +138,12 @@ class Pair(Force):
         if not (self.use_tiles and self._tiled_kernels) or self._state is None:
             return None
         st, nl = self._state, self.nlist
-        return nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nl.mean_neighbors(st.N)))
+        nbar = nl.mean_neighbors(st.N)
+        return nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nbar), group_width=self._group_width(nbar))
+
+    def _group_width(self, nbar):
+        """Lanes per particle of the kernel that will walk the slot rows (0: same as the slot-row layout)."""
+        return 0
 
     def _pair_value(self, store, a, b, default):
         key = tuple(sorted((a, b)))
@@ -200,6 +206,7 @@ class Pair(Force):
         self._plan = self._current_plan()
         a.tiles = self._plan.pointer() if self._plan is not None else None
         a.tile_begin, a.tile_count = self._tile_range if (self._plan is not None and self._tile_range) else (0, 0)
+        a.d_tile_order = self._tile_order.data_ptr() if (self._plan is not None and self._tile_order is not None) else None
 
     def _prepare(self):
         if self._state is None:
@@ -208,9 +215,9 @@ class Pair(Force):
         if self._dirty:
             self._tables()
 
-    def _build_args(self, timestep, tile_range=None):
+    def _build_args(self, timestep, tile_range=None, tile_order=None):
         """The C-ABI argument struct of one launch (kept alive by the caller until the launch is issued)."""
-        self._tile_range = tile_range
+        self._tile_range, self._tile_order = tile_range, tile_order
         args = _abi.PairArgs()
         self._fill_pair_args(args)
         return args
@@ -224,11 +231,15 @@ class Pair(Force):
         _abi.check(code, f"azb_pair_forces[{self._spec.name}]")
         self.launches += 1
 
-    def compute(self, timestep=0, tile_range=None):
-        """One evaluation (one kernel launch). ``tile_range=(first_tile, n_tiles)`` restricts a tile-staged launch to
-        those tiles and leaves the outputs of all other particles untouched (used to pipeline a step against copies)."""
+    def compute(self, timestep=0, tile_range=None, tile_order=None):
+        """One evaluation (one kernel launch). ``tile_range=(first, count)`` restricts a tile-staged launch to that range
+        of launch positions and leaves the outputs of all other particles untouched; ``tile_order`` (device int32 tensor)
+        maps launch positions to tiles. Together they let a step overlap with copies (``hostio.HostStep``) or with the
+        ghost exchange (``domain.HaloExchange.step``)."""
         self._prepare()
-        self._launch(self._build_args(timestep, tile_range))
+        if tile_range is not None and tile_range[1] == 0:
+            return  # an empty range (the ABI reads tile_count == 0 as "every tile")
+        self._launch(self._build_args(timestep, tile_range, tile_order))
 
 
 class DPDThermoPair(Pair):
@@ -244,14 +255,19 @@ class DPDThermoPair(Pair):
         self.dt = 0.005  # set by the integrator (hoomd passes m_deltaT to the force)
 
     def _slot_lane_width(self, nbar):
-        return 1  # the DPD queue kernels read slots one at a time in list order
+        return 1  # the DPD queue kernels read slots one at a time in row order
+
+    def _group_width(self, nbar):
+        if self.threads_per_particle:
+            return self.threads_per_particle
+        return 1 if nbar <= 8 else (2 if nbar <= 16 else (4 if nbar <= 96 else (8 if nbar <= 256 else 16)))  # azb_dpd.cu's choice, clamped
 
     def _kT_at(self, timestep):
         return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)
 
-    def _build_args(self, timestep, tile_range=None):
+    def _build_args(self, timestep, tile_range=None, tile_order=None):
         st = self._state
-        self._tile_range = tile_range
+        self._tile_range, self._tile_order = tile_range, tile_order
         args = _abi.DPDArgs()
         self._fill_pair_args(args.pair)
         args.d_vel = st.vel.data_ptr()
@@ -276,7 +292,6 @@ class AnisotropicPair(Pair):
 
     _accepted_modes = ("none", "shift")
     _kind = _abi.KIND_ANISO
-    _tiled_kernels = False
 
     def __init__(self, nlist, default_r_cut=None, mode="none"):
         super().__init__(nlist, default_r_cut, 0.0, mode)
@@ -285,9 +300,9 @@ class AnisotropicPair(Pair):
         super()._attach(state)
         self._torque = torch.zeros((state.N, 4), dtype=self._force.dtype, device=state.device)
 
-    def _build_args(self, timestep, tile_range=None):
+    def _build_args(self, timestep, tile_range=None, tile_order=None):
         st = self._state
-        self._tile_range = tile_range
+        self._tile_range, self._tile_order = tile_range, tile_order
         args = _abi.AnisoArgs()
         self._fill_pair_args(args.pair)
         args.d_orientation = st.orientation.data_ptr()

@@ -33,18 +33,19 @@ class NeighborList:
         self.n_neigh = None
         self._tiles = {}
 
-    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1):
+    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0):
         """Tile plan of the current arrays (``azb_tiles_build``), built once per list rebuild and cached; ``None`` when a
         tile holds more than ``uniq_capacity`` distinct neighbours even at the smallest tile size. ``lane_width`` is the
-        slot-row layout: 1 for the DPD kernels, the lanes per particle for the pair kernels."""
-        key = (int(tile_size), int(uniq_capacity), int(lane_width))
+        slot-row layout: 1 for the DPD kernels, the lanes per particle for the pair kernels; ``group_width`` the lanes per
+        particle of the kernel that walks the rows (bank rotation of the row order; 0 = ``lane_width``)."""
+        key = (int(tile_size), int(uniq_capacity), int(lane_width), int(group_width))
         if key not in self._tiles:
             from . import _nlist_gpu
 
             plan = None
             ts = int(tile_size)
             while plan is None and ts >= 32:
-                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width))
+                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width))
                 ts //= 2
             self._tiles[key] = plan
         return self._tiles[key]

@@ -103,11 +103,13 @@ typedef struct azb_box
 /* Tile plan (optional, azb_tiles_build below): a derived view of one neighbour list that lets the force kernels stage
  * neighbour data in shared memory. Particles [t*tile_size, (t+1)*tile_size) form tile t; d_uniq holds, per tile, the
  * ascending list of distinct particle indices appearing in its rows; d_slots holds, entry for entry, the position of
- * each neighbour inside its tile's list. Slot rows are laid out for the kernel that reads them: a group of W =
+ * each neighbour inside its tile's list. A slot row holds the same neighbours as the list row, in bank-rotated order
+ * (csrc/azb_tiles.cu: dealt round-robin over the 8 shared-memory bank groups, so that the lanes of a quarter-warp read 8
+ * different bank groups at every step). Slot rows are laid out for the kernel that reads them: a group of W =
  * lane_width lanes walks a row in blocks of 4W entries, each lane fetching its four entries of a block with one 8-byte
  * load, and the lanes of a group touching consecutive list entries at the same time (consecutive entries are mostly
- * consecutive slots, i.e. distinct shared-memory banks). So the slot of list entry e = b*4W + u*W + l of particle i
- * (d_nlist[d_head_list[i] + e]) is stored at d_slots[AZB_SLOT_HEAD(head, i, W) + b*4W + 4*l + u], rows are padded with
+ * bank groups in sequence). So entry e = b*4W + u*W + l of particle i's (reordered) row is stored at
+ * d_slots[AZB_SLOT_HEAD(head, i, W) + b*4W + 4*l + u], rows are padded with
  * slot 0 to a multiple of 4W entries and start on a multiple of max(4W, 8) entries, i.e. 16 bytes (W = 1 is the plain
  * order). This needs rows that
  * are disjoint and ordered by particle (head_list[i+1] >= head_list[i] + n_neigh[i], as HOOMD's prefix-sum head list
@@ -155,6 +157,8 @@ typedef struct azb_pair_args
     const azb_tile_plan* tiles;        /* host pointer; NULL = gather neighbour data straight from global memory */
     unsigned int tile_begin;           /* with tiles: evaluate only tiles [tile_begin, tile_begin + tile_count) and leave the */
     unsigned int tile_count;           /* outputs of all other particles untouched; tile_count == 0 = every tile */
+    const unsigned int* d_tile_order;  /* optional device permutation of the tiles: launch position p evaluates tile
+                                          d_tile_order[p] (e.g. ghost-free tiles first, so they overlap the halo exchange) */
     } azb_pair_args;
 
 /* mirrors HOOMD dpd_pair_args_t: pair args + velocities, tags, RNG key material, dt and kT */
@@ -288,6 +292,8 @@ typedef struct azb_tile_build_args
     unsigned int tile_size;
     unsigned int uniq_capacity;
     unsigned int lane_width;         /* 1, 2, 4, 8 or 16 */
+    unsigned int group_width;        /* lanes per particle of the kernel that will walk the rows (bank rotation of the row
+                                        order); 0 = lane_width */
     unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
     unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
     uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */

@@ -26,6 +26,11 @@ def error_metrics(got, want):
     return (float(err[i]) if len(err) else 0.0), i
 
 
+def _with_periodic(box, periodic):
+    """Same extent, other periodic flags (what a domain-decomposed rank hands to the kernels)."""
+    return box if periodic is None else az.Box(box.Lx, box.Ly, box.Lz, periodic=tuple(periodic))
+
+
 def make_state(box, pos, typeid, ntypes, bits, **kw):
     snap = az.Snapshot(box, pos, typeid=typeid, types=TYPE_NAMES[:ntypes], **kw)
     return az.State(snap, device="cuda", scalar_bits=bits)
@@ -39,9 +44,10 @@ def attach_with_oracle_nlist(force, state, hs):
 
 
 def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", ron_by=None, seed=101, tpp=0, virial=True, which=None,
-             buffer=0.3, system=None, use_tiles=True, tile_size=128):
+             buffer=0.3, system=None, use_tiles=True, tile_size=128, periodic=None):
     spec = cases.SPEC_BY_API[api]
     box, pos, typeid = system if system is not None else cases.random_fluid(n, rho, ntypes, seed)
+    box = _with_periodic(box, periodic)
     par, rcsq, ronsq, rc = cases.pair_tables(spec, par_by, rc_by, ntypes, bits, ron_by)
     r_list = np.where(rc > 0, rc + buffer, 0.0)
     # oracle in double on the same (bits-rounded) coordinates: convert through the Scalar type first
@@ -77,9 +83,10 @@ def run_pair(api, par_by, rc_by, bits, n=4000, rho=0.7, ntypes=2, mode="none", r
 
 
 def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0, sim_seed=42, dt=0.01, kT=1.0, tpp=0, buffer=0.4,
-            use_tiles=True, tile_size=128):
+            use_tiles=True, tile_size=128, periodic=None):
     spec = cases.SPEC_BY_API["DPDGeneralWeight"]
     box, pos, typeid = cases.random_fluid(n, rho, ntypes, seed, jitter=0.5)
+    box = _with_periodic(box, periodic)
     rng = np.random.default_rng(seed + 1)
     vel = rng.normal(size=pos.shape)
     tag = rng.permutation(len(pos)).astype(np.uint32)
@@ -109,7 +116,7 @@ def run_dpd(par_by, rc_by, bits, n=6000, rho=3.0, ntypes=2, seed=201, timestep=0
     return f, hs_b, hs
 
 
-def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=301, tpp=0, buffer=0.4):
+def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=301, tpp=0, buffer=0.4, use_tiles=True, tile_size=128):
     spec = cases.SPEC_BY_API["TwoPatchMorse"]
     box, pos, typeid = cases.random_fluid(n, rho, ntypes, seed)
     q = cases.random_unit_quaternions(len(pos), seed + 1)
@@ -130,8 +137,10 @@ def run_aniso(par_by, rc_by, bits, n=5000, rho=0.6, ntypes=2, mode="none", seed=
         f.params[key] = p
         f.r_cut[key] = rc_by[(i, j)]
     f.threads_per_particle = tpp
+    f.use_tiles, f.tile_size = use_tiles, tile_size
     attach_with_oracle_nlist(f, st, hs_b)
     f.compute(0)
+    assert (f._plan is not None) == bool(use_tiles)
     return f, hs_b
 
 

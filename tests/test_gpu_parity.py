@@ -214,6 +214,17 @@ def test_pair_threads_per_particle_variants(tiles, tpp):
         _check(f"pair/plj/tiles{tiles}/tpp{tpp}/T{ntypes}", f, hs, 32)
 
 
+@pytest.mark.parametrize("periodic", [(False, True, True), (True, False, False), (False, False, False)], ids=lambda p: "".join("p" if x else "n" for x in p))
+@pytest.mark.parametrize("tiles", [False, True], ids=["direct", "tiles"])
+def test_partly_periodic_boxes(tiles, periodic):
+    """The box a domain-decomposed rank sees: periodic only along the undecomposed directions."""
+    par_by, rc_by = PAIRS["PerturbedLennardJones"]
+    f, hs = GC.run_pair("PerturbedLennardJones", par_by, rc_by, 32, n=3000, use_tiles=tiles, periodic=periodic)
+    _check(f"pair/plj/{'tiles' if tiles else 'direct'}/box{periodic}", f, hs, 32)
+    f, hs, _ = GC.run_dpd(DPD_PARAMS[0], DPD_PARAMS[1], 32, n=3000, timestep=3, use_tiles=tiles, periodic=periodic)
+    _check(f"dpd/{'tiles' if tiles else 'direct'}/box{periodic}", f, hs, 32)
+
+
 def test_pair_without_virial_leaves_virial_untouched():
     par_by, rc_by = PAIRS["ExpandedYukawa"]
     f, hs = GC.run_pair("ExpandedYukawa", par_by, rc_by, 32, n=2000, virial=False)
@@ -313,9 +324,17 @@ TPM_PARAMS = ({(0, 0): dict(M_d=1.8347, M_r=0.0302, r_eq=1.0043, omega=20.0, alp
 
 @pytest.mark.parametrize("bits", [32, 64])
 @pytest.mark.parametrize("mode", ["none", "shift"])
-def test_aniso_random_system(mode, bits):
-    f, hs = GC.run_aniso(TPM_PARAMS[0], TPM_PARAMS[1], bits, mode=mode)
-    _check(f"aniso/tpm/{mode}/{bits}", f, hs, bits, torque=True)
+@pytest.mark.parametrize("tiles", [False, True], ids=["direct", "tiles"])
+def test_aniso_random_system(tiles, mode, bits):
+    f, hs = GC.run_aniso(TPM_PARAMS[0], TPM_PARAMS[1], bits, mode=mode, use_tiles=tiles)
+    _check(f"aniso/{'tiles' if tiles else 'direct'}/tpm/{mode}/{bits}", f, hs, bits, torque=True)
+
+
+@pytest.mark.parametrize("tpp", [2, 4, 8, 16])
+@pytest.mark.parametrize("tile_size", [32, 256])
+def test_aniso_tile_variants(tile_size, tpp):
+    f, hs = GC.run_aniso(TPM_PARAMS[0], TPM_PARAMS[1], 32, n=3000, tpp=tpp, tile_size=tile_size)
+    _check(f"aniso/tiles{tile_size}/tpp{tpp}", f, hs, 32, torque=True)
 
 
 @pytest.mark.parametrize("bits", [32, 64])

@@ -45,8 +45,15 @@ def test_tile_plan_matches_numpy(tile_size, lane_width):
             e = np.arange((nn[i] + M - 1) // M * M)
             r = e % M
             stored = slots[sh + (e - r) + 4 * (r % W) + r // W]  # entry e of the row in the lane-transposed layout
-            assert np.array_equal(want[stored[: nn[i]]], lst[head[i] : head[i] + nn[i]])  # slot -> the listed neighbour
+            # a slot row holds the row's neighbours, each exactly once, in bank-rotated order
+            assert np.array_equal(np.sort(want[stored[: nn[i]]]), np.sort(lst[head[i] : head[i] + nn[i]]))
             assert np.all(stored[nn[i] :] == 0)  # padding
+            # the deal: position e carries bank group (start + e) mod 8 until the first bucket runs dry
+            if nn[i]:
+                groups = stored[: nn[i]] & 7
+                dry = np.bincount(groups, minlength=8).min() * 8
+                start = (i * W) & 7
+                assert np.array_equal(groups[:dry], (start + np.arange(dry)) & 7)
         worst = max(worst, len(want))
     assert plan.max_uniq == worst
     spans = []
