@@ -175,7 +175,40 @@ EXPORTS = (
     "azb_nlist_fill",
     "azb_gather_scalar4",
     "azb_tiles_build",
+    "azb_ipc_export",
+    "azb_ipc_open",
+    "azb_halo_push",
+    "azb_halo_wait",
+    "azb_halo_signal",
 )
+
+IPC_HANDLE_BYTES = 64
+
+
+class HaloRoute(C.Structure):
+    """``azb_halo_route``: rows ``d_src[d_idx[0..n)]`` (+ shift) -> ``d_dst[0..n)``."""
+
+    _fields_ = [
+        ("d_src", C.c_void_p),
+        ("d_dst", C.c_void_p),
+        ("d_idx", C.c_void_p),
+        ("n", C.c_uint),
+        ("row_begin", C.c_uint),
+        ("shift", C.c_double * 3),
+    ]
+
+
+class HaloPushArgs(C.Structure):
+    _fields_ = [
+        ("d_routes", C.c_void_p),
+        ("n_routes", C.c_uint),
+        ("total_rows", C.c_uint),
+        ("d_peer_flags", C.c_void_p),
+        ("n_flags", C.c_uint),
+        ("d_counter", C.c_void_p),
+        ("epoch", C.c_uint),
+    ]
+
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
 
@@ -218,6 +251,16 @@ def load():
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.azb_tiles_build.restype = C.c_int
     lib.azb_tiles_build.argtypes = [C.POINTER(TileBuildArgs), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_void_p]
+    lib.azb_ipc_export.restype = C.c_int
+    lib.azb_ipc_export.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_size_t)]
+    lib.azb_ipc_open.restype = C.c_int
+    lib.azb_ipc_open.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.azb_halo_push.restype = C.c_int
+    lib.azb_halo_push.argtypes = [C.c_int, C.POINTER(HaloPushArgs), C.c_void_p]
+    lib.azb_halo_wait.restype = C.c_int
+    lib.azb_halo_wait.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_void_p]
+    lib.azb_halo_signal.restype = C.c_int
+    lib.azb_halo_signal.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

@@ -14,6 +14,7 @@ so forces are independent of the decomposition up to summation order.
 
 import ctypes as C
 import itertools
+import os
 
 import numpy as np
 import torch
@@ -113,9 +114,11 @@ def _gather_rows(out, src, idx, shift):
 class HaloExchange:
     """Ghost bookkeeping of one rank: builds the send lists, appends ghost storage to the State, refreshes it per step."""
 
-    def __init__(self, decomp, state, r_ghost, fields=("pos",), group=None):
+    def __init__(self, decomp, state, r_ghost, fields=("pos",), group=None, transport=None):
         self.decomp, self.state, self.group = decomp, state, group
         self.fields = tuple(fields)
+        self.transport = "nccl"  # "peer" once the neighbours' arrays are mapped (below)
+        self.timeout_ms = 30000
         self.r_ghost = float(r_ghost)
         self.launches = 0  # pack kernels issued (azb_gather_scalar4)
         if np.any(decomp.width[np.array(decomp.grid) > 1] < 2 * r_ghost):
@@ -166,6 +169,119 @@ class HaloExchange:
             recvs.append((state.tag[o0:o1], self.peers_recv[k]))
         self._p2p(sends, recvs)
         self.update(all_fields=True)
+        want = transport or os.environ.get("AZB_HALO_TRANSPORT", "auto")
+        if want not in ("auto", "peer", "nccl"):
+            raise ValueError("transport must be 'auto', 'peer' or 'nccl'")
+        if want != "nccl" and decomp.world > 1 and dev.type == "cuda":
+            self._setup_peer(required=(want == "peer"))
+
+    # ---- ghost refresh over peer memory: one push kernel per step instead of pack kernels + grouped send/recv ---------
+    def _setup_peer(self, required):
+        """Map the neighbours' particle arrays and flag words into this process (CUDA IPC over NVLink) and build the route
+        table of ``azb_halo_push``. Every rank decides together: if any mapping fails, all stay on the NCCL exchange."""
+        st, lib, nd = self.state, _abi.load(), len(self.dirs)
+        dev = st.device
+        # flag words: [0, nd) data epochs written by the ranks that send to me; [nd, 2 nd) acknowledgements written by the ranks
+        # I send to; then the push kernel's arrival counter and the timeout indicator
+        self._sync = torch.zeros(2 * nd + 2, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
+
+        def export(t):
+            h = C.create_string_buffer(_abi.IPC_HANDLE_BYTES)
+            off = C.c_size_t(0)
+            code = lib.azb_ipc_export(C.c_void_p(t.data_ptr()), h, C.byref(off))
+            return (code, h.raw, int(off.value))
+
+        mine = {"N": st.N, "recv_offsets": [int(x) for x in self.recv_offsets], "sync": export(self._sync),
+                "fields": {name: export(getattr(st, name)) for name in ("pos", "vel", "orientation")}}
+        everyone = [None] * self.decomp.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        ok, opened = True, {}
+
+        def open_(rank, what):
+            nonlocal ok
+            code, handle, off = what
+            if rank == self.decomp.rank:
+                return None  # caller uses the local pointer
+            if code != 0:
+                ok = False
+                return 0
+            key = (rank, handle, off)
+            if key not in opened:
+                ptr = C.c_void_p(0)
+                if lib.azb_ipc_open(handle, off, C.byref(ptr)) != 0:
+                    ok = False
+                    return 0
+                opened[key] = int(ptr.value)
+            return opened[key]
+
+        row_bytes = 4 * (st.scalar_bits // 8)
+        routes, data_flags, ack_flags = [], [], []
+        for k, d in enumerate(self.dirs):
+            to, frm = self.peers_send[k], self.peers_recv[k]
+            # the rank in direction d stores what I send for direction k in ITS slot k; its data flag k is mine to raise
+            base = open_(to, everyone[to]["sync"])
+            data_flags.append((self._sync.data_ptr() if base is None else base) + 4 * k)
+            # the rank behind me filled my slot k: its acknowledgement word k is mine to raise once I have read the ghosts
+            base = open_(frm, everyone[frm]["sync"])
+            ack_flags.append((self._sync.data_ptr() if base is None else base) + 4 * (nd + k))
+            first = everyone[to]["N"] + everyone[to]["recv_offsets"][k]
+            for name in self.fields:
+                base = open_(to, everyone[to]["fields"][name])
+                if base is None:
+                    base = getattr(st, name).data_ptr()
+                shift = self.decomp.neighbor(d)[1] if name == "pos" else np.zeros(3)
+                routes.append((getattr(st, name).data_ptr(), base + first * row_bytes, self.send_idx[k].data_ptr(),
+                               int(self.send_idx[k].numel()), shift))
+        flag = torch.tensor([0 if ok else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, group=self.group)
+        if int(flag.item()) != 0:
+            if required:
+                raise RuntimeError("halo transport 'peer': the neighbours' memory cannot be mapped (no P2P access between the GPUs?)")
+            return
+        table = (_abi.HaloRoute * max(len(routes), 1))()
+        begin = 0
+        for r, (src, dst, idx, n, shift) in zip(table, routes):
+            r.d_src, r.d_dst, r.d_idx, r.n, r.row_begin = src, dst, idx, n, begin
+            r.shift[0], r.shift[1], r.shift[2] = (float(x) for x in shift)
+            begin += n
+        self._routes = torch.frombuffer(bytearray(bytes(table)), dtype=torch.uint8).to(dev)
+        self._data_ptrs = torch.tensor(data_flags, dtype=torch.int64, device=dev)
+        self._ack_ptrs = torch.tensor(ack_flags, dtype=torch.int64, device=dev)
+        a = _abi.HaloPushArgs()
+        a.d_routes, a.n_routes, a.total_rows = self._routes.data_ptr(), len(routes), begin
+        a.d_peer_flags, a.n_flags = self._data_ptrs.data_ptr(), nd
+        a.d_counter = self._sync.data_ptr() + 4 * (2 * nd)
+        self._push_args, self._epoch = a, 0
+        self._d_error = self._sync.data_ptr() + 4 * (2 * nd + 1)
+        dist.barrier(group=self.group)  # nobody raises a flag before everybody's words exist
+        self.transport = "peer"
+
+    def _peer_begin(self, stream):
+        """Start of a refresh on ``stream``: whatever was enqueued before has finished reading the previous ghosts."""
+        lib, nd = _abi.load(), len(self.dirs)
+        self._epoch = (self._epoch + 1) & 0x7FFFFFFF
+        _abi.check(lib.azb_halo_signal(self._ack_ptrs.data_ptr(), nd, self._epoch - 1, stream), "azb_halo_signal")
+        self.launches += 1
+
+    def _peer_push(self, stream):
+        """Wait until the receivers have released their ghost rows, then store this step's rows into them."""
+        lib, nd = _abi.load(), len(self.dirs)
+        _abi.check(lib.azb_halo_wait(self._sync.data_ptr() + 4 * nd, nd, self._epoch - 1, self.timeout_ms, self._d_error, stream), "azb_halo_wait")
+        self._push_args.epoch = self._epoch
+        _abi.check(lib.azb_halo_push(self.state.scalar_bits, C.byref(self._push_args), stream), "azb_halo_push")
+        self.launches += 2
+
+    def _peer_arrived(self, stream):
+        """Stream-ordered wait for this step's ghosts from every neighbour."""
+        lib, nd = _abi.load(), len(self.dirs)
+        _abi.check(lib.azb_halo_wait(self._sync.data_ptr(), nd, self._epoch, self.timeout_ms, self._d_error, stream), "azb_halo_wait")
+        self.launches += 1
+
+    def check(self):
+        """Raise if a flag wait ever timed out (a neighbour stopped stepping); synchronises."""
+        if self.transport == "peer" and int(self._sync[2 * len(self.dirs) + 1].item()) != 0:
+            raise RuntimeError("halo exchange: timed out waiting for a neighbouring rank")
 
     def _p2p(self, sends, recvs):
         """One grouped exchange; per peer, sends and receives are posted in direction order on both sides so they match."""
@@ -184,6 +300,12 @@ class HaloExchange:
         """Refresh ghost copies of the dynamic fields (every step, before the force kernels)."""
         st = self.state
         N = st.N
+        if self.transport == "peer" and not all_fields:
+            stream = C.c_void_p(torch.cuda.current_stream(st.device).cuda_stream)
+            self._peer_begin(stream)
+            self._peer_push(stream)
+            self._peer_arrived(stream)
+            return
         fields = ("pos", "vel", "orientation") if all_fields else self.fields
         sends, recvs = [], []
         for name in fields:
@@ -234,6 +356,19 @@ class HaloExchange:
             # high priority: the pack and NCCL kernels must get SM slots ahead of the queued CTAs of the force kernel
             self._comm_stream = torch.cuda.Stream(self.state.device, priority=-1)
         comm = self._comm_stream
+        if self.transport == "peer":
+            s_cur, s_comm = C.c_void_p(cur.cuda_stream), C.c_void_p(comm.cuda_stream)
+            self._peer_begin(s_cur)  # acknowledge: the previous step's kernels are done with the old ghosts
+            comm.wait_stream(cur)    # ... and with the local rows the push reads
+            force.compute(timestep, tile_range=(0, n_interior), tile_order=order)
+            # the boundary tiles go on the (high-priority) side stream right behind the arrival wait: they start as soon as
+            # the neighbours' rows have landed and share the GPU with the tail of the ghost-free launch
+            with torch.cuda.stream(comm):
+                self._peer_push(s_comm)
+                self._peer_arrived(s_comm)
+                force.compute(timestep, tile_range=(n_interior, plan.n_tiles - n_interior), tile_order=order)
+            cur.wait_stream(comm)
+            return
         comm.wait_stream(cur)  # the previous step's boundary tiles still read the old ghosts
         # ghost-free tiles first: whatever the exchange does on the host side (torch's P2P wait may block), the GPU is busy
         force.compute(timestep, tile_range=(0, n_interior), tile_order=order)

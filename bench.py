@@ -447,7 +447,7 @@ def run_b200(args):
                    "neighbor_data": tile_note,
                    "l2": "flushed between timed steps (384 MiB fill)" if flush is not None else "not flushed; working set > L2",
                    "parallelism": "1 GPU" if world == 1 else
-                   f"{world} GPUs, spatial domains {GRIDS[world]}, ghost halo over NCCL P2P every step ({halo.bytes_per_update()} B sent/rank/step, "
+                   f"{world} GPUs, spatial domains {GRIDS[world]}, ghost halo every step over {'peer memory (one push kernel storing into the neighbours\' arrays over NVLink, flag-synchronised)' if halo.transport == 'peer' else 'NCCL send/recv'}, overlapped with the ghost-free tiles ({halo.bytes_per_update()} B sent/rank/step, "
                    f"{st.n_ghost} ghosts on rank 0)"},
         "clocks": clocks, "roofline": roofline, "gpu_launches": int(launches),
         "nlist_build_s": nlist_build_s, "host_affinity": numa_note,
@@ -530,6 +530,8 @@ def run_b200(args):
                                                   f"{sec * 1e3:.1f} ms each, OpenMP over particles, Scalar={'float' if args.bits == 32 else 'double'}"}
             except Exception as exc:  # the baseline is a report, never a reason to lose the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
+    if halo is not None:
+        halo.check()  # a flag wait that timed out would have left stale ghosts
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

@@ -309,6 +309,48 @@ AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max
 AZB_API int azb_gather_scalar4(int scalar_bits, const void* d_src, const unsigned int* d_idx, const void* d_shift, void* d_out,
                                size_t n, void* stream);
 
+/* ---- ghost halo over peer memory (SURVEY.md §8 e; replaces HOOMD's CommunicatorGPU pack -> MPI -> unpack for ranks on one
+ * NVLink/NVSwitch node). One kernel per step gathers every boundary row of every direction and field and stores it
+ * straight into the neighbouring rank's particle arrays (behind its local particles, where HOOMD keeps ghosts), then
+ * raises a flag in that rank's memory; the receiver's stream waits on its own flags. No staging buffer, no unpack.
+ *
+ *   azb_ipc_export   handle + byte offset of a device pointer inside its allocation, to hand to the other processes
+ *   azb_ipc_open     map another process' allocation (cached per handle), returns the pointer at that offset
+ *   azb_halo_push    rows of all routes -> destination memory; when every row is written, *d_peer_flags[i] = epoch
+ *   azb_halo_wait    stream-ordered wait until d_flags[i] has reached epoch for all i (bounded: after timeout_ms it sets
+ *                    *d_error = 1 and returns, it never hangs the device)
+ *   azb_halo_signal  *d_peer_flags[i] = epoch, stream-ordered ("everything before this on the stream is done": the
+ *                    receiver's acknowledgement that the previous ghosts have been read and may be overwritten)
+ * Epochs are compared as signed differences, so the counter may wrap. */
+#define AZB_IPC_HANDLE_BYTES 64
+typedef struct azb_halo_route
+    {
+    const void* d_src;         /* Scalar4 array the rows are taken from (local) */
+    void* d_dst;               /* first destination row (peer memory from azb_ipc_open, or local) */
+    const unsigned int* d_idx; /* [n] rows of d_src */
+    unsigned int n;
+    unsigned int row_begin; /* sum of n over the routes before this one */
+    double shift[3];        /* added to x, y, z: the periodic image the receiver sees */
+    } azb_halo_route;
+
+typedef struct azb_halo_push_args
+    {
+    const azb_halo_route* d_routes; /* device array */
+    unsigned int n_routes;
+    unsigned int total_rows;
+    unsigned int* const* d_peer_flags; /* device array of n_flags pointers (peer memory) */
+    unsigned int n_flags;
+    unsigned int* d_counter; /* one u32 of scratch, zero before the first call */
+    unsigned int epoch;
+    } azb_halo_push_args;
+
+AZB_API int azb_ipc_export(const void* d_ptr, unsigned char* handle, size_t* offset);
+AZB_API int azb_ipc_open(const unsigned char* handle, size_t offset, void** d_ptr);
+AZB_API int azb_halo_push(int scalar_bits, const azb_halo_push_args* args, void* stream);
+AZB_API int azb_halo_wait(const unsigned int* d_flags, unsigned int n, unsigned int epoch, unsigned int timeout_ms, unsigned int* d_error,
+                          void* stream);
+AZB_API int azb_halo_signal(unsigned int* const* d_peer_flags, unsigned int n, unsigned int epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,6 +32,7 @@ def main():
     box, pos, vel, tag, typeid = domain_worker.global_system(n=20000)
     params = {(0, 0): dict(A=25.0, gamma=4.5, s=2.0), (0, 1): dict(A=50.0, gamma=4.5, s=2.0), (1, 1): dict(A=25.0, gamma=4.5, s=0.5)}
     worst = 0.0
+    transports = set()
     # float: a ghost that crossed the global boundary is stored pre-shifted (x_j +/- L rounded to float), the undecomposed
     # system wraps dx instead; the two roundings differ by ~ulp(L) on dx, i.e. ~1e-5 on a force — inherent to float
     # coordinates under any decomposition (HOOMD's MPI ghosts included), so float is held to 1e-4 here
@@ -76,6 +77,29 @@ def main():
             order, n_interior = halo.tile_order(f._plan)
             assert sorted(order.tolist()) == list(range(f._plan.n_tiles))
             assert 0 <= n_interior <= f._plan.n_tiles  # (in a 10 000-particle domain every tile touches a face)
+            # several steps with moving particles: the peer-memory push (flags, epochs, acknowledgements) must deliver exactly
+            # the rows the grouped NCCL send/recv delivers
+            transports.add(halo.transport)
+            if halo.transport == "peer":
+                gen = torch.Generator(device="cpu").manual_seed(100 + rank)
+                for it in range(4):
+                    st.pos[: st.N, :3] += (torch.rand((st.N, 3), generator=gen, dtype=torch.float64) * 2e-3 - 1e-3).to(st.pos)
+                    st.vel[: st.N, :3] += (torch.rand((st.N, 3), generator=gen, dtype=torch.float64) * 2e-3 - 1e-3).to(st.vel)
+                    halo.step(f, 8 + it)
+                    torch.cuda.synchronize()
+                    by_peer = (f._force.clone(), st.pos[st.N:].clone(), st.vel[st.N:].clone())
+                    halo.transport = "nccl"
+                    st.pos[st.N:].zero_()
+                    st.vel[st.N:].zero_()
+                    halo.step(f, 8 + it)
+                    torch.cuda.synchronize()
+                    halo.transport = "peer"
+                    assert torch.equal(st.pos[st.N:], by_peer[1]) and torch.equal(st.vel[st.N:], by_peer[2]), (rank, bits, it, "ghost rows differ")
+                    assert torch.equal(f._force, by_peer[0]), (rank, bits, it, "forces differ between transports")
+                halo.update()  # the non-overlapped refresh uses the same flags
+                torch.cuda.synchronize()
+                assert torch.equal(st.pos[st.N:], by_peer[1])
+                halo.check()
         want = f_by_tag[tag[own]]
         keep = ~amb[tag[own]]
         scale = np.sqrt(np.mean(np.sum(want[:, :3] ** 2, axis=1)))
@@ -86,7 +110,7 @@ def main():
     t = torch.tensor([worst], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print(f"mgpu force check ok: world={world} worst err/tol={t.item():.3g}")
+        print(f"mgpu force check ok: world={world} worst err/tol={t.item():.3g} halo transports={sorted(transports)}")
     dist.destroy_process_group()
 
 

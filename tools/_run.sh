@@ -1,11 +1,6 @@
-#!/bin/bash
-# scratch GPU script
-cd /root/repo
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > gpurun_out/t.log
-{
-python bench.py --workload plj4m --tpp 2 --steps 20 --warmup 5 --no-cpu-baseline
-AZB_NO_PACKED=1 python bench.py --workload plj4m --tpp 2 --steps 20 --warmup 5 --no-cpu-baseline
-python bench.py --steps 30 --warmup 5 --no-cpu-baseline
-python bench.py --workload patchy2m --steps 20 --warmup 5 --no-cpu-baseline
-} > gpurun_out/b.log 2>&1
+cd /root/repo; mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -30 > gpurun_out/r1t_pytest.log
+for w in dpd plj4m; do
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --workload $w --steps 10 --warmup 3 --no-cpu-baseline 2>> gpurun_out/r1t_err.log | tail -1 >> gpurun_out/r1t_bench.log
+done
+
