@@ -175,6 +175,10 @@ EXPORTS = (
     "azb_nlist_fill",
     "azb_gather_scalar4",
     "azb_tiles_build",
+    "azb_barrier_forces",
+    "azb_nve_step_one",
+    "azb_nve_step_two",
+    "azb_displacement_check",
     "azb_ipc_export",
     "azb_ipc_open",
     "azb_halo_push",
@@ -183,6 +187,43 @@ EXPORTS = (
 )
 
 IPC_HANDLE_BYTES = 64
+ERR_BARRIER_INVALID = 10004
+BARRIER_PLANAR, BARRIER_SPHERICAL = 0, 1
+
+
+class NveArgs(C.Structure):
+    """``azb_nve_args``."""
+
+    _fields_ = [
+        ("d_pos", C.c_void_p),
+        ("d_vel", C.c_void_p),
+        ("d_accel", C.c_void_p),
+        ("d_image", C.c_void_p),
+        ("N", C.c_uint),
+        ("box", Box),
+        ("deltaT", C.c_double),
+        ("d_forces", C.c_void_p),
+        ("n_forces", C.c_uint),
+        ("d_net_force", C.c_void_p),
+    ]
+
+
+class BarrierArgs(C.Structure):
+    """``azb_barrier_args``."""
+
+    _fields_ = [
+        ("d_force", C.c_void_p),
+        ("d_virial", C.c_void_p),
+        ("virial_pitch", C.c_size_t),
+        ("N", C.c_uint),
+        ("ntypes", C.c_uint),
+        ("d_pos", C.c_void_p),
+        ("d_params", C.c_void_p),
+        ("global_box", Box),
+        ("location", C.c_double),
+        ("block_size", C.c_uint),
+    ]
+
 
 
 class HaloRoute(C.Structure):
@@ -251,6 +292,13 @@ def load():
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.azb_tiles_build.restype = C.c_int
     lib.azb_tiles_build.argtypes = [C.POINTER(TileBuildArgs), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_void_p]
+    lib.azb_barrier_forces.restype = C.c_int
+    lib.azb_barrier_forces.argtypes = [C.c_int, C.c_int, C.POINTER(BarrierArgs), C.c_void_p]
+    for fn in (lib.azb_nve_step_one, lib.azb_nve_step_two):
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_int, C.POINTER(NveArgs), C.c_void_p]
+    lib.azb_displacement_check.restype = C.c_int
+    lib.azb_displacement_check.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint, C.POINTER(Box), C.c_double, C.c_void_p, C.c_void_p]
     lib.azb_ipc_export.restype = C.c_int
     lib.azb_ipc_export.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_size_t)]
     lib.azb_ipc_open.restype = C.c_int

@@ -57,6 +57,7 @@ def build_cell_nlist(nl, state, row_align=1):
     del keep
     nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
     nl._tiles = {}
+    nl._last_pos = state.pos[: state.N].clone()  # reference point of the displacement check (md.Integrator)
     nl.launches = getattr(nl, "launches", 0) + 1
     return nl
 

@@ -159,6 +159,7 @@ class HaloExchange:
         tag[:N] = state.tag[:N]
         state.tag = tag
         state.n_ghost = n_ghost
+        state.global_box = decomp.global_box  # what external.HarmonicBarrier wraps positions into
         state.box = decomp.local_box()
         self._bufs = {}
         # static data once: tags (as a 1-column exchange) — types travel inside pos.w with every position update

@@ -309,6 +309,65 @@ AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max
 AZB_API int azb_gather_scalar4(int scalar_bits, const void* d_src, const unsigned int* d_idx, const void* d_shift, void* d_out,
                                size_t n, void* stream);
 
+/* ---- external.PlanarHarmonicBarrier / SphericalHarmonicBarrier -----------------------------------------
+ * azb_barrier_forces <- azplugins::gpu::compute_harmonic_barrier<BarrierEvaluatorT>(d_force, d_virial, d_pos, d_params,
+ *                       global_box, evaluator, N, ntypes, block_size)   (/root/reference/src/HarmonicBarrierGPU.cuh:106-133,
+ *                       called from HarmonicBarrierGPU<T>::computeForces, HarmonicBarrierGPU.h:47-72)
+ * One thread per particle: wrap the position into the GLOBAL box (HarmonicBarrierGPU.cuh:76-78), evaluate
+ * PlanarBarrierEvaluator.h:36-48 (plane y = location + offset, pushes down) or SphericalBarrierEvaluator.h:36-51 (sphere
+ * r = location + offset, pushes inward), overwrite force.xyz and energy (.w). The virial is NOT computed and is zeroed
+ * (HarmonicBarrierGPU.cuh:130, HarmonicBarrier.h:176). d_params is the reference's per-type Scalar2 array {k, offset}
+ * (HarmonicBarrier.h:33-34,95-99). The evaluator's own validity test (Planar: lo.y <= location < hi.y; Spherical:
+ * location >= 0 and every nearest-plane distance >= 2 location; HarmonicBarrier.h:125-133) is made first and reported as
+ * AZB_ERR_BARRIER_INVALID, for which the reference throws "Barrier position is invalid". */
+#define AZB_ERR_BARRIER_INVALID 10004
+enum azb_barrier_geometry
+    {
+    AZB_BARRIER_PLANAR = 0,    /* "PlanarHarmonicBarrier" */
+    AZB_BARRIER_SPHERICAL = 1, /* "SphericalHarmonicBarrier" */
+    AZB_BARRIER_COUNT_ = 2
+    };
+typedef struct azb_barrier_args
+    {
+    void* d_force;        /* Scalar4[N], overwritten */
+    void* d_virial;       /* Scalar[6*virial_pitch], zeroed (may be NULL) */
+    size_t virial_pitch;
+    unsigned int N;
+    unsigned int ntypes;
+    const void* d_pos;    /* Scalar4[N]: x, y, z, type */
+    const void* d_params; /* Scalar2[ntypes]: k, offset */
+    azb_box global_box;
+    double location;      /* the Variant evaluated at this timestep */
+    unsigned int block_size;
+    } azb_barrier_args;
+AZB_API int azb_barrier_forces(int geometry, int scalar_bits, const azb_barrier_args* args, void* stream);
+
+/* ---- the step around the force path: hoomd.md.methods.ConstantVolume without a thermostat (velocity Verlet,
+ * what every reference test integrates with: test_pair.py:325-327, test_pair_dpd.py:31-32) and the neighbour-list rebuild
+ * trigger. HOOMD-blue itself is not under /root/reference; the update order follows TwoStepConstantVolume (recalled):
+ *   azb_nve_step_one   v += (dt/2) a;  x += dt v;  wrap x into the box by one image, counting images
+ *   azb_nve_step_two   F = sum of the force arrays (Integrator::computeNetForce);  a = F / m;  v += (dt/2) a
+ *                      optionally writes the net force / energy rows to d_net_force
+ *   azb_displacement_check  *d_flag |= 1 if any local particle moved farther than sqrt(max_disp_sq) from d_last_pos
+ *                      (NeighborList::distanceCheck: rebuild when a particle has moved r_buff / 2) */
+typedef struct azb_nve_args
+    {
+    void* d_pos;          /* Scalar4[N] */
+    void* d_vel;          /* Scalar4[N]: vx, vy, vz, mass */
+    void* d_accel;        /* Scalar4[N] (xyz used; 16/32-byte rows keep the traffic vectorised) */
+    int* d_image;         /* int[3N] x,y,z interleaved, or NULL */
+    unsigned int N;
+    azb_box box;          /* the box positions are wrapped into */
+    double deltaT;
+    const void* const* d_forces; /* HOST array of n_forces device pointers, Scalar4[N] each (step two) */
+    unsigned int n_forces;       /* <= 8 */
+    void* d_net_force;           /* Scalar4[N] or NULL (step two) */
+    } azb_nve_args;
+AZB_API int azb_nve_step_one(int scalar_bits, const azb_nve_args* args, void* stream);
+AZB_API int azb_nve_step_two(int scalar_bits, const azb_nve_args* args, void* stream);
+AZB_API int azb_displacement_check(int scalar_bits, const void* d_pos, const void* d_last_pos, unsigned int N, const azb_box* box,
+                                   double max_disp_sq, unsigned int* d_flag, void* stream);
+
 /* ---- ghost halo over peer memory (SURVEY.md §8 e; replaces HOOMD's CommunicatorGPU pack -> MPI -> unpack for ranks on one
  * NVLink/NVSwitch node). One kernel per step gathers every boundary row of every direction and field and stores it
  * straight into the neighbouring rank's particle arrays (behind its local particles, where HOOMD keeps ghosts), then

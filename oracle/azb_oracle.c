@@ -128,6 +128,15 @@ int azo_bond_forces(int potential, int scalar_bits, const azb_bond_args* a, cons
     return AZB_ERR_BAD_SCALAR;
     }
 
+int azo_barrier_forces(int geometry, int scalar_bits, const azb_barrier_args* a)
+    {
+    if (scalar_bits == 32)
+        return barrier_loop_f32(geometry, a);
+    if (scalar_bits == 64)
+        return barrier_loop_f64(geometry, a);
+    return AZB_ERR_BAD_SCALAR;
+    }
+
 /* neighbour list: see azb_oracle_nlist.h. *out_nlist is malloc'ed; release with azo_free. */
 int azo_nlist_build(int scalar_bits, const void* pos, unsigned int N, unsigned int n_max, const azb_box* box,
                     const double* r_list, unsigned int ntypes, const size_t* excl_head, const unsigned int* excl_list,

@@ -774,3 +774,106 @@ static int SUF(bond_loop)(int potential, const azb_bond_args* a, const void* par
         *flags = 1;
     return 0;
     }
+
+/* HarmonicBarrier<BarrierEvaluatorT>::computeForces (/root/reference/src/HarmonicBarrier.h:148-178): validity test of the
+ * barrier location (:125-133; PlanarBarrierEvaluator.h:51-56, SphericalBarrierEvaluator.h:54-60), then per particle: wrap
+ * the position into the global box by one image (z, y, x with tilt terms), evaluate PlanarBarrierEvaluator.h:36-48 or
+ * SphericalBarrierEvaluator.h:36-51; the virial is zeroed (:176). */
+static int SUF(barrier_loop)(int geometry, const azb_barrier_args* a)
+    {
+    const azb_box* b = &a->global_box;
+    const REAL Lx = (REAL)b->Lx, Ly = (REAL)b->Ly, Lz = (REAL)b->Lz, xy = (REAL)b->xy, xz = (REAL)b->xz, yz = (REAL)b->yz;
+    const REAL lox = -Lx / (REAL)2, loy = -Ly / (REAL)2, loz = -Lz / (REAL)2;
+    const REAL hix = lox + Lx, hiy = loy + Ly, hiz = loz + Lz;
+    const REAL loc = (REAL)a->location;
+    const SUF(real4)* pos = (const SUF(real4)*)a->d_pos;
+    const REAL* params = (const REAL*)a->d_params;
+    SUF(real4)* force = (SUF(real4)*)a->d_force;
+    if (geometry == AZB_BARRIER_PLANAR)
+        {
+        const REAL lo_y = loy + yz * loz, hi_y = hiy + yz * hiz; /* y of makeCoordinates(0,0,0) and (1,1,1) */
+        if (!(loc >= lo_y && loc < hi_y))
+            return AZB_ERR_BARRIER_INVALID;
+        }
+    else if (geometry == AZB_BARRIER_SPHERICAL)
+        {
+        const REAL term = xy * yz - xz;
+        const REAL dx = Lx / SQRT((REAL)1 + xy * xy + term * term), dy = Ly / SQRT((REAL)1 + yz * yz), dz = Lz;
+        const REAL two_R = (REAL)2 * loc;
+        if (!(loc >= (REAL)0 && dx >= two_R && dy >= two_R && dz >= two_R))
+            return AZB_ERR_BARRIER_INVALID;
+        }
+    else
+        return AZB_ERR_BAD_POTENTIAL;
+    for (unsigned int i = 0; i < a->N; ++i)
+        {
+        REAL x = pos[i].x, y = pos[i].y, z = pos[i].z;
+        const unsigned int type = (unsigned int)SUF(type_of)(pos[i].w);
+        const REAL k = params[2 * type], offset = params[2 * type + 1];
+        if (b->periodic[2])
+            {
+            if (z >= hiz)
+                {
+                z -= Lz;
+                y -= Lz * yz;
+                x -= Lz * xz;
+                }
+            else if (z < loz)
+                {
+                z += Lz;
+                y += Lz * yz;
+                x += Lz * xz;
+                }
+            }
+        if (b->periodic[1])
+            {
+            const REAL tilt_y = yz * z;
+            if (y >= hiy + tilt_y)
+                {
+                y -= Ly;
+                x -= Ly * xy;
+                }
+            else if (y < loy + tilt_y)
+                {
+                y += Ly;
+                x += Ly * xy;
+                }
+            }
+        if (b->periodic[0])
+            {
+            const REAL tilt_x = (xz - xy * yz) * z + xy * y;
+            if (x >= hix + tilt_x)
+                x -= Lx;
+            else if (x < lox + tilt_x)
+                x += Lx;
+            }
+        SUF(real4) f = {0, 0, 0, 0};
+        if (geometry == AZB_BARRIER_PLANAR)
+            {
+            const REAL dy = y - (loc + offset);
+            if (dy > (REAL)0)
+                {
+                f.y = -k * dy;
+                f.w = (REAL)-0.5 * f.y * dy;
+                }
+            }
+        else
+            {
+            const REAL r = SQRT(x * x + y * y + z * z);
+            const REAL dr = r - (loc + offset);
+            if (dr > (REAL)0)
+                {
+                const REAL k_dr = k * dr;
+                const REAL c = -(k_dr / r);
+                f.x = c * x;
+                f.y = c * y;
+                f.z = c * z;
+                f.w = (REAL)0.5 * k_dr * dr;
+                }
+            }
+        force[i] = f;
+        }
+    if (a->d_virial)
+        memset(a->d_virial, 0, sizeof(REAL) * 6 * a->virial_pitch);
+    return 0;
+    }

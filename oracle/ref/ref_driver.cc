@@ -17,6 +17,7 @@
 #include <stdexcept>
 #include <vector>
 
+#include "hoomd/BoxDim.h"
 #include "hoomd/HOOMDMath.h"
 #include "hoomd/RandomNumbers.h"
 #include "hoomd/VectorMath.h"
@@ -29,6 +30,8 @@
 #include "PairEvaluatorExpandedYukawa.h"
 #include "PairEvaluatorHertz.h"
 #include "PairEvaluatorPerturbedLennardJones.h"
+#include "PlanarBarrierEvaluator.h"
+#include "SphericalBarrierEvaluator.h"
 
 #include "azb200.h"
 
@@ -600,6 +603,39 @@ extern "C"
             {
             return AZB_ERR_BAD_ARGUMENT;
             }
+        return AZB_ERR_BAD_POTENTIAL;
+        }
+
+    // HarmonicBarrier<BarrierEvaluatorT>::computeForces (HarmonicBarrier.h:148-178) around the reference's evaluators:
+    // validity test (:125-133), wrap into the global box, evaluate, zero virial.
+    int AZREF(barrier_forces)(int geometry, const azb_barrier_args* a)
+        {
+        const azb_box& b = a->global_box;
+        const BoxDim box((Scalar)b.Lx, (Scalar)b.Ly, (Scalar)b.Lz, (Scalar)b.xy, (Scalar)b.xz, (Scalar)b.yz, b.periodic[0], b.periodic[1],
+                         b.periodic[2]);
+        const Scalar4* pos = (const Scalar4*)a->d_pos;
+        const Scalar* params = (const Scalar*)a->d_params;
+        Scalar4* force = (Scalar4*)a->d_force;
+        auto run = [&](const auto& evaluator) -> int
+        {
+            if (!evaluator.valid(box))
+                return AZB_ERR_BARRIER_INVALID;
+            for (unsigned int idx = 0; idx < a->N; ++idx)
+                {
+                Scalar3 p = make_scalar3(pos[idx].x, pos[idx].y, pos[idx].z);
+                const unsigned int type = type_of(pos[idx]);
+                int3 img = make_int3(0, 0, 0);
+                box.wrap(p, img);
+                force[idx] = evaluator(p, params[2 * type], params[2 * type + 1]);
+                }
+            if (a->d_virial)
+                std::memset(a->d_virial, 0, sizeof(Scalar) * 6 * a->virial_pitch);
+            return 0;
+        };
+        if (geometry == AZB_BARRIER_PLANAR)
+            return run(hoomd::azplugins::PlanarBarrierEvaluator((Scalar)a->location));
+        if (geometry == AZB_BARRIER_SPHERICAL)
+            return run(hoomd::azplugins::SphericalBarrierEvaluator((Scalar)a->location));
         return AZB_ERR_BAD_POTENTIAL;
         }
 

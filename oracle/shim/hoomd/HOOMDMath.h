@@ -2,7 +2,7 @@
 // reference's evaluator headers (/root/reference/src/*Evaluator*.h, included at PairEvaluator.h:13)
 // compile unmodified on the host. HOOMD-blue v5 itself is not vendored under /root/reference and is not
 // installed here; this file restates only what those headers use: Scalar, Scalar3/4, make_scalar3/4,
-// fast::{sqrt,rsqrt,exp,pow}. Written from the documented HOOMD v5 semantics, not copied.
+// fast::{sqrt,rsqrt,exp,pow}, Scalar * Scalar3. Written from the documented HOOMD v5 semantics, not copied.
 #ifndef AZB_ORACLE_SHIM_HOOMDMATH_H_
 #define AZB_ORACLE_SHIM_HOOMDMATH_H_
 
@@ -43,6 +43,16 @@ inline Scalar4 make_scalar4(Scalar x, Scalar y, Scalar z, Scalar w)
 inline Scalar dot(const Scalar3& a, const Scalar3& b)
     {
     return a.x * b.x + a.y * b.y + a.z * b.z;
+    }
+
+// the float3/double3 operators of HOOMDMath.h that the barrier evaluators use (SphericalBarrierEvaluator.h:47)
+inline Scalar3 operator*(const Scalar& a, const Scalar3& b)
+    {
+    return make_scalar3(a * b.x, a * b.y, a * b.z);
+    }
+inline Scalar3 operator*(const Scalar3& a, const Scalar& b)
+    {
+    return make_scalar3(a.x * b, a.y * b, a.z * b);
     }
 
 // host flavour of hoomd::fast (no device intrinsics on the CPU path)

@@ -43,6 +43,8 @@ def port():
             fn.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         lib.azo_bond_forces.restype = C.c_int
         lib.azo_bond_forces.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        lib.azo_barrier_forces.restype = C.c_int
+        lib.azo_barrier_forces.argtypes = [C.c_int, C.c_int, C.c_void_p]
         lib.azo_nlist_build.restype = C.c_int
         lib.azo_nlist_build.argtypes = [C.c_int, C.c_void_p, C.c_uint, C.c_uint, C.POINTER(_abi.Box), C.c_void_p, C.c_uint,
                                         C.c_void_p, C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p,
@@ -65,7 +67,8 @@ def ref():
             # PyDLL keeps the GIL: make_params / params_as_dict touch Python objects. One library per precision.
             dll = C.PyDLL(REF_PATHS[bits])
             p = f"azref{bits}_"
-            for name in ("pair_forces", "dpd_forces", "aniso_forces", "bond_forces", "dpd_alpha", "param_size", "make_params", "params_as_dict"):
+            for name in ("pair_forces", "dpd_forces", "aniso_forces", "bond_forces", "barrier_forces", "dpd_alpha", "param_size", "make_params",
+                         "params_as_dict"):
                 setattr(lib, p + name, getattr(dll, p + name))
             for name in ("pair_forces", "dpd_forces", "aniso_forces"):
                 fn = getattr(lib, p + name)
@@ -74,6 +77,9 @@ def ref():
             fn = getattr(lib, p + "bond_forces")
             fn.restype = C.c_int
             fn.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+            fn = getattr(lib, p + "barrier_forces")
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_int, C.c_void_p]
             fn = getattr(lib, p + "dpd_alpha")
             fn.restype = C.c_double
             fn.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_uint]
@@ -235,6 +241,27 @@ class HostSystem:
         assert rc == 0, rc
         self.flags = flags.value
         return self
+
+
+def barrier(geometry, box, position, typeid, params, location, bits, which="port"):
+    """HarmonicBarrier oracle: returns (rc, force[N,4], virial[6,N]); params = [(k, offset)] per type."""
+    ftype = scalar_dtype(bits)[0]
+    pos = pack_scalar4(np.asarray(position, dtype=np.float64), np.asarray(typeid), bits, True)
+    n = len(pos)
+    par = np.ascontiguousarray(params, dtype=ftype).reshape(-1, 2)
+    force = np.full((n, 4), np.nan, dtype=ftype)
+    virial = np.full((6, max(n, 1)), np.nan, dtype=ftype)
+    a = _abi.BarrierArgs()
+    a.d_force, a.d_virial, a.virial_pitch = force.ctypes.data, virial.ctypes.data, virial.shape[1]
+    a.N, a.ntypes = n, len(par)
+    a.d_pos, a.d_params = pos.ctypes.data, par.ctypes.data
+    a.global_box = box.as_abi()
+    a.location = float(location)
+    if which == "port":
+        rc = port().azo_barrier_forces(geometry, bits, C.addressof(a))
+    else:
+        rc = getattr(ref(), f"azref{bits}_barrier_forces")(geometry, C.addressof(a))
+    return rc, force, virial
 
 
 def ref_make_params(spec, d, bits):
