@@ -6,9 +6,10 @@
 // Pipeline (all on `stream`):
 //   1. cell index per particle (locals + ghosts)                      cell_index_kernel
 //   2. stable radix sort of (cell, particle index)                    cub::DeviceRadixSort (plumbing)
-//   3. cell start/end offsets + cell-ordered copy of the positions    cell_bounds_kernel
-//   4. count pass: one warp per local particle walks its <= 27 neighbouring cells; candidates are read from the
-//      cell-ordered copy (coalesced), tested against r_list^2(type_i, type_j) and the exclusion row        nlist_kernel<COUNT>
+//   3. cell offsets (empty cells included) + cell-ordered copy of the positions    cell_bounds_kernel
+//   4. count pass: one warp per local particle walks the 9 (y, z) rows of its 27 neighbouring cells — the three x-cells of
+//      a row are one contiguous range of the cell-ordered copy, so the 32 lanes stay busy even at 8 particles per cell —
+//      testing r_list^2(type_i, type_j) and the exclusion row                                              nlist_kernel<COUNT>
 //   5. exclusive scan of the (row_align-padded) counts -> head_list    cub::DeviceScan
 //   6. fill pass: same walk, warp-ballot compaction keeps rows in deterministic cell-traversal order      nlist_kernel<FILL>
 #include <cub/cub.cuh>
@@ -49,19 +50,23 @@ __global__ void cell_index_kernel(const typename vec4<S>::type* __restrict__ pos
     idx[i] = i;
     }
 
+// cell_begin[c] = first position in cell order whose cell is >= c (so cell c is [cell_begin[c], cell_begin[c+1]) and a run of
+// cells that are consecutive in memory — the x-neighbours of a cell — is ONE contiguous range, empty cells included)
 template<class S>
 __global__ void cell_bounds_kernel(const unsigned int* __restrict__ cell_sorted, const unsigned int* __restrict__ idx_sorted, unsigned int n_max,
                                    const typename vec4<S>::type* __restrict__ pos, typename vec4<S>::type* __restrict__ pos_sorted,
-                                   unsigned int* __restrict__ cell_start, unsigned int* __restrict__ cell_end)
+                                   unsigned int* __restrict__ cell_begin, unsigned int ncell)
     {
     const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_max)
         return;
     const unsigned int c = cell_sorted[s];
-    if (s == 0 || cell_sorted[s - 1] != c)
-        cell_start[c] = s;
-    if (s == n_max - 1 || cell_sorted[s + 1] != c)
-        cell_end[c] = s + 1;
+    const unsigned int prev = s ? cell_sorted[s - 1] + 1u : 0u;
+    for (unsigned int k = prev; k <= c; ++k) // empty unless s starts a cell; then also covers the empty cells before it
+        cell_begin[k] = s;
+    if (s == n_max - 1)
+        for (unsigned int k = c + 1u; k <= ncell; ++k)
+            cell_begin[k] = n_max;
     const auto p = ld4(pos + idx_sorted[s]);
     st4(pos_sorted + s, p.x, p.y, p.z, p.w);
     }
@@ -72,8 +77,7 @@ template<class S> struct NlistDev
     const typename vec4<S>::type* pos_sorted;
     const unsigned int* idx_sorted;
     const unsigned int* cell_of;
-    const unsigned int* cell_start;
-    const unsigned int* cell_end;
+    const unsigned int* cell_begin;
     const S* r_listsq;
     const size_t* excl_head;
     const unsigned int* excl_list;
@@ -86,7 +90,9 @@ template<class S> struct NlistDev
     unsigned int N, ntypes;
     };
 
-template<class S, bool FILL> __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
+// FAST: fully periodic orthorhombic box (straight-line minimum image); SINGLE: one particle type (r_list^2 is one number);
+// EXCL: an exclusion table is present
+template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
     {
     const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned int lane = threadIdx.x & 31u;
@@ -111,70 +117,130 @@ template<class S, bool FILL> __global__ void __launch_bounds__(128) nlist_kernel
         hi_o[d] = (per && a.grid.nc[d] < 2) ? 0 : 1;
         }
     size_t ex0 = 0, ex1 = 0;
-    if (a.excl_head)
+    if (EXCL)
         {
         ex0 = a.excl_head[i];
         ex1 = a.excl_head[i + 1];
         }
+    const S rl_single = SINGLE ? a.r_listsq[0] : S(0);
     unsigned int count = 0;
     unsigned int* row = FILL ? a.nlist + a.head_list[i] : nullptr;
     const size_t row_cap = FILL ? a.capacity - a.head_list[i] : 0;
 
-    for (int oz = lo_o[2]; oz <= hi_o[2]; ++oz)
+    // Lane r < 9 prepares the (y, z) row r = 3 (oz + 1) + (oy + 1) of the 27-cell neighbourhood: the cells x-1, x, x+1 of a row
+    // are consecutive in cell order, so a row is ONE range of the cell-ordered copy, or two where it wraps around the periodic
+    // boundary (visited x-1, x, x+1: the list's row order). All cell_begin loads of a particle are in flight together.
+    unsigned int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+    if (lane < 9u)
         {
-        int z = ci[2] + oz;
+        const int oz = (int)lane / 3 - 1, oy = (int)lane % 3 - 1;
+        bool ok = oz >= lo_o[2] && oz <= hi_o[2] && oy >= lo_o[1] && oy <= hi_o[1];
+        int z = ci[2] + oz, y = ci[1] + oy;
         if ((a.grid.periodic >> 2) & 1u)
-            z = (z + a.grid.nc[2]) % a.grid.nc[2];
-        else if (z < 0 || z >= a.grid.nc[2])
-            continue;
-        for (int oy = lo_o[1]; oy <= hi_o[1]; ++oy)
+            z += z < 0 ? a.grid.nc[2] : (z >= a.grid.nc[2] ? -a.grid.nc[2] : 0);
+        else
+            ok = ok && z >= 0 && z < a.grid.nc[2];
+        if ((a.grid.periodic >> 1) & 1u)
+            y += y < 0 ? a.grid.nc[1] : (y >= a.grid.nc[1] ? -a.grid.nc[1] : 0);
+        else
+            ok = ok && y >= 0 && y < a.grid.nc[1];
+        if (ok)
             {
-            int y = ci[1] + oy;
-            if ((a.grid.periodic >> 1) & 1u)
-                y = (y + a.grid.nc[1]) % a.grid.nc[1];
-            else if (y < 0 || y >= a.grid.nc[1])
-                continue;
-            for (int ox = lo_o[0]; ox <= hi_o[0]; ++ox)
+            const unsigned int rb = (unsigned int)((z * a.grid.nc[1] + y) * a.grid.nc[0]);
+            int xlo = ci[0] + lo_o[0], xhi = ci[0] + hi_o[0];
+            if (a.grid.periodic & 1u)
                 {
-                int x = ci[0] + ox;
-                if (a.grid.periodic & 1u)
-                    x = (x + a.grid.nc[0]) % a.grid.nc[0];
-                else if (x < 0 || x >= a.grid.nc[0])
-                    continue;
-                const unsigned int cc = (unsigned int)((z * a.grid.nc[1] + y) * a.grid.nc[0] + x);
-                const unsigned int s0 = a.cell_start[cc], s1 = a.cell_end[cc];
-                for (unsigned int base = s0; base < s1; base += 32)
+                if (xlo < 0)
                     {
-                    const unsigned int s = base + lane;
-                    bool take = false;
-                    unsigned int j = 0;
-                    if (s < s1)
-                        {
-                        j = a.idx_sorted[s];
-                        const auto pj = ld4(a.pos_sorted + s);
-                        S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                        min_image(a.box, dx, dy, dz);
-                        const S rl = a.r_listsq[trow + type_of(pj.w)];
-                        take = (j != i) && (rl > S(0)) && (dx * dx + dy * dy + dz * dz < rl);
-                        if (take)
-                            for (size_t e = ex0; e < ex1; ++e)
-                                if (a.excl_list[e] == j)
-                                    take = false;
-                        }
-                    const unsigned int m = __ballot_sync(0xffffffffu, take);
-                    if constexpr (FILL)
-                        {
-                        const unsigned int slot = count + __popc(m & ((1u << lane) - 1u));
-                        if (take && slot < row_cap)
-                            row[slot] = j;
-                        }
-                    count += __popc(m);
+                    a0 = a.cell_begin[rb + xlo + a.grid.nc[0]];
+                    a1 = a.cell_begin[rb + a.grid.nc[0]];
+                    b0 = a.cell_begin[rb];
+                    b1 = a.cell_begin[rb + xhi + 1];
                     }
+                else if (xhi >= a.grid.nc[0])
+                    {
+                    a0 = a.cell_begin[rb + xlo];
+                    a1 = a.cell_begin[rb + a.grid.nc[0]];
+                    b0 = a.cell_begin[rb];
+                    b1 = a.cell_begin[rb + xhi - a.grid.nc[0] + 1];
+                    }
+                else
+                    {
+                    a0 = a.cell_begin[rb + xlo];
+                    a1 = a.cell_begin[rb + xhi + 1];
+                    }
+                }
+            else
+                {
+                xlo = xlo < 0 ? 0 : xlo;
+                xhi = xhi >= a.grid.nc[0] ? a.grid.nc[0] - 1 : xhi;
+                a0 = a.cell_begin[rb + xlo];
+                a1 = a.cell_begin[rb + xhi + 1];
                 }
             }
         }
+    auto visit = [&](unsigned int s0, unsigned int s1)
+    {
+        for (unsigned int base = s0; base < s1; base += 32)
+            {
+            const unsigned int s = base + lane;
+            bool take = false;
+            unsigned int j = 0;
+            if (s < s1)
+                {
+                j = a.idx_sorted[s];
+                const auto pj = ld4(a.pos_sorted + s);
+                S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                if (FAST)
+                    min_image_ortho(a.box, dx, dy, dz);
+                else
+                    min_image(a.box, dx, dy, dz);
+                const S rl = SINGLE ? rl_single : a.r_listsq[trow + type_of(pj.w)];
+                take = (j != i) && (rl > S(0)) && (dx * dx + dy * dy + dz * dz < rl);
+                if (EXCL && take)
+                    for (size_t e = ex0; e < ex1; ++e)
+                        if (a.excl_list[e] == j)
+                            take = false;
+                }
+            const unsigned int m = __ballot_sync(0xffffffffu, take);
+            if constexpr (FILL)
+                {
+                const unsigned int slot = count + __popc(m & ((1u << lane) - 1u));
+                if (take && slot < row_cap)
+                    row[slot] = j;
+                }
+            count += __popc(m);
+            }
+    };
+#pragma unroll 1
+    for (int r = 0; r < 9; ++r)
+        {
+        visit(__shfl_sync(0xffffffffu, a0, r), __shfl_sync(0xffffffffu, a1, r));
+        visit(__shfl_sync(0xffffffffu, b0, r), __shfl_sync(0xffffffffu, b1, r));
+        }
     if (!FILL && lane == 0)
         a.n_neigh[i] = count;
+    }
+
+template<class S, bool FILL> static void launch_nlist_kernel(const NlistDev<S>& d, unsigned int grid, cudaStream_t stream)
+    {
+    const bool fast = d.box.flags == 7u, single = d.ntypes == 1, excl = d.excl_head != nullptr;
+#define AZB_NL(F, T, E) nlist_kernel<S, FILL, F, T, E><<<grid, 128, 0, stream>>>(d)
+    if (excl)
+        {
+        if (fast)
+            single ? AZB_NL(true, true, true) : AZB_NL(true, false, true);
+        else
+            single ? AZB_NL(false, true, true) : AZB_NL(false, false, true);
+        }
+    else
+        {
+        if (fast)
+            single ? AZB_NL(true, true, false) : AZB_NL(true, false, false);
+        else
+            single ? AZB_NL(false, true, false) : AZB_NL(false, false, false);
+        }
+#undef AZB_NL
     }
 
 struct PadTo
@@ -199,7 +265,7 @@ static size_t align_up(size_t x)
 
 struct Workspace
     {
-    unsigned int *cell, *idx, *cell_sorted, *idx_sorted, *cell_start, *cell_end;
+    unsigned int *cell, *idx, *cell_sorted, *idx_sorted, *cell_begin;
     void* pos_sorted;
     size_t* total;
     void* cub_tmp;
@@ -256,8 +322,7 @@ static Workspace carve(void* base, unsigned int n_max, size_t ncell, size_t scal
     w.idx = (unsigned int*)take(4 * n);
     w.cell_sorted = (unsigned int*)take(4 * n);
     w.idx_sorted = (unsigned int*)take(4 * n);
-    w.cell_start = (unsigned int*)take(4 * (ncell + 1));
-    w.cell_end = (unsigned int*)take(4 * (ncell + 1));
+    w.cell_begin = (unsigned int*)take(4 * (ncell + 2));
     w.pos_sorted = take(scalar4_bytes * n);
     w.total = (size_t*)take(sizeof(size_t));
     w.cub_tmp = take(cub_bytes);
@@ -297,18 +362,15 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
             ++bits;
         size_t tmp = w.cub_bytes;
         cub::DeviceRadixSort::SortPairs(w.cub_tmp, tmp, w.cell, w.cell_sorted, w.idx, w.idx_sorted, (int)a.n_max, 0, bits, stream);
-        cudaMemsetAsync(w.cell_start, 0, 4 * (ncell + 1), stream);
-        cudaMemsetAsync(w.cell_end, 0, 4 * (ncell + 1), stream);
-        cell_bounds_kernel<S><<<grd, blk, 0, stream>>>(w.cell_sorted, w.idx_sorted, a.n_max, (const s4*)a.d_pos, (s4*)w.pos_sorted, w.cell_start,
-                                                        w.cell_end);
+        cell_bounds_kernel<S><<<grd, blk, 0, stream>>>(w.cell_sorted, w.idx_sorted, a.n_max, (const s4*)a.d_pos, (s4*)w.pos_sorted, w.cell_begin,
+                                                        (unsigned int)ncell);
         }
     NlistDev<S> d;
     d.pos = (const s4*)a.d_pos;
     d.pos_sorted = (const s4*)w.pos_sorted;
     d.idx_sorted = w.idx_sorted;
     d.cell_of = w.cell;
-    d.cell_start = w.cell_start;
-    d.cell_end = w.cell_end;
+    d.cell_begin = w.cell_begin;
     d.r_listsq = (const S*)a.d_r_listsq;
     d.excl_head = a.d_excl_head;
     d.excl_list = a.d_excl_list;
@@ -324,7 +386,7 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     if (a.N)
         {
         const unsigned int grd = (a.N + 3) / 4;
-        nlist_kernel<S, false><<<grd, 128, 0, stream>>>(d);
+        launch_nlist_kernel<S, false>(d, grd, stream);
         thrust::transform_iterator<PadTo, const unsigned int*, size_t> it(a.d_n_neigh, PadTo {align});
         size_t tmp = w.cub_bytes;
         cub::DeviceScan::ExclusiveSum(w.cub_tmp, tmp, it, a.d_head_list, (int)a.N, stream);
@@ -354,8 +416,7 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     d.pos_sorted = (const s4*)w.pos_sorted;
     d.idx_sorted = w.idx_sorted;
     d.cell_of = w.cell;
-    d.cell_start = w.cell_start;
-    d.cell_end = w.cell_end;
+    d.cell_begin = w.cell_begin;
     d.r_listsq = (const S*)a.d_r_listsq;
     d.excl_head = a.d_excl_head;
     d.excl_list = a.d_excl_list;
@@ -368,7 +429,7 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     d.N = a.N;
     d.ntypes = a.ntypes;
     if (a.N)
-        nlist_kernel<S, true><<<(a.N + 3) / 4, 128, 0, stream>>>(d);
+        launch_nlist_kernel<S, true>(d, (a.N + 3) / 4, stream);
     return (int)cudaGetLastError();
     }
     } // namespace azb

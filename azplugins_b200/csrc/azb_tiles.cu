@@ -146,7 +146,9 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
     __syncthreads();
 
     // 4. list entry -> slot, stored in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD).
-    // The entries of a row are emitted in BANK-ROTATED order: bucket the row's slots by shared-memory bank group
+    // With group_width = 0 a slot row keeps the order of the list row. Otherwise (opt-in: it halves the shared-memory bank
+    // conflicts of the force kernels' neighbour reads, which round 1's kernels are not bound by, and doubles this step)
+    // the entries of a row are emitted in BANK-ROTATED order: bucket the row's slots by shared-memory bank group
     // (slot mod 8: the 16-byte Scalar4 of slot s lives in bank group s mod 8) and deal the buckets round-robin, starting
     // at bucket (particle * G) mod 8 for a kernel that walks rows with groups of G lanes. Emitted position e then holds
     // bank group (start + e) mod 8 while no bucket has run dry, so the 8 lanes of a quarter-warp — 8/G particles x G
@@ -160,6 +162,26 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         const size_t head = head_list[i];
         const size_t shead = AZB_SLOT_HEAD(head, i, W);
         const unsigned int nnp = (nn + M - 1u) / M * M;
+        if (G == 0u)
+            {
+            // plain order: slot row = list row
+            for (unsigned int e = lane; e < nnp; e += 32)
+                {
+                uint16_t v = 0;
+                if (e < nn)
+                    {
+                    const unsigned int j = nlist[head + e];
+                    unsigned int h = tile_hash(j, hshift);
+                    while (keys[h] != j)
+                        h = (h + 1u) & hmask;
+                    v = vals[h];
+                    }
+                const unsigned int r = e % M;
+                slots[shead + (e - r) + 4u * (r % W) + r / W] = v;
+                }
+            }
+        else
+            {
         // pass 1: bucket sizes
         unsigned int cnt[8];
 #pragma unroll
@@ -228,6 +250,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
             const unsigned int r = e % M;
             slots[shead + (e - r) + 4u * (r % W) + r / W] = 0;
             }
+            }
         // rows must be disjoint and ordered by particle for the padded layout to be collision-free
         if (lane == 0 && i + 1 < N && head_list[i + 1] < head + nn)
             atomicExch(status + 1, 2u);
@@ -244,7 +267,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         return AZB_ERR_BAD_ARGUMENT;
     const unsigned int ts = a->tile_size, ucap = a->uniq_capacity;
     const unsigned int W = a->lane_width;
-    const unsigned int G = a->group_width ? a->group_width : W;
+    const unsigned int G = a->group_width; // 0: rows keep the list's order
     if (!(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u))
         || !(W == 1 || W == 2 || W == 4 || W == 8 || W == 16) || G > 32 || (G & (G - 1u)))
         return AZB_ERR_BAD_ARGUMENT;

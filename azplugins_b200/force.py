@@ -142,7 +142,8 @@ class Pair(Force):
         return nl.tile_plan(st.N, self.tile_size, lane_width=self._slot_lane_width(nbar), group_width=self._group_width(nbar))
 
     def _group_width(self, nbar):
-        """Lanes per particle of the kernel that will walk the slot rows (0: same as the slot-row layout)."""
+        """Bank rotation of the slot rows (``azb_tile_build_args.group_width``): off. It halves the shared-memory bank conflicts
+        of the neighbour reads but the kernels are not bound by them, and it doubles the plan build."""
         return 0
 
     def _pair_value(self, store, a, b, default):
@@ -257,10 +258,6 @@ class DPDThermoPair(Pair):
     def _slot_lane_width(self, nbar):
         return 1  # the DPD queue kernels read slots one at a time in row order
 
-    def _group_width(self, nbar):
-        if self.threads_per_particle:
-            return self.threads_per_particle
-        return 1 if nbar <= 8 else (2 if nbar <= 16 else (4 if nbar <= 96 else (8 if nbar <= 256 else 16)))  # azb_dpd.cu's choice, clamped
 
     def _kT_at(self, timestep):
         return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)

@@ -103,9 +103,9 @@ typedef struct azb_box
 /* Tile plan (optional, azb_tiles_build below): a derived view of one neighbour list that lets the force kernels stage
  * neighbour data in shared memory. Particles [t*tile_size, (t+1)*tile_size) form tile t; d_uniq holds, per tile, the
  * ascending list of distinct particle indices appearing in its rows; d_slots holds, entry for entry, the position of
- * each neighbour inside its tile's list. A slot row holds the same neighbours as the list row, in bank-rotated order
- * (csrc/azb_tiles.cu: dealt round-robin over the 8 shared-memory bank groups, so that the lanes of a quarter-warp read 8
- * different bank groups at every step). Slot rows are laid out for the kernel that reads them: a group of W =
+ * each neighbour inside its tile's list. A slot row holds the same neighbours as the list row — in the same order, or
+ * (group_width > 0) in bank-rotated order (csrc/azb_tiles.cu: dealt round-robin over the 8 shared-memory bank groups, so
+ * that the lanes of a quarter-warp read 8 different bank groups at every step). Slot rows are laid out for the kernel that reads them: a group of W =
  * lane_width lanes walks a row in blocks of 4W entries, each lane fetching its four entries of a block with one 8-byte
  * load, and the lanes of a group touching consecutive list entries at the same time (consecutive entries are mostly
  * bank groups in sequence). So entry e = b*4W + u*W + l of particle i's (reordered) row is stored at
@@ -292,8 +292,8 @@ typedef struct azb_tile_build_args
     unsigned int tile_size;
     unsigned int uniq_capacity;
     unsigned int lane_width;         /* 1, 2, 4, 8 or 16 */
-    unsigned int group_width;        /* lanes per particle of the kernel that will walk the rows (bank rotation of the row
-                                        order); 0 = lane_width */
+    unsigned int group_width;        /* 0: slot rows keep the list's row order. G > 0: rows are re-ordered for a kernel that
+                                        walks them with groups of G lanes (bank rotation, see above) */
     unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
     unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
     uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */

@@ -20,12 +20,13 @@ def _list_on_device(n, rho, r_list, seed, shuffle=False):
     return hs, nl
 
 
+@pytest.mark.parametrize("rotate", [False, True])
 @pytest.mark.parametrize("lane_width", [1, 2, 4, 8, 16])
 @pytest.mark.parametrize("tile_size", [32, 64, 128, 256])
-def test_tile_plan_matches_numpy(tile_size, lane_width):
+def test_tile_plan_matches_numpy(tile_size, lane_width, rotate):
     n = 5000
     hs, nl = _list_on_device(n, 3.0, 1.4, 11)
-    plan = nl.tile_plan(n, tile_size, 2048, lane_width)
+    plan = nl.tile_plan(n, tile_size, 2048, lane_width, group_width=lane_width if rotate else 0)
     W, M = lane_width, 4 * lane_width
     A = max(M, 8)  # AZB_SLOT_ROW_ALIGN
     assert plan is not None and plan.tile_size == tile_size and plan.n_tiles == (n + tile_size - 1) // tile_size
@@ -45,9 +46,12 @@ def test_tile_plan_matches_numpy(tile_size, lane_width):
             e = np.arange((nn[i] + M - 1) // M * M)
             r = e % M
             stored = slots[sh + (e - r) + 4 * (r % W) + r // W]  # entry e of the row in the lane-transposed layout
-            # a slot row holds the row's neighbours, each exactly once, in bank-rotated order
-            assert np.array_equal(np.sort(want[stored[: nn[i]]]), np.sort(lst[head[i] : head[i] + nn[i]]))
             assert np.all(stored[nn[i] :] == 0)  # padding
+            if not rotate:
+                assert np.array_equal(want[stored[: nn[i]]], lst[head[i] : head[i] + nn[i]])  # slot -> the listed neighbour, in order
+                continue
+            # group_width > 0: the row's neighbours, each exactly once, in bank-rotated order
+            assert np.array_equal(np.sort(want[stored[: nn[i]]]), np.sort(lst[head[i] : head[i] + nn[i]]))
             # the deal: position e carries bank group (start + e) mod 8 until the first bucket runs dry
             if nn[i]:
                 groups = stored[: nn[i]] & 7
