@@ -233,14 +233,32 @@ __global__ void __launch_bounds__(256)
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
-    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
+    // (64 / sizeof(V4)) rows per thread in flight: the gather is two dependent loads per row
+    constexpr int B = 64 / sizeof(V4);
+    for (unsigned int s0 = threadIdx.x; s0 < U; s0 += B * blockDim.x)
         {
-        const unsigned int g = __ldg(uq + s);
-        s_pos[s] = ld4(a.pos + g);
-        const V4 q = ld4(d.orientation + g);
-        V4 n = q;
-        patch_director<S>(q, n.x, n.y, n.z);
-        s_dir[s] = n;
+        unsigned int g[B];
+        V4 pv[B], qv[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            g[u] = (s0 + u * blockDim.x < U) ? __ldg(uq + s0 + u * blockDim.x) : 0xffffffffu;
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                pv[u] = ld4(a.pos + g[u]);
+                qv[u] = ld4(d.orientation + g[u]);
+                }
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                const unsigned int s = s0 + u * blockDim.x;
+                s_pos[s] = pv[u];
+                V4 n = qv[u];
+                patch_director<S>(qv[u], n.x, n.y, n.z);
+                s_dir[s] = n;
+                }
         }
     for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
         {

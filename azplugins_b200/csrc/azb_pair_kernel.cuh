@@ -256,6 +256,32 @@ template<bool LAZY, class S> __device__ __forceinline__ S separation(const Box<S
 // Walk: blockDim / TPP groups, each taking tile_size / groups particles. A row is read in blocks of 4 TPP entries:
 // every lane fetches its four slots of a block with one 8-byte load (the next block's load is issued before the
 // current block is evaluated) and the lanes of a group visit consecutive list entries together (azb200.h, slot rows).
+// Stage rows src[uq[0..U)] of a tile into shared memory. The gather is two dependent loads per row (index, then row); eight
+// (four) rows per thread are kept in flight so a tile of <= 2048 distinct neighbours costs two (four) memory round trips, not
+// 2 * U / 256.
+template<class V4>
+__device__ __forceinline__ void stage_rows(V4* __restrict__ dst, const V4* __restrict__ src, const unsigned int* __restrict__ uq, const unsigned int U)
+    {
+    constexpr int B = 128 / sizeof(V4); // 32 registers of rows in flight: 8 float rows, 4 double rows
+    const unsigned int step = blockDim.x;
+    for (unsigned int base = threadIdx.x; base < U; base += B * step)
+        {
+        unsigned int j[B];
+        V4 v[B];
+#pragma unroll
+        for (int k = 0; k < B; ++k)
+            j[k] = (base + k * step < U) ? __ldg(uq + base + k * step) : 0xffffffffu;
+#pragma unroll
+        for (int k = 0; k < B; ++k)
+            if (j[k] != 0xffffffffu)
+                v[k] = ld4(src + j[k]);
+#pragma unroll
+        for (int k = 0; k < B; ++k)
+            if (j[k] != 0xffffffffu)
+                dst[base + k * step] = v[k];
+        }
+    }
+
 template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, const TilePlanDev plan,
                                                         const typename Pot::template Params<S>* __restrict__ params, const S wrap_sq)
@@ -272,8 +298,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
-    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
-        s_pos[s] = ld4(a.pos + __ldg(uq + s));
+    stage_rows(s_pos, a.pos, uq, U);
     for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
         {
         const S rc = a.rcutsq[t];

@@ -19,7 +19,7 @@ __device__ __forceinline__ float2 f2(float a, float b)
     }
 
 template<int SHIFT, bool VIRIAL, int TPP>
-__global__ void __launch_bounds__(256) plj_packed_tile_kernel(const PairArgsDev<float> a, const TilePlanDev plan,
+__global__ void __launch_bounds__(256, 4) plj_packed_tile_kernel(const PairArgsDev<float> a, const TilePlanDev plan,
                                                               const PerturbedLJ::Params<float>* __restrict__ params, const float wrap_sq)
     {
     extern __shared__ __align__(32) unsigned char smem_raw[];
@@ -28,8 +28,31 @@ __global__ void __launch_bounds__(256) plj_packed_tile_kernel(const PairArgsDev<
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
-    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
-        s_pos[s] = ld4(a.pos + __ldg(uq + s));
+    // the group's first particle: its row header and first slot packet do not depend on the staged tile, so their two memory
+    // round trips are started before the staging gather and hide behind it
+    constexpr unsigned int M = 4 * TPP;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    unsigned int nn_next = 0;
+    const uint2* row_next = nullptr;
+    float4 pi_next = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint2 pkt_next = make_uint2(0u, 0u);
+    auto load_header = [&](const unsigned int p)
+    {
+        const unsigned int idx = tile * plan.tile_size + p;
+        nn_next = 0;
+        if (p < plan.tile_size && idx < a.N)
+            {
+            nn_next = __ldg(a.n_neigh + idx);
+            row_next = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
+            pi_next = ld4(a.pos + idx);
+            if (nn_next)
+                pkt_next = __ldg(row_next);
+            }
+    };
+    load_header(gid);
+    stage_rows(s_pos, a.pos, uq, U);
     // one particle type: every thread derives the coefficients itself (same expressions as the generic kernel's table)
     const float rc = __ldg(a.rcutsq);
     const PerturbedLJ::Coeff<float> c = PerturbedLJ::make(params[0], rc, SHIFT == 1);
@@ -44,10 +67,6 @@ __global__ void __launch_bounds__(256) plj_packed_tile_kernel(const PairArgsDev<
     const float add_wca = c.wca_shift - c.e_shift, add_far = -c.e_shift;
     const float BIG = 1.0e30f;
 
-    constexpr unsigned int M = 4 * TPP;
-    const unsigned int groups = blockDim.x / TPP;
-    const unsigned int gid = threadIdx.x / TPP;
-    const unsigned int lane = threadIdx.x % TPP;
     for (unsigned int p = gid; p < plan.tile_size; p += groups)
         {
         const unsigned int idx = tile * plan.tile_size + p;
@@ -55,9 +74,9 @@ __global__ void __launch_bounds__(256) plj_packed_tile_kernel(const PairArgsDev<
         float2 fx = f2(0, 0), fy = fx, fz = fx, pe = fx, vxx = fx, vxy = fx, vxz = fx, vyy = fx, vyz = fx, vzz = fx;
         if (active)
             {
-            const unsigned int nn = __ldg(a.n_neigh + idx);
-            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
-            const float4 pi = ld4(a.pos + idx);
+            const unsigned int nn = nn_next;
+            const uint2* row = row_next;
+            const float4 pi = pi_next;
             const float2 pix = f2(pi.x, pi.x), piy = f2(pi.y, pi.y), piz = f2(pi.z, pi.z);
 
             auto visit2 = [&](const unsigned int sA, const unsigned int sB, const bool vA, const bool vB)
@@ -111,9 +130,8 @@ __global__ void __launch_bounds__(256) plj_packed_tile_kernel(const PairArgsDev<
 
             const unsigned int full = nn / M;
             const unsigned int nblk = (nn + M - 1u) / M;
-            uint2 next = make_uint2(0u, 0u);
-            if (nblk)
-                next = __ldg(row);
+            uint2 next = pkt_next;
+            load_header(p + groups); // the group's next particle, if the tile has more particles than the CTA has groups
             for (unsigned int b = 0; b < full; ++b)
                 {
                 const uint2 s4 = next;

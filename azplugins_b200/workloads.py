@@ -66,6 +66,24 @@ def lj_fluid(m=20, rho=0.8, seed=1001, jitter=0.15):
 PLJ_PARAMS = {("A", "A"): dict(epsilon=1.0, sigma=1.0, attraction_scale_factor=0.5)}
 
 
+def yukawa_dpd_fluid(n=8_000_000, rho=1.0, seed=5001, jitter=0.15, kT=1.0):
+    """C5: one system, two force objects on one neighbour list (ExpandedYukawa r_cut = 2.0 + DPDGeneralWeight r_cut = 1.0);
+    jittered FCC lattice at rho = 1.0, N = 4 m^3 nearest to n."""
+    rng = np.random.default_rng(seed)
+    m = max(2, round((n / 4) ** (1.0 / 3.0)))
+    box, pos = fcc_lattice(m, rho, jitter, rng)
+    order = spatial_sort(pos, box, cell=1.2)
+    pos = pos[order]
+    n = len(pos)
+    tag = np.random.default_rng(seed + 1).permutation(n).astype(np.uint32)
+    vel = np.random.default_rng(seed + 2).normal(scale=np.sqrt(kT), size=(n, 3))
+    return Snapshot(box, pos, types=["A"], velocity=vel, tag=tag)
+
+
+EY_PARAMS = {("A", "A"): dict(epsilon=1.0, kappa=1.0, delta=0.5)}
+C5_DPD_PARAMS = {("A", "A"): dict(A=25.0, gamma=4.5, s=2.0)}
+
+
 def patchy_fluid(m=80, rho=0.6, seed=4001):
     """C4a: TwoPatchMorse colloids, N = 4 m^3 (m = 80 -> 2 048 000), uniform random unit quaternions."""
     rng = np.random.default_rng(seed)

@@ -33,8 +33,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="dpd", choices=["dpd", "plj", "plj4m", "patchy", "melt"])
+    ap.add_argument("--workload", default="dpd", choices=["dpd", "plj", "plj4m", "patchy", "melt", "eydpd"])
     ap.add_argument("--n", type=int, default=0, help="override particle count (per GPU)")
+    ap.add_argument("--strong", action="store_true", help="strong scaling: the workload's particle count is the TOTAL, split over the GPUs")
     ap.add_argument("--bits", type=int, default=32, choices=[32, 64])
     ap.add_argument("--tpp", type=int, default=0)
     ap.add_argument("--block", type=int, default=0)
@@ -131,6 +132,22 @@ def make_workload(name, n_override, rank=0):
             return [f, q]
 
         return f"C3 bead-spring melt N={snap.N} (chains of 100) PerturbedLJ r_cut=3.0 + bond.Quartic", snap, setup, 0.4
+    if name == "eydpd":
+        n = n_override or 8_000_000
+        snap = W.yukawa_dpd_fluid(n=n, seed=5001 + 17 * rank)
+
+        def setup(nl):
+            d = pair.DPDGeneralWeight(nlist=nl, kT=1.0, default_r_cut=1.0)
+            d.dt = 0.01
+            for k, v in W.C5_DPD_PARAMS.items():
+                d.params[k] = v
+            y = pair.ExpandedYukawa(nlist=nl, default_r_cut=2.0)
+            for k, v in W.EY_PARAMS.items():
+                y.params[k] = v
+            return [d, y]
+
+        return (f"C5 DPDGeneralWeight r_cut=1.0 + ExpandedYukawa r_cut=2.0 on one neighbour list, N={snap.N} rho=1.0 buffer=0.4 "
+                "(roofline: the DPD kernel)"), snap, setup, 0.4
     raise ValueError(name)
 
 
@@ -248,6 +265,14 @@ def time_reference_cpu(workload, snap, bits, nl_arrays, seconds, steps=None, war
     elif workload == "patchy":
         par, rcsq, _, _ = tables(cases.SPEC_BY_API["TwoPatchMorse"], W.TPM_PARAMS, 1.6)
         step = lambda t: hs.aniso(par, rcsq, nthreads=cores, which=which)  # noqa: E731
+    elif workload == "eydpd":
+        par_d, rcsq_d, _, _ = tables(cases.SPEC_BY_API["DPDGeneralWeight"], W.C5_DPD_PARAMS, 1.0)
+        spec_y = cases.SPEC_BY_API["ExpandedYukawa"]
+        par_y, rcsq_y, ronsq_y, _ = tables(spec_y, W.EY_PARAMS, 2.0)
+
+        def step(t):
+            hs.dpd(par_d, rcsq_d, seed=42, timestep=t, dt=0.01, kT=1.0, nthreads=cores, which=which)
+            hs.pair(spec_y.potential_id, par_y, rcsq_y, ronsq_y, nthreads=cores, which=which)
     else:
         raise ValueError(workload)
     for t in range(warmup):
@@ -284,7 +309,7 @@ def run_reference(args):
     if rank != 0:
         return
     label, snap, _, buffer = make_workload(args.workload, args.n)
-    rc = {"dpd": 1.0, "plj": 3.0, "plj4m": 3.0, "melt": 3.0, "patchy": 1.6}[args.workload]
+    rc = {"dpd": 1.0, "plj": 3.0, "plj4m": 3.0, "melt": 3.0, "patchy": 1.6, "eydpd": 2.0}[args.workload]
     nl = oracle_nlist(snap, args.bits, rc + buffer)  # input preparation, not timed
     value, cores, kind, sec, k = time_reference_cpu(args.workload, snap, args.bits, nl, 0.0, steps=args.steps, warmup=args.warmup)
     line = {
@@ -320,7 +345,12 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     _abi.load()
 
-    label, snap, setup, buffer = make_workload(args.workload, args.n, rank)
+    n_per_gpu = args.n
+    if args.strong and world > 1:
+        # strong scaling: the total is fixed (the workload's default size, or --n), every rank takes 1/world of it
+        total = args.n or {"dpd": 1_000_188, "plj": 32_000, "plj4m": 4_000_000, "patchy": 2_048_000, "melt": 4_000_000, "eydpd": 8_000_000}[args.workload]
+        n_per_gpu = max(total // world, 1000)
+    label, snap, setup, buffer = make_workload(args.workload, n_per_gpu, rank)
     nl = nlist.Cell(buffer=buffer)
     forces = setup(nl)
     halo = None
@@ -340,8 +370,8 @@ def run_b200(args):
         snap.box = gbox
     st = az.State(snap, device=dev, scalar_bits=args.bits, seed=42)
     if world > 1:
-        kind = forces[0]._kind
-        fields = ("pos", "vel") if kind == _abi.KIND_DPD else (("pos", "orientation") if kind == _abi.KIND_ANISO else ("pos",))
+        kinds = {f._kind for f in forces}
+        fields = ("pos",) + (("vel",) if _abi.KIND_DPD in kinds else ()) + (("orientation",) if _abi.KIND_ANISO in kinds else ())
         halo = HaloExchange(dec, st, float(nl.r_list(st.types).max()), fields=fields)
     virial = not args.no_virial
     for f in forces:
@@ -440,7 +470,7 @@ def run_b200(args):
                  f"built in {plan.build_ms:.2f} ms per neighbour-list rebuild, outside the timed region like the list itself)")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
-        "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong" if (args.strong and world > 1) else "weak", "vs_baseline": None,
         "dtype": "f32" if args.bits == 32 else "f64", "data": "synthetic",
         "config": {"workload": label, "particles_per_gpu": st.N, "mean_neighbors": round(nbar, 2), "compute_virial": virial,
                    "threads_per_particle": args.tpp or "auto", "neighbor_list": "full, HOOMD layout, built on GPU (azb_nlist_*)",

@@ -241,6 +241,41 @@ def test_pair_c1_configuration():
             _check(f"C1/plj/{mode}/{bits}", f, hs, bits)
 
 
+def test_c5_two_forces_on_one_neighbour_list():
+    """BASELINE config 5 at test size: ExpandedYukawa (r_cut 2.0) and DPDGeneralWeight (r_cut 1.0) share one Cell list built for
+    the larger cutoff; each kernel applies its own cutoff to the shared rows (and its own tile plan of the same list)."""
+    import azplugins_b200 as az
+    from azplugins_b200 import nlist, pair, workloads
+
+    snap = workloads.yukawa_dpd_fluid(n=6000)
+    spec_d, spec_y = cases.SPEC_BY_API["DPDGeneralWeight"], cases.SPEC_BY_API["ExpandedYukawa"]
+    for bits in (32, 64):
+        st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
+        cell = nlist.Cell(buffer=0.4)
+        d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
+        d.dt = 0.01
+        d.params[("A", "A")] = workloads.C5_DPD_PARAMS[("A", "A")]
+        y = pair.ExpandedYukawa(nlist=cell, default_r_cut=2.0)
+        y.params[("A", "A")] = workloads.EY_PARAMS[("A", "A")]
+        d._attach(st)
+        y._attach(st)
+        d.compute(3)
+        y.compute(3)
+        assert cell.launches == 1 and float(cell.r_list(st.types)[0, 0]) == pytest.approx(2.4)
+        assert d._plan is not None and y._plan is not None and d._plan is not y._plan
+        arrays = (cell.n_neigh.cpu().numpy().view(np.uint32), cell.head_list.cpu().numpy().view(np.uint64), cell.nlist.cpu().numpy().view(np.uint32))
+        which = "ref" if O.have_ref() else "port"
+        for name, f, spec, params, rc in (("dpd", d, spec_d, workloads.C5_DPD_PARAMS, 1.0), ("yukawa", y, spec_y, workloads.EY_PARAMS, 2.0)):
+            par, rcsq, ronsq, _ = cases.pair_tables(spec, {(0, 0): params[("A", "A")]}, {(0, 0): rc}, 1, bits)
+            hs = O.HostSystem(snap.box, snap.position, snap.typeid, 1, bits, velocity=snap.velocity, tag=snap.tag)
+            hs.n_neigh, hs.head_list, hs.nlist = arrays
+            if name == "dpd":
+                hs.dpd(par, rcsq, seed=42, timestep=3, dt=0.01, kT=1.0, which=which, nthreads=4)
+            else:
+                hs.pair(spec.potential_id, par, rcsq, ronsq, which=which, nthreads=4)
+            _check(f"C5/{name}/{bits}", f, hs, bits)
+
+
 DPD_PARAMS = ({(0, 0): dict(A=25.0, gamma=4.5, s=2.0), (0, 1): dict(A=50.0, gamma=4.5, s=2.0), (1, 1): dict(A=25.0, gamma=4.5, s=2.0)},
               {(0, 0): 1.0, (0, 1): 1.0, (1, 1): 1.0})
 
