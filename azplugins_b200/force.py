@@ -10,6 +10,7 @@ There is no CPU path: a state that does not live on a CUDA device raises.
 
 import ctypes as C
 import itertools
+import os
 
 import numpy as np
 import torch
@@ -143,7 +144,10 @@ class Pair(Force):
 
     def _group_width(self, nbar):
         """Bank rotation of the slot rows (``azb_tile_build_args.group_width``): off. It halves the shared-memory bank conflicts
-        of the neighbour reads but the kernels are not bound by them, and it doubles the plan build."""
+        of the neighbour reads but the kernels are not bound by them, and it doubles the plan build. ``AZB_BANK_ROTATE=1``
+        turns it on for A/B measurements."""
+        if os.environ.get("AZB_BANK_ROTATE", "0") == "1":
+            return self._slot_lane_width(nbar)
         return 0
 
     def _pair_value(self, store, a, b, default):

@@ -1,6 +1,10 @@
 cd /root/repo; mkdir -p gpurun_out
-tr() { n=$1; shift; timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 10 --warmup 3 --no-cpu-baseline "$@" 2>> gpurun_out/r2b_err.log | tail -1 >> gpurun_out/r2b_bench.log; }
-tr 8 --workload eydpd
-tr 8 --workload eydpd --strong
-tr 8 --workload dpd --strong --n 8000000
-tr 8 --workload plj4m --strong
+run() { python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-extras "$@" 2>> gpurun_out/r2d_err.log | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$*', d['ms_per_step'], d['roofline']['kernel_ms'], d['value'], d['roofline']['frac'], d['e2e']['value'])" >> gpurun_out/r2d_sweep.log 2>&1; }
+run --workload plj4m
+AZB_BANK_ROTATE=1 run --workload plj4m
+run --workload plj4m
+AZB_BANK_ROTATE=1 run --workload plj4m
+AZB_BANK_ROTATE=1 run --workload melt
+run --workload melt
+AZB_BANK_ROTATE=1 run --workload patchy
+run --workload patchy
