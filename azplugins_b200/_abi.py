@@ -162,6 +162,7 @@ class NlistArgs(C.Structure):
 
 # every symbol include/azb200.h declares (tests check the library exports exactly these)
 EXPORTS = (
+    "azb_host_step",
     "azb_abi_version",
     "azb_param_size",
     "azb_param_align",
@@ -253,6 +254,41 @@ class HaloPushArgs(C.Structure):
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libazb200.so")
 
+class HostBuffer(C.Structure):
+    _fields_ = [("d_ptr", C.c_void_p), ("h_ptr", C.c_void_p), ("row_bytes", C.c_size_t)]
+
+
+class HostLaunch(C.Structure):
+    _fields_ = [("wait_chunk", C.c_uint), ("tile_begin", C.c_uint), ("tile_count", C.c_uint)]
+
+
+class HostOutRange(C.Structure):
+    _fields_ = [("after_launch", C.c_uint), ("row_lo", C.c_size_t), ("row_hi", C.c_size_t)]
+
+
+class HostStepArgs(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int),
+        ("potential", C.c_int),
+        ("scalar_bits", C.c_int),
+        ("force_args", C.c_void_p),
+        ("d_params", C.c_void_p),
+        ("n_inputs", C.c_uint),
+        ("n_outputs", C.c_uint),
+        ("inputs", HostBuffer * 4),
+        ("outputs", HostBuffer * 4),
+        ("n_in_chunks", C.c_uint),
+        ("in_edges", C.POINTER(C.c_size_t)),
+        ("n_launches", C.c_uint),
+        ("launches", C.POINTER(HostLaunch)),
+        ("n_outs", C.c_uint),
+        ("outs", C.POINTER(HostOutRange)),
+        ("stream", C.c_void_p),
+        ("stream_in", C.c_void_p),
+        ("stream_out", C.c_void_p),
+    ]
+
+
 _lib = None
 
 
@@ -309,6 +345,8 @@ def load():
     lib.azb_halo_wait.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_void_p]
     lib.azb_halo_signal.restype = C.c_int
     lib.azb_halo_signal.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
+    lib.azb_host_step.restype = C.c_int
+    lib.azb_host_step.argtypes = [C.POINTER(HostStepArgs)]
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

@@ -262,7 +262,6 @@ class DPDThermoPair(Pair):
     def _slot_lane_width(self, nbar):
         return 1  # the DPD queue kernels read slots one at a time in row order
 
-
     def _kT_at(self, timestep):
         return float(self.kT(timestep)) if callable(self.kT) else float(self.kT)
 

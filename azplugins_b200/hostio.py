@@ -5,15 +5,17 @@ orientations), give me the forces". With the arrays in pinned host memory the st
 overlapped instead of run back to back:
 
   H2D   the inputs are copied in ascending index chunks on a copy stream;
-  force the tile kernel is launched chunk of tiles by chunk of tiles (``azb_pair_args.tile_begin / tile_count``), each
-        launch waiting only for the input chunk that holds the highest particle index its tiles read (the tile plan knows
-        it: the last entry of each tile's ascending distinct-neighbour list). Chunks are launched in the order their
-        inputs complete — the tiles on the periodic boundary, whose neighbours sit at the far end of the index range, go
-        last;
-  D2H   each chunk's forces are copied back on a third stream while later chunks compute.
+  force one launch per input chunk, holding exactly the tiles whose inputs are complete once that chunk has arrived (the
+        tile plan knows the highest particle index a tile reads: the last entry of its ascending distinct-neighbour
+        list; ``azb_pair_args.d_tile_order`` + ``tile_begin / tile_count`` select them) — the tiles on the periodic
+        boundary, whose neighbours sit at the far end of the index range, fall into the last launch;
+  D2H   blocks of output rows are copied back on a third stream as soon as the last launch writing into them is done,
+        while later launches compute.
 
 Neighbour list, tile plan, tags and parameter tables stay resident between list rebuilds, as they do in HOOMD.
 """
+
+import ctypes as C
 
 import numpy as np
 import torch
@@ -56,7 +58,8 @@ class HostStep:
         return [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in self.outputs]
 
     def _make_schedule(self):
-        """Tile chunks, the input chunk each one has to wait for, and the launch order (by input arrival)."""
+        """Which tiles each launch holds (by the input chunk that completes their inputs), and which launch completes
+        each block of output rows."""
         f, st = self.force, self.force._state
         f.nlist.compute(st)
         plan = f._current_plan()
@@ -66,7 +69,6 @@ class HostStep:
         K = max(1, min(self.chunks, plan.n_tiles))
         n_rows = st.pos.shape[0]
         in_edges = np.linspace(0, n_rows, K + 1).astype(np.int64)
-        tile_edges = np.linspace(0, plan.n_tiles, K + 1).astype(np.int64)
         count = plan.uniq_count.cpu().numpy().astype(np.int64)
         # highest index a tile reads: its own last particle, or the last (largest) entry of its ascending uniq list
         last = torch.arange(plan.n_tiles, device=plan.uniq.device, dtype=torch.int64) * plan.uniq_capacity + torch.from_numpy(
@@ -75,24 +77,65 @@ class HostStep:
         hi = np.where(count > 0, hi, 0)
         own_hi = np.minimum((np.arange(plan.n_tiles) + 1) * plan.tile_size, st.N) - 1
         hi = np.maximum(hi, own_hi)
-        sched = []
-        for c in range(K):
-            tb, te = int(tile_edges[c]), int(tile_edges[c + 1])
-            if te <= tb:
-                continue
-            need = int(hi[tb:te].max())
-            wait_chunk = int(np.searchsorted(in_edges, need, side="right") - 1)
-            lo, up = tb * plan.tile_size, min(te * plan.tile_size, st.N)
-            sched.append((wait_chunk, tb, te - tb, lo, up))
-        sched.sort(key=lambda x: (x[0], x[1]))
-        # one argument struct per chunk, built once per plan: a step only patches the timestep into them
-        args = [f._build_args(0, tile_range=(tb, tn)) for _, tb, tn, _, _ in sched]
-        self._schedule = (in_edges, sched, args)
+        # a tile is ready when the input chunk holding the highest index it reads has arrived. Launch e holds exactly the
+        # tiles that become ready with chunk e (ascending tile index inside), through the launch-position -> tile map; tiles
+        # on the periodic boundary, whose neighbours sit at the far end of the index range, fall into the last launch.
+        ready = np.clip(np.searchsorted(in_edges, hi, side="right") - 1, 0, K - 1)
+        order = np.argsort(ready, kind="stable")
+        per_class = np.bincount(ready, minlength=K)
+        sched, launch_of_class, at = [], {}, 0
+        for e in range(K):
+            if per_class[e]:
+                launch_of_class[e] = len(sched)
+                sched.append((e, at, int(per_class[e])))
+                at += int(per_class[e])
+        # outputs go back in blocks of consecutive tiles, each after the last launch that writes into it
+        B = max(1, min(8 * K, plan.n_tiles))
+        tile_edges = np.linspace(0, plan.n_tiles, B + 1).astype(np.int64)
+        outs = []
+        for b in range(B):
+            tb, te = int(tile_edges[b]), int(tile_edges[b + 1])
+            if te > tb:
+                outs.append((launch_of_class[int(ready[tb:te].max())], tb * plan.tile_size, min(te * plan.tile_size, st.N)))
+        outs.sort(key=lambda x: (x[0], x[1]))
+        merged = []
+        for o in outs:  # neighbouring blocks finished by the same launch travel as one copy
+            if merged and merged[-1][0] == o[0] and merged[-1][2] == o[1]:
+                merged[-1] = (o[0], merged[-1][1], o[2])
+            else:
+                merged.append(o)
+        # the native call's tables, built once per plan: a step only patches the timestep and the host pointers
+        d_order = torch.from_numpy(order.astype(np.int32)).to(st.device)
+        whole = f._build_args(0, tile_order=d_order)
+        hs = _abi.HostStepArgs()
+        hs.kind = f._kind
+        hs.potential = f._spec.potential_id
+        hs.scalar_bits = st.scalar_bits
+        hs.force_args = C.addressof(whole)
+        hs.d_params = f._d_params.data_ptr()
+        hs.n_inputs, hs.n_outputs = len(self.inputs), len(self.outputs)
+        for k, t in enumerate(self.inputs):
+            hs.inputs[k].d_ptr, hs.inputs[k].row_bytes = t.data_ptr(), t.shape[1] * t.element_size()
+        for k, t in enumerate(self.outputs):
+            hs.outputs[k].d_ptr, hs.outputs[k].row_bytes = t.data_ptr(), t.shape[1] * t.element_size()
+        edges = (C.c_size_t * (K + 1))(*[int(e) for e in in_edges])
+        launches = (_abi.HostLaunch * len(sched))()
+        for k, (wait_chunk, tb, tn) in enumerate(sched):
+            launches[k].wait_chunk, launches[k].tile_begin, launches[k].tile_count = wait_chunk, tb, tn
+        out_ranges = (_abi.HostOutRange * len(merged))()
+        for k, (after, lo, up) in enumerate(merged):
+            out_ranges[k].after_launch, out_ranges[k].row_lo, out_ranges[k].row_hi = after, lo, up
+        hs.n_in_chunks, hs.in_edges = K, edges
+        hs.n_launches, hs.launches = len(sched), launches
+        hs.n_outs, hs.outs = len(merged), out_ranges
+        hs.stream_in, hs.stream_out = self.s_in.cuda_stream, self.s_out.cuda_stream
+        self._schedule = (hs, whole, (edges, launches, out_ranges, d_order), merged, sched)  # the ctypes objects must outlive the calls
         self._plan_id = id(plan)
 
     def run(self, timestep, host_in, host_out):
         """host_in / host_out: lists of pinned host tensors matching ``inputs`` / ``outputs``. Returns after the forces are
-        in ``host_out`` (the host consumes them every step)."""
+        in ``host_out`` (the host consumes them every step). With a tile plan this is ONE call into the C-ABI
+        (``azb_host_step``, csrc/azb_hostio.cu), which issues the chunked copies and the tile-range launches itself."""
         f = self.force
         dev = f._state.device
         cur = torch.cuda.current_stream(dev)
@@ -109,27 +152,12 @@ class HostStep:
                 dst.copy_(src, non_blocking=True)
             cur.synchronize()
             return
-        in_edges, sched, chunk_args = self._schedule
-        self.s_in.wait_stream(cur)
-        arrived = []
-        with torch.cuda.stream(self.s_in):
-            for c in range(len(in_edges) - 1):
-                lo, up = int(in_edges[c]), int(in_edges[c + 1])
-                for dst, src in zip(self.inputs, host_in):
-                    dst[lo:up].copy_(src[lo:up], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(self.s_in)
-                arrived.append(ev)
-        for (wait_chunk, tb, tn, lo, up), a in zip(sched, chunk_args):
-            cur.wait_event(arrived[wait_chunk])
-            f._set_timestep(a, timestep)
-            f._launch(a)
-            done = torch.cuda.Event()
-            done.record(cur)
-            self.s_out.wait_event(done)
-            with torch.cuda.stream(self.s_out):
-                for dst, src in zip(host_out, self.outputs):
-                    dst[lo:up].copy_(src[lo:up], non_blocking=True)
-        cur.wait_stream(self.s_in)
-        self.s_out.synchronize()
-        cur.synchronize()
+        hs, whole, _, _, sched = self._schedule
+        f._set_timestep(whole, timestep)
+        for k, t in enumerate(host_in):
+            hs.inputs[k].h_ptr = t.data_ptr()
+        for k, t in enumerate(host_out):
+            hs.outputs[k].h_ptr = t.data_ptr()
+        hs.stream = cur.cuda_stream
+        _abi.check(f._lib.azb_host_step(C.byref(hs)), "azb_host_step")
+        f.launches += len(sched)

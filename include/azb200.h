@@ -410,6 +410,62 @@ AZB_API int azb_halo_wait(const unsigned int* d_flags, unsigned int n, unsigned 
                           void* stream);
 AZB_API int azb_halo_signal(unsigned int* const* d_peer_flags, unsigned int n, unsigned int epoch, void* stream);
 
+/* ---- one force evaluation from HOST buffers, pipelined inside the call ----------------------------------------------------
+ * azb_host_step is what a host code that keeps its particle data in (pinned) host memory calls per timestep: "here are this
+ * step's positions (+ velocities / orientations), give me the forces". HOOMD's own GPU path keeps the arrays resident
+ * (GlobalArray, cf. /root/reference/src/HarmonicBarrierGPU.h:50-56); this entry is for callers on the CPU side of the
+ * boundary (hoomd CPU integrators driving a GPU force, the bench's end-to-end leg). The three legs overlap:
+ *   H2D   every input is copied in n_in_chunks ascending row ranges (in_edges) on stream_in;
+ *   force launch c evaluates launch positions [tile_begin, tile_begin + tile_count) of the tile plan (positions map to tiles
+ *         through force_args' d_tile_order, so a launch can hold exactly the tiles whose inputs are complete) as soon as
+ *         input chunk launches[c].wait_chunk has arrived — the caller knows from the plan which input rows a tile reads;
+ *   D2H   rows [row_lo, row_hi) of every output follow on stream_out once launch outs[k].after_launch has finished,
+ *         while later launches compute.
+ * force_args is the azb_pair_args / azb_dpd_args / azb_aniso_args of the whole evaluation (kind says which); its tiles must
+ * be set; tile_begin / tile_count are overwritten per launch on a private copy. Returns after every output row is in host
+ * memory. */
+typedef struct azb_host_buffer
+    {
+    void* d_ptr;      /* device array (a field of force_args points at it too) */
+    void* h_ptr;      /* host array, same layout; pinned memory if the copies are to overlap */
+    size_t row_bytes; /* bytes per particle row */
+    } azb_host_buffer;
+
+typedef struct azb_host_launch
+    {
+    unsigned int wait_chunk; /* index of the last input chunk this launch reads */
+    unsigned int tile_begin, tile_count;
+    } azb_host_launch;
+
+typedef struct azb_host_out_range
+    {
+    unsigned int after_launch; /* index into launches: the last launch that writes rows of this range */
+    size_t row_lo, row_hi;
+    } azb_host_out_range;
+
+typedef struct azb_host_step_args
+    {
+    int kind; /* AZB_KIND_PAIR, AZB_KIND_DPD or AZB_KIND_ANISO */
+    int potential;
+    int scalar_bits;
+    const void* force_args;
+    const void* d_params;
+    unsigned int n_inputs, n_outputs; /* <= 4 each */
+    azb_host_buffer inputs[4];
+    azb_host_buffer outputs[4];
+    unsigned int n_in_chunks;
+    const size_t* in_edges; /* host array [n_in_chunks + 1], ascending row indices */
+    unsigned int n_launches;
+    const azb_host_launch* launches; /* host array, in launch order */
+    unsigned int n_outs;
+    const azb_host_out_range* outs; /* host array, ascending after_launch */
+    void* stream;     /* compute stream */
+    void* stream_in;  /* H2D copies */
+    void* stream_out; /* D2H copies */
+    } azb_host_step_args;
+
+AZB_API int azb_host_step(const azb_host_step_args* args);
+
 #ifdef __cplusplus
 }
 #endif
