@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--tpp", type=int, default=0)
     ap.add_argument("--block", type=int, default=0)
     ap.add_argument("--no-tiles", action="store_true", help="gather neighbour data from global memory instead of per-tile shared-memory staging")
-    ap.add_argument("--tile-size", type=int, default=128)
+    ap.add_argument("--tile-size", type=int, default=0, help="particles per tile of the tile plan (0 = the force's own choice)")
     ap.add_argument("--no-virial", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
