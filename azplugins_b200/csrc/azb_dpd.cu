@@ -55,7 +55,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
             return bad;
         if (a.pair.ntypes > 255)
             return AZB_ERR_BAD_ARGUMENT; // the ring packs slot | type pair << 16
-        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + (size_t)(block / tpp) * (4 * tpp + 1) * sizeof(V4)
+        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + (size_t)(block / tpp) * (AZB_DPD_QMUL * tpp + 1) * sizeof(V4)
                             + T2 * sizeof(coeff_t);
         if (smem > AZB_MAX_SMEM)
             return AZB_ERR_BAD_ARGUMENT;
@@ -89,7 +89,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     const unsigned int block = pick_block(a.pair.block_size);
     const unsigned int per_block = block / tpp;
     const unsigned int grid = (a.pair.N + per_block - 1) / per_block;
-    const size_t smem = (size_t)(block / tpp) * (4 * tpp + 1) * (sizeof(V4) + sizeof(unsigned int)) + T2 * sizeof(coeff_t);
+    const size_t smem = (size_t)(block / tpp) * (AZB_DPD_QMUL * tpp + 1) * (sizeof(V4) + sizeof(unsigned int)) + T2 * sizeof(coeff_t);
     if (smem > AZB_MAX_SMEM)
         return AZB_ERR_BAD_ARGUMENT;
 #define AZB_LAUNCH_Q(TPP, FB, SG)                                                            \

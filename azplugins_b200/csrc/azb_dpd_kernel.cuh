@@ -23,6 +23,17 @@
 #include "azb_pair_kernel.cuh"
 #include "azb_rng.cuh"
 
+// ring capacity per group in units of TPP (power of two), and the minimum number of resident CTAs per SM asked of the
+// tile kernel; build-time switches for occupancy experiments
+#ifndef AZB_DPD_QMUL
+#define AZB_DPD_QMUL 4
+#endif
+#ifdef AZB_DPD_TILE_MINB
+#define AZB_DPD_TILE_BOUNDS __launch_bounds__(256, AZB_DPD_TILE_MINB)
+#else
+#define AZB_DPD_TILE_BOUNDS __launch_bounds__(256)
+#endif
+
 namespace azb
     {
 template<class S> struct DPDArgsDev
@@ -128,7 +139,7 @@ __device__ __forceinline__ void dpd_walk_row(const Src& src, const unsigned int 
     {
     typedef typename vec4<S>::type V4;
     typedef DPDThermo::Coeff<S> coeff_t;
-    constexpr unsigned int QCAP = 4 * TPP;
+    constexpr unsigned int QCAP = AZB_DPD_QMUL * TPP;
     constexpr unsigned int FULL = 0xffffffffu;
     const unsigned int lane = threadIdx.x % TPP;
     const unsigned int gshift = (threadIdx.x & 31u) & ~(unsigned int)(TPP - 1);
@@ -289,7 +300,7 @@ template<class S> struct TileSource
 // shared-memory footprint of the rings of a CTA: one ring of QCAP + 1 entries per group (+ the type-pair side ring)
 template<class S, int TPP> __host__ __device__ constexpr unsigned int dpd_ring_stride()
     {
-    return (4u * TPP + 1u) * (unsigned int)sizeof(typename vec4<S>::type);
+    return ((unsigned int)AZB_DPD_QMUL * TPP + 1u) * (unsigned int)sizeof(typename vec4<S>::type);
     }
 
 template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
@@ -298,7 +309,7 @@ __global__ void __launch_bounds__(256)
     {
     typedef DPDThermo::Coeff<S> coeff_t;
     typedef typename vec4<S>::type V4;
-    constexpr unsigned int QCAP = 4 * TPP;
+    constexpr unsigned int QCAP = AZB_DPD_QMUL * TPP;
     const PairArgsDev<S>& a = d.pair;
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const unsigned int T2 = a.ntypes * a.ntypes;
@@ -341,12 +352,12 @@ __global__ void __launch_bounds__(256)
 // One CTA per tile: stage pos/vel/tag of the tile's distinct neighbours (ascending indices -> coalesced runs; four
 // gathers per thread in flight), then every group walks tile_size / (blockDim / TPP) particles against the staged copy.
 template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
-__global__ void __launch_bounds__(256)
+__global__ void AZB_DPD_TILE_BOUNDS
     dpd_tile_kernel(const DPDArgsDev<S> d, const TilePlanDev plan, const DPDThermo::Params<S>* __restrict__ params, const S wrap_sq)
     {
     typedef DPDThermo::Coeff<S> coeff_t;
     typedef typename vec4<S>::type V4;
-    constexpr unsigned int QCAP = 4 * TPP;
+    constexpr unsigned int QCAP = AZB_DPD_QMUL * TPP;
     const PairArgsDev<S>& a = d.pair;
     extern __shared__ __align__(32) unsigned char smem_raw[];
     const unsigned int T2 = a.ntypes * a.ntypes;
