@@ -98,6 +98,56 @@ def patchy_fluid(m=80, rho=0.6, seed=4001):
 TPM_PARAMS = {("A", "A"): dict(M_d=1.8347, M_r=0.0302, r_eq=1.0043, omega=20.0, alpha=0.5, repulsion=True)}
 
 
+def hertz_mixture(m=80, rho=1.2, seed=4101):
+    """C4b: polydisperse soft spheres (pair.Hertz), N = 4 m^3 (m = 80 -> 2 048 000), four species of diameter
+    0.85 / 0.95 / 1.05 / 1.15 in equal numbers; the cutoff of a type pair is the mean of the two diameters."""
+    rng = np.random.default_rng(seed)
+    box, pos = fcc_lattice(m, rho, 0.15, rng)
+    order = spatial_sort(pos, box, cell=1.6)
+    pos = pos[order]
+    typeid = rng.integers(0, 4, size=len(pos))
+    return Snapshot(box, pos, typeid=typeid, types=["A", "B", "C", "D"])
+
+
+HERTZ_DIAMETERS = {"A": 0.85, "B": 0.95, "C": 1.05, "D": 1.15}
+HERTZ_EPSILON = 100.0
+
+
+def hertz_tables():
+    """(params, r_cut) per type pair of the polydisperse Hertz mixture."""
+    names = sorted(HERTZ_DIAMETERS)
+    par = {(a, b): dict(epsilon=HERTZ_EPSILON) for i, a in enumerate(names) for b in names[i:]}
+    rc = {(a, b): 0.5 * (HERTZ_DIAMETERS[a] + HERTZ_DIAMETERS[b]) for (a, b) in par}
+    return par, rc
+
+
+def colloid_mixture(m=75, rho=0.6, seed=4201, radius=1.5, spacing=5.0):
+    """C4b: colloids (type C, radius 1.5) on a simple cubic lattice of the given spacing in a solvent (type S, radius 0) on a
+    jittered FCC lattice at density rho; solvent particles closer than radius + 0.9 to a colloid centre are removed (the
+    colloid-solvent potential diverges at r = radius). m = 75 -> ~1.0 M particles (1.69 M lattice sites, 41 % of them inside
+    an exclusion zone)."""
+    rng = np.random.default_rng(seed)
+    box, pos = fcc_lattice(m, rho, 0.1, rng)
+    L = box.L
+    nc = np.maximum(1, np.floor(L / spacing)).astype(np.int64)
+    g = np.stack(np.meshgrid(*[np.arange(k) for k in nc], indexing="ij"), axis=-1).reshape(-1, 3)
+    cpos = (g + 0.5) * (L / nc) - L / 2
+    # distance of every solvent particle to its nearest lattice site (the sites form a regular grid: round to it)
+    rel = (pos + L / 2) / (L / nc) - 0.5
+    d = (rel - np.rint(rel)) * (L / nc)
+    keep = np.sum(d * d, axis=1) > (radius + 0.9) ** 2
+    pos = np.concatenate([pos[keep], cpos])
+    typeid = np.concatenate([np.zeros(int(keep.sum()), dtype=np.int64), np.ones(len(cpos), dtype=np.int64)])
+    order = spatial_sort(pos, box, cell=1.7)
+    return Snapshot(box, pos[order], typeid=typeid[order], types=["S", "C"])
+
+
+COLLOID_RADIUS = 1.5
+COLLOID_PARAMS = {("S", "S"): dict(A=144.0, a_1=0.0, a_2=0.0, sigma=1.0), ("C", "S"): dict(A=100.0, a_1=COLLOID_RADIUS, a_2=0.0, sigma=1.0),
+                  ("C", "C"): dict(A=40.0, a_1=COLLOID_RADIUS, a_2=COLLOID_RADIUS, sigma=1.0)}
+COLLOID_RCUT = {("S", "S"): 3.0, ("C", "S"): COLLOID_RADIUS + 3.0, ("C", "C"): 2 * COLLOID_RADIUS + 3.0}
+
+
 def polymer_melt(n_chains=40_000, chain_len=100, rho=0.85, seed=3001, bond_len=0.97, double_well_fraction=0.1):
     """C3: bead-spring melt. Chains are laid along a boustrophedon (snake) path through a simple-cubic lattice of spacing
     ~rho^(-1/3) compressed to the bond length along the path direction, so consecutive beads sit one bond apart and no

@@ -33,7 +33,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="dpd", choices=["dpd", "plj", "plj4m", "patchy", "melt", "eydpd"])
+    ap.add_argument("--workload", default="dpd", choices=["dpd", "plj", "plj4m", "patchy", "hertz", "colloid", "melt", "eydpd"])
     ap.add_argument("--n", type=int, default=0, help="override particle count (per GPU)")
     ap.add_argument("--strong", action="store_true", help="strong scaling: the workload's particle count is the TOTAL, split over the GPUs")
     ap.add_argument("--bits", type=int, default=32, choices=[32, 64])
@@ -118,6 +118,32 @@ def make_workload(name, n_override, rank=0):
             return [f]
 
         return f"C4a TwoPatchMorse N={snap.N} rho=0.6 r_cut=1.6 buffer=0.4", snap, setup, 0.4
+    if name == "hertz":
+        m = 80 if not n_override else max(2, round((n_override / 4) ** (1 / 3)))
+        snap = W.hertz_mixture(m=m, seed=4101 + 17 * rank)
+
+        def setup(nl):
+            f = pair.Hertz(nlist=nl, default_r_cut=0.0)
+            par, rc = W.hertz_tables()
+            for k, v in par.items():
+                f.params[k] = v
+                f.r_cut[k] = rc[k]
+            return [f]
+
+        return f"C4b polydisperse Hertz mixture N={snap.N} rho=1.2, 4 species, r_cut = mean diameter (0.85..1.15), buffer=0.4", snap, setup, 0.4
+    if name == "colloid":
+        m = 75 if not n_override else max(2, round((n_override / 4 / 0.59) ** (1 / 3)))
+        snap = W.colloid_mixture(m=m, seed=4201 + 17 * rank)
+
+        def setup(nl):
+            f = pair.Colloid(nlist=nl, default_r_cut=0.0)
+            for k, v in W.COLLOID_PARAMS.items():
+                f.params[k] = v
+                f.r_cut[k] = W.COLLOID_RCUT[k]
+            return [f]
+
+        return (f"C4b Colloid mixture N={snap.N}: colloids of radius 1.5 on a cubic lattice in a solvent at rho=0.6, "
+                "r_cut 3.0 / 4.5 / 6.0 (solvent-solvent / colloid-solvent / colloid-colloid), buffer=0.4"), snap, setup, 0.4
     if name == "melt":
         chains = 40_000 if not n_override else max(1, n_override // 100)
         snap = W.polymer_melt(n_chains=chains, seed=3001 + 17 * rank)
@@ -252,7 +278,7 @@ def time_reference_cpu(workload, snap, bits, nl_arrays, seconds, steps=None, war
 
     def tables(spec, pdict, rc):
         par_by = {(min(i, j), max(i, j)): pdict[tuple(sorted((names[i], names[j])))] for i in range(T) for j in range(T)}
-        rc_by = {k: rc for k in par_by}
+        rc_by = {(min(i, j), max(i, j)): (rc[tuple(sorted((names[i], names[j])))] if isinstance(rc, dict) else rc) for i in range(T) for j in range(T)}
         return cases.pair_tables(spec, par_by, rc_by, T, bits)
 
     if workload == "dpd":
@@ -261,6 +287,11 @@ def time_reference_cpu(workload, snap, bits, nl_arrays, seconds, steps=None, war
     elif workload in ("plj", "plj4m", "melt"):
         spec = cases.SPEC_BY_API["PerturbedLennardJones"]
         par, rcsq, ronsq, _ = tables(spec, W.PLJ_PARAMS, 3.0)
+        step = lambda t: hs.pair(spec.potential_id, par, rcsq, ronsq, nthreads=cores, which=which)  # noqa: E731
+    elif workload in ("hertz", "colloid"):
+        spec = cases.SPEC_BY_API["Hertz" if workload == "hertz" else "Colloid"]
+        pdict, rc = W.hertz_tables() if workload == "hertz" else (W.COLLOID_PARAMS, W.COLLOID_RCUT)
+        par, rcsq, ronsq, _ = tables(spec, pdict, rc)
         step = lambda t: hs.pair(spec.potential_id, par, rcsq, ronsq, nthreads=cores, which=which)  # noqa: E731
     elif workload == "patchy":
         par, rcsq, _, _ = tables(cases.SPEC_BY_API["TwoPatchMorse"], W.TPM_PARAMS, 1.6)
@@ -309,7 +340,14 @@ def run_reference(args):
     if rank != 0:
         return
     label, snap, _, buffer = make_workload(args.workload, args.n)
-    rc = {"dpd": 1.0, "plj": 3.0, "plj4m": 3.0, "melt": 3.0, "patchy": 1.6, "eydpd": 2.0}[args.workload]
+    if args.workload in ("hertz", "colloid"):
+        from azplugins_b200 import workloads as W
+
+        by_pair = W.hertz_tables()[1] if args.workload == "hertz" else W.COLLOID_RCUT
+        names = snap.types
+        rc = np.array([[by_pair[tuple(sorted((a, b)))] for b in names] for a in names])
+    else:
+        rc = {"dpd": 1.0, "plj": 3.0, "plj4m": 3.0, "melt": 3.0, "patchy": 1.6, "eydpd": 2.0}[args.workload]
     nl = oracle_nlist(snap, args.bits, rc + buffer)  # input preparation, not timed
     value, cores, kind, sec, k = time_reference_cpu(args.workload, snap, args.bits, nl, 0.0, steps=args.steps, warmup=args.warmup)
     line = {
@@ -348,7 +386,7 @@ def run_b200(args):
     n_per_gpu = args.n
     if args.strong and world > 1:
         # strong scaling: the total is fixed (the workload's default size, or --n), every rank takes 1/world of it
-        total = args.n or {"dpd": 1_000_188, "plj": 32_000, "plj4m": 4_000_000, "patchy": 2_048_000, "melt": 4_000_000, "eydpd": 8_000_000}[args.workload]
+        total = args.n or {"dpd": 1_000_188, "plj": 32_000, "plj4m": 4_000_000, "patchy": 2_048_000, "hertz": 2_048_000, "colloid": 1_000_000, "melt": 4_000_000, "eydpd": 8_000_000}[args.workload]
         n_per_gpu = max(total // world, 1000)
     label, snap, setup, buffer = make_workload(args.workload, n_per_gpu, rank)
     nl = nlist.Cell(buffer=buffer)

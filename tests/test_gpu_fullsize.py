@@ -32,8 +32,10 @@ SUM_TOL = 1e-5
 
 def _tables(spec, pdict, rc, names, bits=32):
     T = len(names)
-    par_by = {(min(i, j), max(i, j)): pdict[tuple(sorted((names[i], names[j])))] for i in range(T) for j in range(T)}
-    return cases.pair_tables(spec, par_by, {k: rc for k in par_by}, T, bits)
+    key = lambda i, j: tuple(sorted((names[i], names[j])))  # noqa: E731
+    par_by = {(min(i, j), max(i, j)): pdict[key(i, j)] for i in range(T) for j in range(T)}
+    rc_by = {(min(i, j), max(i, j)): (rc[key(i, j)] if isinstance(rc, dict) else rc) for i in range(T) for j in range(T)}
+    return cases.pair_tables(spec, par_by, rc_by, T, bits)
 
 
 def _owns_ambiguous_pair(hs, i, rcutsq, rel=2e-6):
@@ -138,6 +140,23 @@ def test_c4_patchy_full_size():
     worst_t, n_bad_t = _compare("c4/patchy/torque", f._torque[:, :3].cpu().numpy(), hs.torque[:, :3], hs, rcsq, 2e-3)
     _energy_sum(f, hs)
     bench_report("c4_patchy_2M", max(worst, worst_t), max(n_bad, n_bad_t))
+
+
+@pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("workload", ["hertz", "colloid"])
+def test_c4_mixture_full_size(workload):
+    """C4b: the polydisperse Hertz mixture (four species, per-pair cutoffs) and the Colloid mixture (three regimes of the
+    potential, cutoffs 3.0 / 4.5 / 6.0 on one neighbour list)."""
+    snap, f, hs = _run(workload)
+    assert snap.N >= 900_000
+    _third_law(f)
+    spec = cases.SPEC_BY_API["Hertz" if workload == "hertz" else "Colloid"]
+    pdict, rc = W.hertz_tables() if workload == "hertz" else (W.COLLOID_PARAMS, W.COLLOID_RCUT)
+    par, rcsq, ronsq, _ = _tables(spec, pdict, rc, snap.types)
+    hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=bench.os.cpu_count() or 1, which="ref")
+    worst, n_bad = _compare(f"c4/{workload}", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    _energy_sum(f, hs)
+    bench_report(f"c4_{workload}", worst, n_bad)
 
 
 _REPORT = {}
