@@ -20,7 +20,7 @@ template<class S, int SHIFT, bool VIRIAL> static int launch_aniso_variant(const 
             return AZB_ERR_BAD_ARGUMENT;
         TilePlanDev plan;
         unsigned int block = 0, grid = 0;
-        const int bad = make_tile_plan(a.pair, tpp, tpp, plan, block, grid);
+        const int bad = make_tile_plan(a.pair, tpp, tpp, plan, block, grid, 128u);
         if (bad)
             return bad;
         const size_t smem = (size_t)plan.smem_uniq * 2 * sizeof(typename vec4<S>::type) + T2t * (sizeof(coeff_t) + sizeof(S));

@@ -85,7 +85,7 @@ template<auto KERNEL> inline void ensure_smem(size_t bytes)
 // Validates a.tiles against the launch and picks the CTA size: blockDim / tpp groups, each walking
 // tile_size / groups particles (both powers of two, so every warp runs the same number of passes).
 inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int slot_lane_width, TilePlanDev& plan, unsigned int& block,
-                          unsigned int& grid)
+                          unsigned int& grid, unsigned int default_block = 256u)
     {
     const azb_tile_plan& t = *a.tiles;
     const unsigned int ts = t.tile_size;
@@ -104,7 +104,7 @@ inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int
     plan.uniq_count = t.d_uniq_count;
     plan.uniq = t.d_uniq;
     plan.slots = t.d_slots;
-    block = a.block_size ? pick_block(a.block_size) : 256u;
+    block = a.block_size ? pick_block(a.block_size) : default_block;
     if (block > ts * tpp)
         block = ts * tpp;
     if (block < 32 || (block & (block - 1u)))

@@ -144,10 +144,9 @@ class Pair(Force):
                             group_width=self._group_width(nbar))
 
     def _auto_tile_size(self, nbar):
-        """Long rows (LJ at r_cut = 3 sigma: ~130 entries) amortise the staging of a larger tile over more pair work
-        (4 M LJ: 0.953 ms at 256 against 0.975 ms at 128); short rows keep more CTAs resident with 128 (DPD 1 M: 0.233 ms at
-        128, 0.269 ms at 256)."""
-        return 256 if (nbar >= 100 and self._kind == _abi.KIND_PAIR) else 128
+        """128 particles per tile for every kernel family. (With 256-thread CTAs, 256-particle tiles were 2 % faster for
+        long rows; with the 128-thread CTAs the pair kernels now use, 128 wins: 4 M LJ 0.931 ms against 0.949 ms.)"""
+        return 128
 
     def _group_width(self, nbar):
         """Bank rotation of the slot rows (``azb_tile_build_args.group_width``): off. It halves the shared-memory bank conflicts
