@@ -23,6 +23,45 @@ import torch
 from . import _abi
 
 
+def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
+    """Pure host logic of the pipelined step (no device access; tests/test_hostio_schedule.py).
+
+    ``hi[t]`` is the highest particle index tile t reads, ``in_edges`` the ascending row boundaries of the K input chunks.
+    A tile is ready when the input chunk holding ``hi[t]`` has arrived: launch e holds exactly the tiles that become ready
+    with chunk e (ascending tile index inside) through the launch-position -> tile map ``order``; tiles on the periodic
+    boundary, whose neighbours sit at the far end of the index range, fall into the last launch. Outputs go back in blocks
+    of consecutive tiles, each after the last launch that writes into it; neighbouring blocks finished by the same launch
+    travel as one copy. Returns ``(order, launches, outs)`` with launches = [(wait_chunk, first_position, n_tiles)] and
+    outs = [(launch_index, row_lo, row_hi)] sorted by launch index."""
+    hi = np.asarray(hi, dtype=np.int64)
+    n_tiles = len(hi)
+    K = len(in_edges) - 1
+    ready = np.clip(np.searchsorted(in_edges, hi, side="right") - 1, 0, K - 1)
+    order = np.argsort(ready, kind="stable")
+    per_class = np.bincount(ready, minlength=K)
+    sched, launch_of_class, at = [], {}, 0
+    for e in range(K):
+        if per_class[e]:
+            launch_of_class[e] = len(sched)
+            sched.append((e, at, int(per_class[e])))
+            at += int(per_class[e])
+    B = max(1, min(out_blocks_per_chunk * K, n_tiles))
+    tile_edges = np.linspace(0, n_tiles, B + 1).astype(np.int64)
+    outs = []
+    for b in range(B):
+        tb, te = int(tile_edges[b]), int(tile_edges[b + 1])
+        if te > tb:
+            outs.append((launch_of_class[int(ready[tb:te].max())], tb * tile_size, min(te * tile_size, N)))
+    outs.sort(key=lambda x: (x[0], x[1]))
+    merged = []
+    for o in outs:
+        if merged and merged[-1][0] == o[0] and merged[-1][2] == o[1]:
+            merged[-1] = (o[0], merged[-1][1], o[2])
+        else:
+            merged.append(o)
+    return order, sched, merged
+
+
 class HostStep:
     def __init__(self, force, chunks=8):
         if force._state is None:
@@ -77,33 +116,7 @@ class HostStep:
         hi = np.where(count > 0, hi, 0)
         own_hi = np.minimum((np.arange(plan.n_tiles) + 1) * plan.tile_size, st.N) - 1
         hi = np.maximum(hi, own_hi)
-        # a tile is ready when the input chunk holding the highest index it reads has arrived. Launch e holds exactly the
-        # tiles that become ready with chunk e (ascending tile index inside), through the launch-position -> tile map; tiles
-        # on the periodic boundary, whose neighbours sit at the far end of the index range, fall into the last launch.
-        ready = np.clip(np.searchsorted(in_edges, hi, side="right") - 1, 0, K - 1)
-        order = np.argsort(ready, kind="stable")
-        per_class = np.bincount(ready, minlength=K)
-        sched, launch_of_class, at = [], {}, 0
-        for e in range(K):
-            if per_class[e]:
-                launch_of_class[e] = len(sched)
-                sched.append((e, at, int(per_class[e])))
-                at += int(per_class[e])
-        # outputs go back in blocks of consecutive tiles, each after the last launch that writes into it
-        B = max(1, min(8 * K, plan.n_tiles))
-        tile_edges = np.linspace(0, plan.n_tiles, B + 1).astype(np.int64)
-        outs = []
-        for b in range(B):
-            tb, te = int(tile_edges[b]), int(tile_edges[b + 1])
-            if te > tb:
-                outs.append((launch_of_class[int(ready[tb:te].max())], tb * plan.tile_size, min(te * plan.tile_size, st.N)))
-        outs.sort(key=lambda x: (x[0], x[1]))
-        merged = []
-        for o in outs:  # neighbouring blocks finished by the same launch travel as one copy
-            if merged and merged[-1][0] == o[0] and merged[-1][2] == o[1]:
-                merged[-1] = (o[0], merged[-1][1], o[2])
-            else:
-                merged.append(o)
+        order, sched, merged = plan_schedule(hi, in_edges, plan.tile_size, st.N)
         # the native call's tables, built once per plan: a step only patches the timestep and the host pointers
         d_order = torch.from_numpy(order.astype(np.int32)).to(st.device)
         whole = f._build_args(0, tile_order=d_order)
