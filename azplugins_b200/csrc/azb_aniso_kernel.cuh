@@ -233,6 +233,7 @@ __global__ void __launch_bounds__(256)
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    warm_tile_rows(a, plan, tile, TPP);
     // (64 / sizeof(V4)) rows per thread in flight: the gather is two dependent loads per row
     constexpr int B = 64 / sizeof(V4);
     for (unsigned int s0 = threadIdx.x; s0 < U; s0 += B * blockDim.x)

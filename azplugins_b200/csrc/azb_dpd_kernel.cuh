@@ -28,6 +28,9 @@
 #ifndef AZB_DPD_QMUL
 #define AZB_DPD_QMUL 4
 #endif
+#ifndef AZB_DPD_LIGHT2
+#define AZB_DPD_LIGHT2 true
+#endif
 #ifdef AZB_DPD_TILE_MINB
 #define AZB_DPD_TILE_BOUNDS __launch_bounds__(256, AZB_DPD_TILE_MINB)
 #else
@@ -130,7 +133,7 @@ __device__ __forceinline__ void dpd_pair(const V4& e, const V4& vi, const V4& vj
 // All 32 lanes of the warp must call this together (warp votes inside); lanes of idle groups pass nn = 0.
 // The ring of a group holds QCAP = 4 TPP entries at shared address q_addr (group rings are QCAP + 1 entries apart so
 // that equal positions of different groups fall into different banks).
-template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE, class Src>
+template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE, bool LIGHT2, class Src>
 __device__ __forceinline__ void dpd_walk_row(const Src& src, const unsigned int nn, const typename vec4<S>::type& pi,
                                              const typename vec4<S>::type& vi, const unsigned int tag_i, const unsigned int trow,
                                              const Box<S>& box, const S wrap_sq, const unsigned int coeff_addr,
@@ -151,47 +154,79 @@ __device__ __forceinline__ void dpd_walk_row(const Src& src, const unsigned int 
     const unsigned int nn_warp = __reduce_max_sync(FULL, nn); // longest row among the warp's groups
 
     unsigned int q_head = 0, q_tail = 0; // group-uniform ring state (monotonic; position = counter mod QCAP)
+    // LIGHT2: two list entries per lane and light visit (entries k and k + TPP) — two independent chains of
+    // load / distance / vote / push per lane, and half as many phase-switch votes. Ring order (hence the lane every
+    // in-range pair is evaluated on, hence the summation order) is the same as with one entry per visit.
+    constexpr unsigned int STEP = LIGHT2 ? 2u * TPP : (unsigned int)TPP;
     unsigned int k = lane;
-    unsigned int j = 0;
+    unsigned int j0 = 0, j1 = 0;
     if (k < nn)
-        j = src.index(k);
+        j0 = src.index(k);
+    if (LIGHT2 && k + TPP < nn)
+        j1 = src.index(k + TPP);
+    bool room = true; // warp-uniform: every ring can take another light visit
     for (;;)
         {
-        // ---- light phase: one list entry per lane, skipped by the whole warp once its longest row is exhausted.
-        // Straight-line: a lane without an entry re-reads the last valid index (or 0) and is masked out of the cutoff
-        // test.
-        if (k - lane < nn_warp)
+        // ---- light phase: skipped by the whole warp once its longest row is exhausted. Straight-line: a lane without
+        // an entry re-reads the last valid index (or 0) and is masked out of the cutoff test.
+        if (room && k - lane < nn_warp)
             {
-            const bool have = k < nn;
-            const unsigned int jc = j;
-            k += TPP;
+            const bool have0 = k < nn, have1 = LIGHT2 && (k + TPP < nn);
+            const unsigned int jc0 = j0, jc1 = j1;
+            k += STEP;
             if (k < nn)
-                j = src.index(k);
-            const V4 pj = src.pos(jc);
-            S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-            unsigned int tp = 0;
-            S rc = c0.rcutsq;
-            if (!SINGLE)
-                {
-                tp = trow + type_of(pj.w);
-                rc = lds_scalar(coeff_addr + tp * (unsigned int)sizeof(coeff_t) + 7u * (unsigned int)sizeof(S), S());
-                }
-            const bool in = have & (separation<FASTBOX>(box, wrap_sq, dx, dy, dz) < rc);
-            const unsigned int b = __ballot_sync(FULL, in);
+                j0 = src.index(k);
+            if (LIGHT2 && k + TPP < nn)
+                j1 = src.index(k + TPP);
+            auto light = [&](const unsigned int jc, const bool have, V4& entry, unsigned int& tp_out) -> bool
+            {
+                const V4 pj = src.pos(jc);
+                S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                unsigned int tp = 0;
+                S rc = c0.rcutsq;
+                if (!SINGLE)
+                    {
+                    tp = trow + type_of(pj.w);
+                    rc = lds_scalar(coeff_addr + tp * (unsigned int)sizeof(coeff_t) + 7u * (unsigned int)sizeof(S), S());
+                    }
+                const bool in = have & (separation<FASTBOX>(box, wrap_sq, dx, dy, dz) < rc);
+                entry = pack_entry<S>(dx, dy, dz, Src::pack(jc, tp));
+                tp_out = tp;
+                return in;
+            };
+            V4 e0, e1;
+            unsigned int tp0 = 0, tp1 = 0;
+            const bool in0 = light(jc0, have0, e0, tp0);
+            const bool in1 = LIGHT2 ? light(jc1, have1, e1, tp1) : false;
+            const unsigned int b0 = __ballot_sync(FULL, in0);
+            const unsigned int b1 = LIGHT2 ? __ballot_sync(FULL, in1) : 0u;
             // branch-free push: every lane computes its ring position, the store is predicated on `in`
-            const unsigned int at = (q_tail + __popc(b & ltmask)) & (QCAP - 1u);
-            sts4_if(in, q_addr + at * (unsigned int)sizeof(V4), pack_entry<S>(dx, dy, dz, Src::pack(jc, tp)));
+            const unsigned int n0 = __popc(b0 & gmask);
+            const unsigned int at0 = (q_tail + __popc(b0 & ltmask)) & (QCAP - 1u);
+            sts4_if(in0, q_addr + at0 * (unsigned int)sizeof(V4), e0);
             if (!SINGLE && !Src::kPackedTypePair)
-                sts32_if(in, qtp_addr + at * 4u, tp);
-            q_tail += __popc(b & gmask);
+                sts32_if(in0, qtp_addr + at0 * 4u, tp0);
+            if (LIGHT2)
+                {
+                const unsigned int at1 = (q_tail + n0 + __popc(b1 & ltmask)) & (QCAP - 1u);
+                sts4_if(in1, q_addr + at1 * (unsigned int)sizeof(V4), e1);
+                if (!SINGLE && !Src::kPackedTypePair)
+                    sts32_if(in1, qtp_addr + at1 * 4u, tp1);
+                }
+            q_tail += n0 + __popc(b1 & gmask);
             }
         const bool light_done = (k - lane) >= nn;
         const unsigned int cnt = q_tail - q_head;
         const bool all_ready = __all_sync(FULL, (cnt >= TPP) | light_done);
 
         // ---- heavy phase: one queued in-range pair per lane ------------------------------------------------------
-        if (all_ready || __any_sync(FULL, cnt > QCAP - TPP))
+        // A light visit pushes up to STEP entries per group, a heavy pass pops TPP: the next light visit needs
+        // cnt <= QCAP - STEP in every group, which one pop may not restore when STEP > TPP (`room`).
+        const unsigned int maxcnt = __reduce_max_sync(FULL, cnt);
+        room = true;
+        if (all_ready || maxcnt > QCAP - STEP)
             {
+            room = !LIGHT2 || (maxcnt <= QCAP - STEP + TPP);
             __syncwarp();
             if (lane < cnt)
                 {
@@ -341,7 +376,7 @@ __global__ void __launch_bounds__(256)
         }
     const coeff_t c0 = s_coeff[0]; // single-type systems keep the one coefficient set in registers
     PairAccum<S, VIRIAL> acc;
-    dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, smem_addr(s_coeff), c0,
+    dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE, false>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, smem_addr(s_coeff), c0,
                                                   smem_addr(s_queue) + gid * dpd_ring_stride<S, TPP>(),
                                                   smem_addr(s_qtp) + gid * (QCAP + 1u) * 4u, d.rk, acc);
     acc.template reduce<TPP>();
@@ -372,6 +407,27 @@ __global__ void AZB_DPD_TILE_BOUNDS
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    // Warm L2 with what the walk will read from global memory: the slot rows and the row headers / positions /
+    // velocities / tags of the tile's own particles. Nothing waits on a prefetch, so the requests overlap the staging
+    // gather below, and the walk's loads then cost an L2 hit instead of a DRAM round trip.
+    for (unsigned int p = threadIdx.x; p < plan.tile_size; p += blockDim.x)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        if (idx < a.N)
+            {
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const char* r = reinterpret_cast<const char*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, 1));
+            for (unsigned int off = 0; off < nn * 2u; off += 128u)
+                prefetch_l2(r + off);
+            if (p % 8u == 0u)
+                {
+                prefetch_l2(a.pos + idx);
+                prefetch_l2(d.vel + idx);
+                }
+            if (p % 32u == 0u)
+                prefetch_l2(d.tag + idx);
+            }
+        }
     for (unsigned int s0 = threadIdx.x; s0 < U; s0 += 4 * blockDim.x)
         {
         unsigned int g[4];
@@ -423,7 +479,7 @@ __global__ void AZB_DPD_TILE_BOUNDS
             trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
             }
         PairAccum<S, VIRIAL> acc;
-        dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, coeff_addr, c0, q_addr, 0u, d.rk, acc);
+        dpd_walk_row<S, VIRIAL, TPP, FASTBOX, SINGLE, AZB_DPD_LIGHT2>(src, nn, pi, vi, tag_i, trow, a.box, wrap_sq, coeff_addr, c0, q_addr, 0u, d.rk, acc);
         acc.template reduce<TPP>();
         if (active && threadIdx.x % TPP == 0)
             acc.store(a, idx);

@@ -43,6 +43,12 @@ __device__ __forceinline__ void st4(vec4<double>::type* p, double x, double y, d
     asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(x), "d"(y), "d"(z), "d"(w) : "memory");
     }
 
+// request a 128-byte line into L2 without a destination register (nothing waits on it)
+__device__ __forceinline__ void prefetch_l2(const void* p)
+    {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    }
+
 // ---- explicit shared-memory accesses at 32-bit shared addresses -----------------------------------------------------
 // (the address stays a plain register add instead of a generic-pointer reconstruction per access)
 __device__ __forceinline__ unsigned int smem_addr(const void* p)

@@ -259,6 +259,27 @@ template<bool LAZY, class S> __device__ __forceinline__ S separation(const Box<S
 // Stage rows src[uq[0..U)] of a tile into shared memory. The gather is two dependent loads per row (index, then row); eight
 // (four) rows per thread are kept in flight so a tile of <= 2048 distinct neighbours costs two (four) memory round trips, not
 // 2 * U / 256.
+// Warm L2 with the slot rows of a tile (the largest stream the walk reads from global memory: 2 B per list entry) and the
+// positions of its own particles. Nothing waits on a prefetch, so the requests overlap the staging gather, and the walk's
+// packet loads then cost an L2 hit instead of a DRAM round trip. W = lanes per particle of the slot-row layout.
+template<class S>
+__device__ __forceinline__ void warm_tile_rows(const PairArgsDev<S>& a, const TilePlanDev& plan, const unsigned int tile, const unsigned int W)
+    {
+    for (unsigned int p = threadIdx.x; p < plan.tile_size; p += blockDim.x)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        if (idx < a.N)
+            {
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const char* r = reinterpret_cast<const char*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, W));
+            for (unsigned int off = 0; off < nn * 2u; off += 128u)
+                prefetch_l2(r + off);
+            if (p % (128u / (unsigned int)sizeof(typename vec4<S>::type)) == 0u)
+                prefetch_l2(a.pos + idx);
+            }
+        }
+    }
+
 template<class V4>
 __device__ __forceinline__ void stage_rows(V4* __restrict__ dst, const V4* __restrict__ src, const unsigned int* __restrict__ uq, const unsigned int U)
     {
@@ -298,6 +319,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    warm_tile_rows(a, plan, tile, TPP);
     stage_rows(s_pos, a.pos, uq, U);
     for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
         {

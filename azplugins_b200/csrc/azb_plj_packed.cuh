@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(256, 4) plj_packed_tile_kernel(const PairArgsD
             }
     };
     load_header(gid);
+    warm_tile_rows(a, plan, tile, TPP);
     stage_rows(s_pos, a.pos, uq, U);
     // one particle type: every thread derives the coefficients itself (same expressions as the generic kernel's table)
     const float rc = __ldg(a.rcutsq);
