@@ -8,7 +8,7 @@ substituted for it: if it is missing, importing a force class fails loudly.
 import ctypes as C
 import os
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 ERR_BAD_POTENTIAL = 10001
 ERR_BAD_SCALAR = 10002
@@ -266,6 +266,10 @@ class HostOutRange(C.Structure):
     _fields_ = [("after_launch", C.c_uint), ("row_lo", C.c_size_t), ("row_hi", C.c_size_t)]
 
 
+class HostForce(C.Structure):
+    _fields_ = [("kind", C.c_int), ("potential", C.c_int), ("force_args", C.c_void_p), ("d_params", C.c_void_p)]
+
+
 class HostStepArgs(C.Structure):
     _fields_ = [
         ("kind", C.c_int),
@@ -275,8 +279,8 @@ class HostStepArgs(C.Structure):
         ("d_params", C.c_void_p),
         ("n_inputs", C.c_uint),
         ("n_outputs", C.c_uint),
-        ("inputs", HostBuffer * 4),
-        ("outputs", HostBuffer * 4),
+        ("inputs", HostBuffer * 8),
+        ("outputs", HostBuffer * 8),
         ("n_in_chunks", C.c_uint),
         ("in_edges", C.POINTER(C.c_size_t)),
         ("n_launches", C.c_uint),
@@ -286,6 +290,8 @@ class HostStepArgs(C.Structure):
         ("stream", C.c_void_p),
         ("stream_in", C.c_void_p),
         ("stream_out", C.c_void_p),
+        ("n_more", C.c_uint),
+        ("more", C.POINTER(HostForce)),
     ]
 
 
@@ -347,6 +353,8 @@ def load():
     lib.azb_halo_signal.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
     lib.azb_host_step.restype = C.c_int
     lib.azb_host_step.argtypes = [C.POINTER(HostStepArgs)]
+    lib.azb_host_step_release.restype = None
+    lib.azb_host_step_release.argtypes = []
     if lib.azb_abi_version() != ABI_VERSION:
         raise ImportError("libazb200.so ABI version mismatch")
     _lib = lib

@@ -33,12 +33,12 @@ template<class S, int SHIFT, bool VIRIAL> static int launch_aniso_variant(const 
         {                                                                                                                      \
         if (lazy)                                                                                                              \
             {                                                                                                                  \
-            ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, true>>(smem);                                                 \
+            if (const int e_ = ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, true>>(smem)) return e_;                                                 \
             aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, true><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq);  \
             }                                                                                                                  \
         else                                                                                                                   \
             {                                                                                                                  \
-            ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, false>>(smem);                                                \
+            if (const int e_ = ensure_smem<aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, false>>(smem)) return e_;                                                \
             aniso_tile_kernel<S, SHIFT, VIRIAL, TPP, false><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
             }                                                                                                                  \
         } while (0)

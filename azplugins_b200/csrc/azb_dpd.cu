@@ -62,7 +62,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
 #define AZB_LAUNCH_T(TPP, FB, SG)                                                            \
     do                                                                                       \
         {                                                                                    \
-        ensure_smem<dpd_tile_kernel<S, VIRIAL, TPP, FB, SG>>(smem);                          \
+        if (const int e_ = ensure_smem<dpd_tile_kernel<S, VIRIAL, TPP, FB, SG>>(smem)) return e_;                          \
         dpd_tile_kernel<S, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
         } while (0)
         switch (tpp)
@@ -95,7 +95,7 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
 #define AZB_LAUNCH_Q(TPP, FB, SG)                                                            \
     do                                                                                       \
         {                                                                                    \
-        ensure_smem<dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG>>(smem);                       \
+        if (const int e_ = ensure_smem<dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG>>(smem)) return e_;                       \
         dpd_force_kernel_q<S, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, (const param_t*)d_params, wrap_sq); \
         } while (0)
 #define AZB_CALL(TPP) AZB_BY_FLAVOUR(AZB_LAUNCH_Q, TPP)

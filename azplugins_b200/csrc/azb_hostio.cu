@@ -27,9 +27,69 @@ struct EventPool
             }
         return ev[i];
         }
+    void release()
+        {
+        for (cudaEvent_t e : ev)
+            cudaEventDestroy(e);
+        ev.clear();
+        }
+    ~EventPool()
+        {
+        // thread exit: the events go with the thread (a context torn down earlier makes the destroy a harmless error)
+        release();
+        }
     };
 thread_local EventPool g_pool;
 
+// One force object of the step: a private copy of its argument struct (tile_begin / tile_count change per launch).
+struct ForceCall
+    {
+    int kind = 0, potential = 0;
+    const void* d_params = nullptr;
+    azb_pair_args pa;
+    azb_dpd_args da;
+    azb_aniso_args aa;
+    azb_pair_args* range = nullptr;
+    int init(int kind_, int potential_, const void* force_args, const void* d_params_)
+        {
+        kind = kind_;
+        potential = potential_;
+        d_params = d_params_;
+        if (!force_args)
+            return AZB_ERR_BAD_ARGUMENT;
+        if (kind == AZB_KIND_PAIR)
+            {
+            pa = *(const azb_pair_args*)force_args;
+            range = &pa;
+            }
+        else if (kind == AZB_KIND_DPD)
+            {
+            da = *(const azb_dpd_args*)force_args;
+            range = &da.pair;
+            }
+        else if (kind == AZB_KIND_ANISO)
+            {
+            aa = *(const azb_aniso_args*)force_args;
+            range = &aa.pair;
+            }
+        else
+            return AZB_ERR_BAD_ARGUMENT;
+        return range->tiles ? 0 : AZB_ERR_BAD_ARGUMENT;
+        }
+    int launch(int scalar_bits, unsigned int tile_begin, unsigned int tile_count, cudaStream_t s)
+        {
+        range->tile_begin = tile_begin;
+        range->tile_count = tile_count;
+        if (kind == AZB_KIND_PAIR)
+            return azb_pair_forces(potential, scalar_bits, &pa, d_params, s);
+        if (kind == AZB_KIND_DPD)
+            return azb_dpd_forces(potential, scalar_bits, &da, d_params, s);
+        return azb_aniso_forces(potential, scalar_bits, &aa, d_params, s);
+        }
+    };
+
+int issue(const azb_host_step_args* a, std::vector<ForceCall>& calls, cudaStream_t cur, cudaStream_t s_in, cudaStream_t s_out)
+    {
 #define AZB_TRY(expr)                 \
     do                                \
         {                             \
@@ -37,40 +97,6 @@ thread_local EventPool g_pool;
         if (_e != 0)                  \
             return _e;                \
         } while (0)
-    } // namespace
-
-extern "C" AZB_API int azb_host_step(const azb_host_step_args* a)
-    {
-    if (!a || !a->force_args || !a->in_edges || !a->launches || (a->n_outs && !a->outs) || a->n_inputs > 4 || a->n_outputs > 4 || a->n_in_chunks == 0)
-        return AZB_ERR_BAD_ARGUMENT;
-    if (a->kind != AZB_KIND_PAIR && a->kind != AZB_KIND_DPD && a->kind != AZB_KIND_ANISO)
-        return AZB_ERR_BAD_ARGUMENT;
-    cudaStream_t cur = (cudaStream_t)a->stream, s_in = (cudaStream_t)a->stream_in, s_out = (cudaStream_t)a->stream_out;
-    // private copies of the argument struct: tile_begin / tile_count change per chunk
-    azb_pair_args pa;
-    azb_dpd_args da;
-    azb_aniso_args aa;
-    azb_pair_args* range = nullptr;
-    if (a->kind == AZB_KIND_PAIR)
-        {
-        pa = *(const azb_pair_args*)a->force_args;
-        range = &pa;
-        }
-    else if (a->kind == AZB_KIND_DPD)
-        {
-        da = *(const azb_dpd_args*)a->force_args;
-        range = &da.pair;
-        }
-    else
-        {
-        aa = *(const azb_aniso_args*)a->force_args;
-        range = &aa.pair;
-        }
-    if (!range->tiles)
-        return AZB_ERR_BAD_ARGUMENT;
-
-    static const bool trace = std::getenv("AZB_TRACE_HOST_STEP") != nullptr; // prints how long the host spent issuing
-    const auto t_begin = std::chrono::steady_clock::now();
     const size_t n_ev = (size_t)a->n_in_chunks + a->n_launches + 1;
     if (!g_pool.get(n_ev))
         return (int)cudaGetLastError();
@@ -101,14 +127,8 @@ extern "C" AZB_API int azb_host_step(const azb_host_step_args* a)
         if (ln.tile_count)
             {
             AZB_TRY(cudaStreamWaitEvent(cur, g_pool.get(ln.wait_chunk), 0));
-            range->tile_begin = ln.tile_begin;
-            range->tile_count = ln.tile_count;
-            if (a->kind == AZB_KIND_PAIR)
-                AZB_TRY(azb_pair_forces(a->potential, a->scalar_bits, &pa, a->d_params, cur));
-            else if (a->kind == AZB_KIND_DPD)
-                AZB_TRY(azb_dpd_forces(a->potential, a->scalar_bits, &da, a->d_params, cur));
-            else
-                AZB_TRY(azb_aniso_forces(a->potential, a->scalar_bits, &aa, a->d_params, cur));
+            for (ForceCall& f : calls)
+                AZB_TRY(f.launch(a->scalar_bits, ln.tile_begin, ln.tile_count, cur));
             }
         if (o < a->n_outs && a->outs[o].after_launch == c)
             {
@@ -131,14 +151,41 @@ extern "C" AZB_API int azb_host_step(const azb_host_step_args* a)
         }
     if (o != a->n_outs)
         return AZB_ERR_BAD_ARGUMENT; // outs must be sorted by after_launch, each naming an existing launch
-    // the compute stream also owns the tail of the input copies (a chunk nobody waited for), then the host waits for the
-    // last output row
+    // the compute stream also owns the tail of the input copies (a chunk nobody waited for)
     AZB_TRY(cudaStreamWaitEvent(cur, g_pool.get(a->n_in_chunks - 1), 0));
+    return 0;
+#undef AZB_TRY
+    }
+    } // namespace
+
+extern "C" AZB_API void azb_host_step_release(void)
+    {
+    g_pool.release();
+    }
+
+extern "C" AZB_API int azb_host_step(const azb_host_step_args* a)
+    {
+    if (!a || !a->force_args || !a->in_edges || !a->launches || (a->n_outs && !a->outs) || a->n_inputs > 8 || a->n_outputs > 8 || a->n_in_chunks == 0
+        || a->n_more > 7 || (a->n_more && !a->more))
+        return AZB_ERR_BAD_ARGUMENT;
+    cudaStream_t cur = (cudaStream_t)a->stream, s_in = (cudaStream_t)a->stream_in, s_out = (cudaStream_t)a->stream_out;
+    std::vector<ForceCall> calls(1 + a->n_more);
+    int rc = calls[0].init(a->kind, a->potential, a->force_args, a->d_params);
+    for (unsigned int k = 0; k < a->n_more && rc == 0; ++k)
+        rc = calls[1 + k].init(a->more[k].kind, a->more[k].potential, a->more[k].force_args, a->more[k].d_params);
+    if (rc != 0)
+        return rc;
+    static const bool trace = std::getenv("AZB_TRACE_HOST_STEP") != nullptr; // prints how long the host spent issuing
+    const auto t_begin = std::chrono::steady_clock::now();
+    rc = issue(a, calls, cur, s_in, s_out);
     const auto t_issued = std::chrono::steady_clock::now();
-    AZB_TRY(cudaStreamSynchronize(s_out));
-    AZB_TRY(cudaStreamSynchronize(cur));
+    // the host waits for the last output row — and, after an error in the middle of the sequence, for whatever copies and
+    // launches were already queued: the caller's buffers must not be written behind its back
+    const int e_in = (int)cudaStreamSynchronize(s_in), e_out = (int)cudaStreamSynchronize(s_out), e_cur = (int)cudaStreamSynchronize(cur);
+    if (rc == 0)
+        rc = e_in ? e_in : (e_out ? e_out : e_cur);
     if (trace)
         std::fprintf(stderr, "azb_host_step: issue %.1f us, total %.1f us\n", std::chrono::duration<double, std::micro>(t_issued - t_begin).count(),
                      std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count());
-    return 0;
+    return rc;
     }

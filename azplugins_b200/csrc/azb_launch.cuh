@@ -1,6 +1,7 @@
 // azb_launch.cuh — host-side glue shared by the per-family translation units: converts the C-ABI argument
 // structs (include/azb200.h) into the typed device argument structs and picks launch shapes.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 
 #include "azb200.h"
@@ -70,16 +71,34 @@ inline unsigned int pick_block(unsigned int requested)
     return (b / 32) * 32;
     }
 
-// opt-in dynamic shared memory above 48 KB, once per kernel instantiation and size
+// opt-in dynamic shared memory above 48 KB. The attribute belongs to (device, kernel): the granted size is tracked per device
+// of this process (one atomic per device and kernel instantiation — a concurrent duplicate call is harmless), and a refusal
+// comes back to the caller as the CUDA error code.
 #define AZB_MAX_SMEM (227 * 1024)
-template<auto KERNEL> inline void ensure_smem(size_t bytes)
+#define AZB_MAX_DEVICES 64
+template<auto KERNEL> inline int ensure_smem(size_t bytes)
     {
-    static size_t granted = 48 * 1024;
-    if (bytes > granted)
+    static std::atomic<size_t> granted[AZB_MAX_DEVICES];
+    if (bytes <= 48 * 1024)
+        return 0;
+    int dev = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess)
+        return (int)err;
+    const bool tracked = dev >= 0 && dev < AZB_MAX_DEVICES;
+    if (tracked && bytes <= granted[dev].load(std::memory_order_acquire))
+        return 0;
+    err = cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (err != cudaSuccess)
+        return (int)err;
+    if (tracked)
         {
-        cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-        granted = bytes;
+        size_t seen = granted[dev].load(std::memory_order_relaxed);
+        while (seen < bytes && !granted[dev].compare_exchange_weak(seen, bytes, std::memory_order_release))
+            {
+            }
         }
+    return 0;
     }
 
 // Validates a.tiles against the launch and picks the CTA size: blockDim / tpp groups, each walking

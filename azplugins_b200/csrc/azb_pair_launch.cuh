@@ -49,7 +49,7 @@ static int launch_pair_variant(const azb_pair_args& a, const void* d_params, cud
 #define AZB_LAUNCH_T(TPP, FB, SG)                                                                                         \
     do                                                                                                                    \
         {                                                                                                                 \
-        ensure_smem<pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG>>(smem);                                          \
+        if (const int e_ = ensure_smem<pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG>>(smem)) return e_;                                          \
         pair_tile_kernel<Pot, S, SHIFT, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
         } while (0)
 #define AZB_CALL_T(TPP)                         \

@@ -22,7 +22,7 @@ template<int SHIFT, bool VIRIAL> struct PackedPLJ
 #define AZB_PACKED(TPP)                                                                                                      \
     do                                                                                                                       \
         {                                                                                                                    \
-        ensure_smem<plj_packed_tile_kernel<SHIFT, VIRIAL, TPP>>(smem);                                                       \
+        if (ensure_smem<plj_packed_tile_kernel<SHIFT, VIRIAL, TPP>>(smem) != 0) return false;                                                       \
         plj_packed_tile_kernel<SHIFT, VIRIAL, TPP><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
         } while (0)
         switch (tpp)

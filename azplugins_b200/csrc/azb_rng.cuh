@@ -12,7 +12,7 @@
 //
 // PARITY UNPINNED: the Seed/Counter packing and the u01 mapping are restated from recollection of HOOMD/Random123;
 // the reference's tests pin only the statistics (pytest/test_pair_dpd.py:46). The Philox core is pinned by
-// Random123's known-answer vectors (tests/test_philox.py). Everything sits in this header (and, independently
+// Random123's known-answer vectors (tests/test_oracle_golden.py::test_philox_known_answers). Everything sits in this header (and, independently
 // restated, in oracle/shim/hoomd/RandomNumbers.h) so a correction is a one-place change.
 #pragma once
 #include <stdint.h>

@@ -63,22 +63,35 @@ def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
 
 
 class HostStep:
+    """``HostStep(force_or_forces, chunks)``: several tile-staged force objects over the same particles and the same neighbour
+    list (C5: DPD + ExpandedYukawa) are evaluated by the same launch ranges of one ``azb_host_step`` call."""
+
     def __init__(self, force, chunks=8):
-        if force._state is None:
+        forces = list(force) if isinstance(force, (list, tuple)) else [force]
+        if not forces or any(f._state is None for f in forces):
             raise RuntimeError("force is not attached to a state")
-        self.force = force
+        if any(f._state is not forces[0]._state for f in forces):
+            raise ValueError("HostStep: every force object must be attached to the same state")
+        self.forces = forces
+        self.force = forces[0]
         self.chunks = int(chunks)
-        st = force._state
+        st = self.force._state
         dev = st.device
         self.s_in = torch.cuda.Stream(dev)
         self.s_out = torch.cuda.Stream(dev)
         self.inputs = [st.pos]
-        if force._kind == _abi.KIND_DPD:
+        if any(f._kind == _abi.KIND_DPD for f in forces):
             self.inputs.append(st.vel)
-        if force._kind == _abi.KIND_ANISO:
+        if any(f._kind == _abi.KIND_ANISO for f in forces):
             self.inputs.append(st.orientation)
-        self.outputs = [force._force] + ([force._torque] if force._torque is not None else [])
-        self._plan_id = None
+        self.outputs = []
+        for f in forces:
+            self.outputs.append(f._force)
+            if f._torque is not None:
+                self.outputs.append(f._torque)
+        if len(self.outputs) > 8:
+            raise ValueError("HostStep: at most 8 output arrays")
+        self._plans = None
         self._schedule = None
 
     # bytes moved per step (the bench reports them)
@@ -96,36 +109,56 @@ class HostStep:
     def pinned_outputs(self):
         return [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in self.outputs]
 
-    def _make_schedule(self):
-        """Which tiles each launch holds (by the input chunk that completes their inputs), and which launch completes
-        each block of output rows."""
-        f, st = self.force, self.force._state
-        f.nlist.compute(st)
-        plan = f._current_plan()
-        if plan is None:
-            self._schedule = None
-            return
-        K = max(1, min(self.chunks, plan.n_tiles))
-        n_rows = st.pos.shape[0]
-        in_edges = np.linspace(0, n_rows, K + 1).astype(np.int64)
+    def _current_plans(self):
+        plans = [f._current_plan() for f in self.forces]
+        if any(p is None for p in plans):
+            return None
+        if any(p.tile_size != plans[0].tile_size or p.n_tiles != plans[0].n_tiles for p in plans):
+            return None  # different tilings: no common launch ranges
+        return plans
+
+    @staticmethod
+    def _tile_hi(plan, N):
+        """Highest particle index a tile reads: its own last particle, or the last (largest) entry of its ascending uniq list."""
         count = plan.uniq_count.cpu().numpy().astype(np.int64)
-        # highest index a tile reads: its own last particle, or the last (largest) entry of its ascending uniq list
         last = torch.arange(plan.n_tiles, device=plan.uniq.device, dtype=torch.int64) * plan.uniq_capacity + torch.from_numpy(
             np.maximum(count - 1, 0)).to(plan.uniq.device)
         hi = plan.uniq[last].cpu().numpy().astype(np.int64)
         hi = np.where(count > 0, hi, 0)
-        own_hi = np.minimum((np.arange(plan.n_tiles) + 1) * plan.tile_size, st.N) - 1
-        hi = np.maximum(hi, own_hi)
+        own_hi = np.minimum((np.arange(plan.n_tiles) + 1) * plan.tile_size, N) - 1
+        return np.maximum(hi, own_hi)
+
+    def _make_schedule(self, plans):
+        """Which tiles each launch holds (by the input chunk that completes their inputs), and which launch completes
+        each block of output rows."""
+        f, st = self.force, self.force._state
+        self._plans = plans
+        if plans is None:
+            self._schedule = None
+            return
+        plan = plans[0]
+        K = max(1, min(self.chunks, plan.n_tiles))
+        n_rows = st.pos.shape[0]
+        in_edges = np.linspace(0, n_rows, K + 1).astype(np.int64)
+        hi = self._tile_hi(plan, st.N)
+        for p in plans[1:]:
+            if p.uniq is not plan.uniq:
+                hi = np.maximum(hi, self._tile_hi(p, st.N))
         order, sched, merged = plan_schedule(hi, in_edges, plan.tile_size, st.N)
         # the native call's tables, built once per plan: a step only patches the timestep and the host pointers
         d_order = torch.from_numpy(order.astype(np.int32)).to(st.device)
-        whole = f._build_args(0, tile_order=d_order)
+        wholes = [g._build_args(0, tile_order=d_order) for g in self.forces]
         hs = _abi.HostStepArgs()
         hs.kind = f._kind
         hs.potential = f._spec.potential_id
         hs.scalar_bits = st.scalar_bits
-        hs.force_args = C.addressof(whole)
+        hs.force_args = C.addressof(wholes[0])
         hs.d_params = f._d_params.data_ptr()
+        more = (_abi.HostForce * max(len(self.forces) - 1, 1))()
+        for k, g in enumerate(self.forces[1:]):
+            more[k].kind, more[k].potential = g._kind, g._spec.potential_id
+            more[k].force_args, more[k].d_params = C.addressof(wholes[1 + k]), g._d_params.data_ptr()
+        hs.n_more, hs.more = len(self.forces) - 1, more
         hs.n_inputs, hs.n_outputs = len(self.inputs), len(self.outputs)
         for k, t in enumerate(self.inputs):
             hs.inputs[k].d_ptr, hs.inputs[k].row_bytes = t.data_ptr(), t.shape[1] * t.element_size()
@@ -142,8 +175,11 @@ class HostStep:
         hs.n_launches, hs.launches = len(sched), launches
         hs.n_outs, hs.outs = len(merged), out_ranges
         hs.stream_in, hs.stream_out = self.s_in.cuda_stream, self.s_out.cuda_stream
-        self._schedule = (hs, whole, (edges, launches, out_ranges, d_order), merged, sched)  # the ctypes objects must outlive the calls
-        self._plan_id = id(plan)
+        # everything the native call dereferences stays referenced from the schedule: the ctypes tables, the launch order, and
+        # the plans + list arrays the argument structs point into (a rebuilt list makes new plan objects -> new schedule)
+        nl = f.nlist
+        keep = (edges, launches, out_ranges, d_order, more, plans, nl.n_neigh, nl.head_list, nl.nlist)
+        self._schedule = (hs, wholes, keep, merged, sched)
 
     def run(self, timestep, host_in, host_out):
         """host_in / host_out: lists of pinned host tensors matching ``inputs`` / ``outputs``. Returns after the forces are
@@ -152,25 +188,35 @@ class HostStep:
         f = self.force
         dev = f._state.device
         cur = torch.cuda.current_stream(dev)
-        f._prepare()
-        plan = f._current_plan()
-        if self._schedule is None or plan is None or id(plan) != self._plan_id:
-            self._make_schedule()
+        for g in self.forces:
+            g._prepare()
+        plans = self._current_plans()
+        stale = self._plans is None or plans is None or len(plans) != len(self._plans) or any(a is not b for a, b in zip(plans, self._plans))
+        if self._schedule is None or stale:
+            self._make_schedule(plans)
         if self._schedule is None:
             # no tile plan (e.g. a kernel family without a tiled flavour): plain copy - compute - copy
             for dst, src in zip(self.inputs, host_in):
                 dst.copy_(src, non_blocking=True)
-            f.compute(timestep)
+            for g in self.forces:
+                g.compute(timestep)
             for dst, src in zip(host_out, self.outputs):
                 dst.copy_(src, non_blocking=True)
             cur.synchronize()
             return
-        hs, whole, _, _, sched = self._schedule
-        f._set_timestep(whole, timestep)
+        hs, wholes, _, _, sched = self._schedule
+        for g, whole in zip(self.forces, wholes):
+            g._set_timestep(whole, timestep)
         for k, t in enumerate(host_in):
             hs.inputs[k].h_ptr = t.data_ptr()
         for k, t in enumerate(host_out):
             hs.outputs[k].h_ptr = t.data_ptr()
         hs.stream = cur.cuda_stream
         _abi.check(f._lib.azb_host_step(C.byref(hs)), "azb_host_step")
-        f.launches += len(sched)
+        for g in self.forces:
+            g.launches += len(sched)
+
+    def release(self):
+        """Drop the native call's per-thread event pool (``azb_host_step_release``) and the cached schedule."""
+        self._schedule = self._plans = None
+        self.force._lib.azb_host_step_release()

@@ -66,9 +66,11 @@ def lj_fluid(m=20, rho=0.8, seed=1001, jitter=0.15):
 PLJ_PARAMS = {("A", "A"): dict(epsilon=1.0, sigma=1.0, attraction_scale_factor=0.5)}
 
 
-def yukawa_dpd_fluid(n=8_000_000, rho=1.0, seed=5001, jitter=0.15, kT=1.0):
+def yukawa_dpd_fluid(n=8_000_000, rho=1.0, seed=5001, jitter=0.1, kT=1.0):
     """C5: one system, two force objects on one neighbour list (ExpandedYukawa r_cut = 2.0 + DPDGeneralWeight r_cut = 1.0);
-    jittered FCC lattice at rho = 1.0, N = 4 m^3 nearest to n."""
+    jittered FCC lattice at rho = 1.0, N = 4 m^3 nearest to n. The jitter is 0.1 lattice constants (0.15 elsewhere): two nearest
+    neighbours (1.122 apart) jittered towards each other then stay 0.67 apart, clear of the ExpandedYukawa pole at
+    r = delta = 0.5; with 0.15 a few hundred of the 48 M nearest-neighbour pairs of the 8 M system would land on it."""
     rng = np.random.default_rng(seed)
     m = max(2, round((n / 4) ** (1.0 / 3.0)))
     box, pos = fcc_lattice(m, rho, jitter, rng)
@@ -180,3 +182,7 @@ def polymer_melt(n_chains=40_000, chain_len=100, rho=0.85, seed=3001, bond_len=0
 
 QUARTIC_PARAMS = dict(k=1434.3, r_0=1.5, b_1=-0.7589, b_2=0.0, U_0=67.2234, sigma=1.0, epsilon=1.0, delta=0.0)
 DOUBLE_WELL_PARAMS = dict(r_0=1.0, r_1=2.0, U_1=1.0, U_tilt=0.5)
+# HOOMD evaluates every bond object on every bond: an object that does not own a bond type is given parameters for which the
+# evaluator returns zero force and zero energy without tripping its validity check (r_0 != 0; r_0 != r_1)
+QUARTIC_NEUTRAL = dict(k=0.0, r_0=1.5, b_1=0.0, b_2=0.0, U_0=0.0, sigma=0.0, epsilon=0.0, delta=0.0)
+DOUBLE_WELL_NEUTRAL = dict(r_0=1.0, r_1=2.0, U_1=0.0, U_tilt=0.0)

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define AZB200_ABI_VERSION 2
+#define AZB200_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define AZB_API __attribute__((visibility("default")))
@@ -422,8 +422,11 @@ AZB_API int azb_halo_signal(unsigned int* const* d_peer_flags, unsigned int n, u
  *   D2H   rows [row_lo, row_hi) of every output follow on stream_out once launch outs[k].after_launch has finished,
  *         while later launches compute.
  * force_args is the azb_pair_args / azb_dpd_args / azb_aniso_args of the whole evaluation (kind says which); its tiles must
- * be set; tile_begin / tile_count are overwritten per launch on a private copy. Returns after every output row is in host
- * memory. */
+ * be set; tile_begin / tile_count are overwritten per launch on a private copy. Several force objects over the same particles
+ * and the same tiling (HOOMD: several pair forces subscribed to one neighbour list; C5 = DPD + ExpandedYukawa) are evaluated by
+ * one call: `more` lists the further objects, every launch range is issued for each of them (their plans must have the same
+ * tile_size and their d_tile_order the same launch positions), and `outputs` carries the force arrays of all of them.
+ * Returns after every output row is in host memory; on an error every stream the call touched is synchronised first. */
 typedef struct azb_host_buffer
     {
     void* d_ptr;      /* device array (a field of force_args points at it too) */
@@ -443,6 +446,14 @@ typedef struct azb_host_out_range
     size_t row_lo, row_hi;
     } azb_host_out_range;
 
+typedef struct azb_host_force
+    {
+    int kind; /* AZB_KIND_PAIR, AZB_KIND_DPD or AZB_KIND_ANISO */
+    int potential;
+    const void* force_args;
+    const void* d_params;
+    } azb_host_force;
+
 typedef struct azb_host_step_args
     {
     int kind; /* AZB_KIND_PAIR, AZB_KIND_DPD or AZB_KIND_ANISO */
@@ -450,9 +461,9 @@ typedef struct azb_host_step_args
     int scalar_bits;
     const void* force_args;
     const void* d_params;
-    unsigned int n_inputs, n_outputs; /* <= 4 each */
-    azb_host_buffer inputs[4];
-    azb_host_buffer outputs[4];
+    unsigned int n_inputs, n_outputs; /* <= 8 each */
+    azb_host_buffer inputs[8];
+    azb_host_buffer outputs[8];
     unsigned int n_in_chunks;
     const size_t* in_edges; /* host array [n_in_chunks + 1], ascending row indices */
     unsigned int n_launches;
@@ -462,7 +473,12 @@ typedef struct azb_host_step_args
     void* stream;     /* compute stream */
     void* stream_in;  /* H2D copies */
     void* stream_out; /* D2H copies */
+    unsigned int n_more;       /* further force objects evaluated by the same launches (<= 7) */
+    const azb_host_force* more; /* host array */
     } azb_host_step_args;
+
+/* Frees the per-thread event pool azb_host_step keeps between calls (optional; call from the thread that ran the steps). */
+AZB_API void azb_host_step_release(void);
 
 AZB_API int azb_host_step(const azb_host_step_args* args);
 

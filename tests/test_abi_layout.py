@@ -29,6 +29,7 @@ MIRRORS = {
     "azb_host_buffer": _abi.HostBuffer,
     "azb_host_launch": _abi.HostLaunch,
     "azb_host_out_range": _abi.HostOutRange,
+    "azb_host_force": _abi.HostForce,
     "azb_host_step_args": _abi.HostStepArgs,
 }
 

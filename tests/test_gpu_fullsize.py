@@ -64,24 +64,31 @@ def _compare(name, got, want, hs, rcutsq, max_outlier_frac):
     return float(np.max(np.delete(err, bad))) if len(bad) < len(err) else 0.0, len(bad)
 
 
-def _run(workload):
+def _run_all(workload):
+    """Every force object of the workload, evaluated twice on the GPU-built list (bit-identical repeat), + the host copy."""
     label, snap, setup, buffer = bench.make_workload(workload, 0)
     nl = nlist.Cell(buffer=buffer)
     forces = setup(nl)
     st = az.State(snap, device="cuda", scalar_bits=32, seed=42)
-    f = forces[0]
-    f.compute_virial = True
-    f._attach(st)
-    f.compute(5)
-    torch.cuda.synchronize()
-    assert f._plan is not None  # the tile-staged production kernel, as in the bench
-    first = f._force.clone()
-    f.compute(5)
-    torch.cuda.synchronize()
-    assert torch.equal(first, f._force), "two launches on the same inputs must agree bit for bit"
+    for f in forces:
+        f.compute_virial = True
+        f._attach(st)
+        f.compute(5)
+        torch.cuda.synchronize()
+        if hasattr(f, "_current_plan"):
+            assert f._plan is not None  # the tile-staged production kernel, as in the bench
+        first = f._force.clone()
+        f.compute(5)
+        torch.cuda.synchronize()
+        assert torch.equal(first, f._force), "two launches on the same inputs must agree bit for bit"
     hs, _ = bench.host_arrays_for_oracle(snap, 32, nl.n_neigh.cpu().numpy().view(np.uint32), nl.head_list.cpu().numpy().view(np.uint64),
                                          nl.nlist.cpu().numpy().view(np.uint32))
-    return snap, f, hs
+    return snap, forces, hs, st
+
+
+def _run(workload):
+    snap, forces, hs, _ = _run_all(workload)
+    return snap, forces[0], hs
 
 
 def _third_law(f):
@@ -159,6 +166,80 @@ def test_c4_mixture_full_size(workload):
     bench_report(f"c4_{workload}", worst, n_bad)
 
 
+@pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref not built")
+def test_c3_melt_full_size():
+    """C3: 4 M-bead melt — PerturbedLJ over a list with the bonded pairs excluded + bond.Quartic on bond type 0 (90 %) +
+    bond.DoubleWell on bond type 1 (10 %), each bond object neutral on the other's type, as three HOOMD force objects."""
+    from azplugins_b200.state import build_bond_table
+
+    snap, (plj, quartic, dwell), hs, st = _run_all("melt")
+    assert snap.N == 4_000_000 and len(snap.bond_group) == 3_960_000
+    assert 0.08 < float(np.mean(snap.bond_typeid == 1)) < 0.12
+    # exclusions: no bonded pair may be on the list. Bonds join consecutive beads of a chain (indices i, i + 1 with the same
+    # i // 100); checked on the device arrays (552 M entries)
+    nl = plj.nlist
+    nn = nl.n_neigh[: snap.N].long()
+    assert torch.equal(nl.head_list[: snap.N], torch.cumsum(nn, 0) - nn), "rows are expected back to back"
+    i_idx = torch.repeat_interleave(torch.arange(snap.N, device=nn.device), nn)
+    j_idx = nl.nlist[: i_idx.numel()].long()
+    bonded = ((i_idx - j_idx).abs() == 1) & (i_idx // 100 == j_idx // 100)
+    assert not bool(bonded.any()), "a bonded pair is on the neighbour list"
+    del i_idx, j_idx, bonded, nn
+    torch.cuda.empty_cache()
+    threads = bench.os.cpu_count() or 1
+    spec = cases.SPEC_BY_API["PerturbedLennardJones"]
+    par, rcsq, ronsq, _ = _tables(spec, W.PLJ_PARAMS, 3.0, snap.types)
+    _third_law(plj)
+    hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=threads, which="ref")
+    worst, n_bad = _compare("c3/plj", plj._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    _energy_sum(plj, hs)
+    bench_report("c3_melt_plj", worst, n_bad)
+    table = build_bond_table(snap.N, snap.N, snap.bond_group, snap.bond_typeid)
+    q, dw = cases.SPEC_BY_API["Quartic"], cases.SPEC_BY_API["DoubleWell"]
+    for name, f, sp, plist in (("quartic", quartic, q, [W.QUARTIC_PARAMS, W.QUARTIC_NEUTRAL]), ("doublewell", dwell, dw, [W.DOUBLE_WELL_NEUTRAL, W.DOUBLE_WELL_PARAMS])):
+        f.check_flags()
+        _third_law(f)
+        hs.bond(sp.potential_id, np.array([sp.pack(p, 32) for p in plist]), *table, 2, nthreads=threads, which="ref")
+        assert hs.flags == 0
+        got, want = f._force.cpu().numpy().astype(np.float64), hs.force.astype(np.float64)
+        mag = np.linalg.norm(want[:, :3], axis=1)
+        err = np.linalg.norm(got[:, :3] - want[:, :3], axis=1) / np.maximum(mag, np.sqrt(np.mean(mag**2)))
+        assert err.max() <= TOL, (name, float(err.max()))  # bonds have no cutoff: no ambiguous membership, no outliers allowed
+        _energy_sum(f, hs)
+        # each object is silent on the other's bond type: particles with bonds of the other type only feel nothing from it
+        bench_report(f"c3_melt_{name}", float(err.max()), 0)
+    # the DoubleWell object must act on exactly the beads of type-1 bonds
+    touched = np.zeros(snap.N, dtype=bool)
+    touched[snap.bond_group[snap.bond_typeid == 1].reshape(-1)] = True
+    fdw = dwell._force.cpu().numpy()
+    assert np.all(fdw[~touched] == 0.0) and np.count_nonzero(np.any(fdw[touched, :3] != 0, axis=1)) > 0.9 * touched.sum()
+
+
+@pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref not built")
+def test_c5_eydpd_full_size():
+    """C5 at its single-GPU size: 8 M particles, DPDGeneralWeight r_cut = 1.0 and ExpandedYukawa r_cut = 2.0 on ONE neighbour
+    list (built for 2.0 + buffer)."""
+    snap, (dpd, ey), hs, st = _run_all("eydpd")
+    assert snap.N >= 7_900_000
+    threads = bench.os.cpu_count() or 1
+    _third_law(dpd)
+    _third_law(ey)
+    par, rcsq, _, _ = _tables(cases.SPEC_BY_API["DPDGeneralWeight"], W.C5_DPD_PARAMS, 1.0, snap.types)
+    hs.dpd(par, rcsq, seed=42, timestep=5, dt=0.01, kT=1.0, nthreads=threads, which="ref")
+    worst, n_bad = _compare("c5/dpd", dpd._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-4)
+    _energy_sum(dpd, hs)
+    bench_report("c5_dpd_8M", worst, n_bad)
+    spec = cases.SPEC_BY_API["ExpandedYukawa"]
+    par, rcsq, ronsq, _ = _tables(spec, W.EY_PARAMS, 2.0, snap.types)
+    hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=threads, which="ref")
+    worst, n_bad = _compare("c5/ey", ey._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    _energy_sum(ey, hs)
+    v = ey._virial[:, : snap.N].double().sum(dim=1).cpu().numpy()
+    v_ref = hs.virial[:, : snap.N].astype(np.float64).sum(axis=1)
+    assert np.max(np.abs(v - v_ref)) <= SUM_TOL * np.max(np.abs(v_ref))
+    bench_report("c5_ey_8M", worst, n_bad)
+
+
 _REPORT = {}
 
 
@@ -167,6 +248,7 @@ def bench_report(name, worst, n_bad):
     import os
 
     _REPORT[name] = {"max_rel_error_excluding_cutoff_ambiguous": worst, "cutoff_ambiguous_outliers": n_bad}
+    print(f"[fullsize parity] {name}: worst rel. error {worst:.3g}, cutoff-ambiguous outliers skipped: {n_bad}")
     os.makedirs("gpurun_out", exist_ok=True)
     with open("gpurun_out/parity_fullsize.json", "w") as fh:
         json.dump(_REPORT, fh, indent=1, sort_keys=True)

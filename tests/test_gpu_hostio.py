@@ -68,3 +68,38 @@ def test_tile_range_leaves_other_particles_untouched():
     assert torch.all(got[: 2 * ts] == -7.0) and torch.all(got[5 * ts :] == -7.0)
     with pytest.raises(RuntimeError):
         f.compute(0, tile_range=(f._plan.n_tiles, 1))
+
+
+@pytest.mark.parametrize("chunks", [1, 4])
+def test_host_step_two_forces_on_one_list(chunks):
+    """C5's shape: DPDGeneralWeight + ExpandedYukawa on one neighbour list, evaluated by the launch ranges of one call."""
+    snap = W.yukawa_dpd_fluid(n=30000, seed=8)
+    nl = nlist.Cell(buffer=0.4)
+    d = pair.DPDGeneralWeight(nlist=nl, kT=1.0, default_r_cut=1.0)
+    d.dt = 0.01
+    for k, v in W.C5_DPD_PARAMS.items():
+        d.params[k] = v
+    y = pair.ExpandedYukawa(nlist=nl, default_r_cut=2.0)
+    for k, v in W.EY_PARAMS.items():
+        y.params[k] = v
+    st = az.State(snap, device="cuda", scalar_bits=32, seed=42)
+    for f in (d, y):
+        f._attach(st)
+        f.compute(4)
+    torch.cuda.synchronize()
+    want = [d._force.cpu().clone(), y._force.cpu().clone()]
+    hs = HostStep([d, y], chunks=chunks)
+    assert len(hs.inputs) == 2 and len(hs.outputs) == 2
+    h_in, h_out = hs.pinned_inputs(), hs.pinned_outputs()
+    for t in (st.pos, st.vel, d._force, y._force):
+        t.zero_()
+    hs.run(4, h_in, h_out)
+    assert torch.equal(h_out[0], want[0]) and torch.equal(h_out[1], want[1])
+    # a list rebuild makes new plans: the cached schedule must not be reused with the old arrays
+    nl.invalidate()
+    hs.run(5, h_in, h_out)
+    d.compute(5)
+    y.compute(5)
+    torch.cuda.synchronize()
+    assert torch.equal(h_out[0], d._force.cpu()) and torch.equal(h_out[1], y._force.cpu())
+    hs.release()
