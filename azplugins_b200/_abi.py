@@ -163,6 +163,7 @@ class NlistArgs(C.Structure):
 # every symbol include/azb200.h declares (tests check the library exports exactly these)
 EXPORTS = (
     "azb_host_step",
+    "azb_host_step_release",
     "azb_abi_version",
     "azb_param_size",
     "azb_param_align",
