@@ -34,10 +34,8 @@ def build_cell_nlist(nl, state, row_align=1):
     a.ntypes = len(state.types)
     a.row_align = row_align
     keep = [rlsq]
-    if "bond" in nl.exclusions and len(state.bond_group):
-        head, lst = state.exclusions_csr()
-        d_head = torch.from_numpy(head.view(np.int64)).to(dev)
-        d_lst = torch.from_numpy(lst.view(np.int32) if lst.size else np.zeros(1, np.int32)).to(dev)
+    if "bond" in nl.exclusions and state.has_bonds:
+        d_head, d_lst = state.exclusions_device()
         a.d_excl_head, a.d_excl_list = d_head.data_ptr(), d_lst.data_ptr()
         keep += [d_head, d_lst]
     n_neigh = torch.zeros(max(state.N, 1), dtype=torch.int32, device=dev)

@@ -75,6 +75,17 @@ class Force:
         self._virial = torch.zeros((6, max(state.N, 1)), dtype=td, device=state.device)
         self._dirty = True
 
+    def _sync_size(self):
+        """Output arrays for the state's current number of local particles (domain decomposition: N changes when particles
+        migrate on a list rebuild)."""
+        st = self._state
+        if st is not None and self._force is not None and self._force.shape[0] != st.N:
+            td = self._force.dtype
+            self._force = torch.zeros((st.N, 4), dtype=td, device=st.device)
+            self._virial = torch.zeros((6, max(st.N, 1)), dtype=td, device=st.device)
+            if self._torque is not None:
+                self._torque = torch.zeros((st.N, 4), dtype=td, device=st.device)
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self._state.device).cuda_stream)
 
@@ -222,6 +233,7 @@ class Pair(Force):
     def _prepare(self):
         if self._state is None:
             raise RuntimeError("force is not attached to a state")
+        self._sync_size()
         self.nlist.compute(self._state)
         if self._dirty:
             self._tables()
@@ -364,6 +376,7 @@ class Bond(Force):
         if self._state is None:
             raise RuntimeError("force is not attached to a state")
         st = self._state
+        self._sync_size()
         if self._dirty:
             self._tables()
         tb = st.bond_table()

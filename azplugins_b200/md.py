@@ -38,27 +38,41 @@ class Integrator:
         self.nlist_rebuilds = 0
         self._state = None
 
-    def attach(self, state, timestep=0):
+    def attach(self, state, timestep=0, domain=None):
+        """``domain``: the ``domain.HaloExchange`` of a decomposed state (one rank of a multi-GPU run). Every list rebuild
+        then migrates particles between the ranks and re-selects the ghost layer (HOOMD: Communicator::migrateParticles /
+        exchangeGhosts before the neighbour list is rebuilt); between rebuilds the ghosts are refreshed every step."""
         if state.device.type != "cuda":
             raise RuntimeError("azplugins_b200 integrates on a CUDA device only (no CPU fallback)")
-        if state.n_ghost:
-            raise NotImplementedError("Integrator: decomposed states are stepped by the caller (migration is not implemented)")
+        if state.n_ghost and domain is None:
+            raise ValueError("Integrator: a decomposed state (ghost particles) needs its HaloExchange passed as `domain`")
         self._lib = _abi.load()
         self._state = state
+        self._domain = domain
         self.timestep = int(timestep)
         dev = state.device
-        state.accel = torch.zeros((state.N, 4), dtype=state.pos.dtype, device=dev)
         if getattr(state, "image", None) is None:
             state.image = torch.zeros((state.N, 3), dtype=torch.int32, device=dev)
-        self._net = torch.zeros((state.N, 4), dtype=state.pos.dtype, device=dev)
         self._flag = torch.zeros(1, dtype=torch.int32, device=dev)
         for f in self.forces:
             if f._state is not state:
                 f._attach(state)
             if hasattr(f, "dt"):
                 f.dt = self.dt  # DPD reads the integrator's step size (HOOMD: m_deltaT)
+        self._size_arrays()
         self._ready = False
         return self
+
+    def _size_arrays(self):
+        """Per-particle work arrays for the current number of local particles (it changes when particles migrate)."""
+        st = self._state
+        state_accel = getattr(st, "accel", None)
+        if state_accel is None or state_accel.shape[0] != st.N:
+            st.accel = torch.zeros((st.N, 4), dtype=st.pos.dtype, device=st.device)
+        if getattr(self, "_net", None) is None or self._net.shape[0] != st.N:
+            self._net = torch.zeros((st.N, 4), dtype=st.pos.dtype, device=st.device)
+        for f in self.forces:
+            f._sync_size()
 
     # ---- helpers ---------------------------------------------------------------------------------------------------
     def _stream(self):
@@ -88,21 +102,37 @@ class Integrator:
         return out
 
     def _update_nlists(self):
-        """NeighborList::distanceCheck: rebuild when any particle has moved buffer / 2 since the last build."""
-        st = self._state
-        for nl in self._nlists():
+        """NeighborList::distanceCheck: rebuild when any particle has moved buffer / 2 since the last build. In a decomposed run
+        the decision is collective (one MAX all-reduce of the flag word): every rank migrates and re-selects ghosts together.
+        Returns True when the lists were invalidated."""
+        st, dom = self._state, self._domain
+        rebuild = False
+        lists = self._nlists()
+        self._flag.zero_()
+        for nl in lists:
             last = getattr(nl, "_last_pos", None)
-            if nl.n_neigh is None or last is None or nl._state is not st:
+            if nl.n_neigh is None or last is None or nl._state is not st or last.shape[0] != st.N:
                 continue  # the force builds it on first use
-            self._flag.zero_()
             box = st.box.as_abi()
             half = 0.5 * nl.buffer
             _abi.check(self._lib.azb_displacement_check(st.scalar_bits, st.pos.data_ptr(), last.data_ptr(), st.N, C.byref(box), half * half,
                                                         self._flag.data_ptr(), self._stream()), "azb_displacement_check")
             self.launches += 1
-            if int(self._flag.item()) != 0:
+        if dom is not None and dom.decomp.world > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(self._flag, op=dist.ReduceOp.MAX, group=dom.group)
+        if int(self._flag.item()) != 0:
+            rebuild = True
+            if dom is not None:
+                dom.rebuild()
+                self._size_arrays()
+            for nl in lists:
                 nl.invalidate()
-                self.nlist_rebuilds += 1
+            self.nlist_rebuilds += 1
+        elif dom is not None:
+            dom.update()
+        return rebuild
 
     # ---- stepping --------------------------------------------------------------------------------------------------
     def run(self, steps):
@@ -114,6 +144,8 @@ class Integrator:
             raise RuntimeError("Integrator needs a ConstantVolume method")
         st, lib, bits = self._state, self._lib, self._state.scalar_bits
         if not self._ready:
+            if self._domain is not None:
+                self._domain.update()
             for f in self.forces:
                 f.compute(self.timestep)
             a = self._args(True)
@@ -124,7 +156,8 @@ class Integrator:
         one, two = self._args(False), self._args(True)
         for _ in range(int(steps)):
             _abi.check(lib.azb_nve_step_one(bits, C.byref(one), self._stream()), "azb_nve_step_one")
-            self._update_nlists()
+            if self._update_nlists() and self._domain is not None:
+                one, two = self._args(False), self._args(True)  # N and the work arrays changed with the migration
             for f in self.forces:
                 f.compute(self.timestep + 1)
             _abi.check(lib.azb_nve_step_two(bits, C.byref(two), self._stream()), "azb_nve_step_two")

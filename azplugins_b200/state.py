@@ -126,6 +126,34 @@ def build_bond_table(n_local, n_max, bond_group, bond_typeid):
     return n_bonds, bondlist.reshape(-1), bond_pos.reshape(-1), pitch, max_bonds
 
 
+def build_bond_table_device(n_local, group, btype):
+    """``build_bond_table`` on torch tensors (any device): ``group`` (nb, 2) int64 particle indices — a member may be a ghost
+    (index >= n_local), ``btype`` (nb,) int64. Same layout and same slot order as the host version. Used where the table is
+    rebuilt during a run (domain decomposition: bonds follow migrating particles, partners may be ghosts)."""
+    dev = group.device
+    nb = group.shape[0]
+    pitch = max(int(n_local), 1)
+    members = torch.cat([group[:, 0], group[:, 1]])
+    partners = torch.cat([group[:, 1], group[:, 0]])
+    types = torch.cat([btype, btype])
+    posin = torch.cat([torch.zeros(nb, dtype=torch.int64, device=dev), torch.ones(nb, dtype=torch.int64, device=dev)])
+    keep = members < n_local
+    members, partners, types, posin = members[keep], partners[keep], types[keep], posin[keep]
+    order = torch.argsort(members, stable=True)
+    members, partners, types, posin = members[order], partners[order], types[order], posin[order]
+    n_bonds = torch.bincount(members, minlength=pitch)[:pitch] if members.numel() else torch.zeros(pitch, dtype=torch.int64, device=dev)
+    max_bonds = max(int(n_bonds.max().item()), 1) if n_bonds.numel() else 1
+    starts = torch.cumsum(n_bonds, 0) - n_bonds
+    slot = torch.arange(members.numel(), device=dev) - starts[members]
+    bondlist = torch.zeros((max_bonds, pitch, 2), dtype=torch.int32, device=dev)
+    bond_pos = torch.zeros((max_bonds, pitch), dtype=torch.int32, device=dev)
+    bondlist[slot, members, 0] = partners.to(torch.int32)
+    bondlist[slot, members, 1] = types.to(torch.int32)
+    bond_pos[slot, members] = posin.to(torch.int32)
+    n_out = n_bonds[:n_local].to(torch.int32) if n_local else torch.zeros(1, dtype=torch.int32, device=dev)
+    return n_out, bondlist.reshape(-1), bond_pos.reshape(-1), pitch, max_bonds
+
+
 class State:
     """Device-resident particle data of one rank: ``N`` local particles followed by ``n_ghost`` ghosts."""
 
@@ -147,7 +175,11 @@ class State:
         self.typeid_host = s.typeid.copy()
         self.bond_group = s.bond_group.copy()  # particle indices
         self.bond_typeid = s.bond_typeid.copy()
+        # the same bonds by particle TAG: the identity that survives migration between domains (azplugins_b200/domain.py)
+        self.bond_tags = s.tag[s.bond_group].astype(np.uint32) if len(s.bond_group) else np.zeros((0, 2), dtype=np.uint32)
         self._bond_table = None
+        self._bonds_dev = None  # (group int64 (nb, 2), type int64 (nb,)) device tensors of LOCAL indices, set by the domain layer
+        self.image = None
 
     @property
     def n_max(self):
@@ -156,14 +188,47 @@ class State:
     def _to_dev(self, arr):
         return torch.from_numpy(np.ascontiguousarray(arr)).to(self.device)
 
+    def set_local_bonds(self, group, btype):
+        """Bonds of this rank as device tensors of local particle indices (a partner may be a ghost). Called by the domain layer
+        after every migration / ghost re-selection; invalidates the per-particle table and the exclusion list."""
+        self._bonds_dev = (group, btype)
+        self._bond_table = None
+
+    @property
+    def has_bonds(self):
+        return bool(self._bonds_dev[0].shape[0]) if self._bonds_dev is not None else bool(len(self.bond_group))
+
     def bond_table(self):
-        """Device copy of the per-particle bond table (built once; bonds are static topology here)."""
+        """Device copy of the per-particle bond table (rebuilt when the domain layer hands in new local bonds)."""
         if self._bond_table is None:
-            n_bonds, bondlist, bond_pos, pitch, max_bonds = build_bond_table(self.N, self.n_max, self.bond_group, self.bond_typeid)
-            self._bond_table = dict(
-                n_bonds=self._to_dev(n_bonds.view(np.int32)), bondlist=self._to_dev(bondlist.view(np.int32)),
-                bond_pos=self._to_dev(bond_pos.view(np.int32)), pitch=pitch, max_bonds=max_bonds)
+            if self._bonds_dev is not None:
+                n_bonds, bondlist, bond_pos, pitch, max_bonds = build_bond_table_device(self.N, *self._bonds_dev)
+                self._bond_table = dict(n_bonds=n_bonds, bondlist=bondlist, bond_pos=bond_pos, pitch=pitch, max_bonds=max_bonds)
+            else:
+                n_bonds, bondlist, bond_pos, pitch, max_bonds = build_bond_table(self.N, self.n_max, self.bond_group, self.bond_typeid)
+                self._bond_table = dict(
+                    n_bonds=self._to_dev(n_bonds.view(np.int32)), bondlist=self._to_dev(bondlist.view(np.int32)),
+                    bond_pos=self._to_dev(bond_pos.view(np.int32)), pitch=pitch, max_bonds=max_bonds)
         return self._bond_table
+
+    def exclusions_device(self):
+        """Bond exclusions as device CSR (head int64 [N + 1], list int32) over local particles."""
+        if self._bonds_dev is None:
+            head, lst = self.exclusions_csr()
+            return (torch.from_numpy(head.view(np.int64)).to(self.device),
+                    torch.from_numpy(lst.view(np.int32) if lst.size else np.zeros(1, np.int32)).to(self.device))
+        g = self._bonds_dev[0]
+        a = torch.cat([g[:, 0], g[:, 1]])
+        b = torch.cat([g[:, 1], g[:, 0]])
+        keep = a < self.N
+        a, b = a[keep], b[keep]
+        order = torch.argsort(a, stable=True)
+        a, b = a[order], b[order]
+        head = torch.zeros(self.N + 1, dtype=torch.int64, device=g.device)
+        if a.numel():
+            head[1:] = torch.cumsum(torch.bincount(a, minlength=self.N)[: self.N], 0)
+        lst = b.to(torch.int32) if b.numel() else torch.zeros(1, dtype=torch.int32, device=g.device)
+        return head, lst.contiguous()
 
     def exclusions_csr(self):
         """Bond exclusions (HOOMD nlist default ``exclusions=('bond',)``) as CSR over local particles."""

@@ -43,3 +43,10 @@ def test_decomposition_geometry():
                 assert back == d.rank and np.allclose(shift, -shift_back)
     with pytest.raises(ValueError):
         Decomposition(3, 0, box)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_migration_ghost_reselection_and_ghost_bonds_gloo(world):
+    """On a list rebuild: leavers migrate (variable-size messages, sizes first), ghosts are re-selected, bonds are re-indexed
+    with ghost partners — four rebuilds with every particle displaced by up to 0.19 each time."""
+    mp.spawn(domain_worker.run_migration, args=(world, _free_port()), nprocs=world, join=True)
