@@ -164,6 +164,9 @@ class NlistArgs(C.Structure):
 EXPORTS = (
     "azb_host_step",
     "azb_host_step_release",
+    "azb_tile_cache_get",
+    "azb_tile_cache_invalidate",
+    "azb_tile_cache_clear",
     "azb_abi_version",
     "azb_param_size",
     "azb_param_align",
@@ -354,6 +357,12 @@ def load():
     lib.azb_halo_signal.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
     lib.azb_host_step.restype = C.c_int
     lib.azb_host_step.argtypes = [C.POINTER(HostStepArgs)]
+    lib.azb_tile_cache_get.restype = C.c_int
+    lib.azb_tile_cache_get.argtypes = [C.POINTER(PairArgs), C.c_uint, C.c_uint, C.c_void_p, C.POINTER(C.POINTER(TilePlan))]
+    lib.azb_tile_cache_invalidate.restype = None
+    lib.azb_tile_cache_invalidate.argtypes = [C.c_void_p]
+    lib.azb_tile_cache_clear.restype = None
+    lib.azb_tile_cache_clear.argtypes = []
     lib.azb_host_step_release.restype = None
     lib.azb_host_step_release.argtypes = []
     if lib.azb_abi_version() != ABI_VERSION:

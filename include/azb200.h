@@ -303,6 +303,20 @@ typedef struct azb_tile_build_args
 AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,
                             void* stream);
 
+/* ---- library-owned tile plans: for callers whose argument struct cannot carry one -----------------------------------------------
+ * HOOMD's pair_args_t / dpd_pair_args_t / a_pair_args_t have no field for a tile plan, and the kernel-driver stubs that replace
+ * /root/reference/src/PotentialPairGPUKernel.cu.inc:25-28 (hoomd_glue/PotentialPairGPUKernel.cu.inc) see only that struct.
+ * azb_tile_cache_get returns the plan of the list in `args` with the given slot layout (lane_width: 1 for azb_dpd_forces,
+ * the lanes per particle — args->threads_per_particle — for azb_pair_forces / azb_aniso_forces), building it on first use
+ * into buffers the library owns (tile_size 0 = 128; halved on overflow; *plan = NULL when no plan is possible: the direct
+ * kernels then run). The plan is reused while the list arrays have the same addresses, N and size; the host class reports
+ * a rebuild that rewrote the arrays in place with azb_tile_cache_invalidate(d_nlist) (HOOMD: NeighborList::hasBeenUpdated;
+ * hoomd_glue/PotentialPairTiledGPU.h). d_nlist = NULL invalidates every entry. azb_tile_cache_clear frees all buffers. */
+AZB_API int azb_tile_cache_get(const azb_pair_args* args, unsigned int lane_width, unsigned int tile_size, void* stream,
+                               const azb_tile_plan** plan);
+AZB_API void azb_tile_cache_invalidate(const void* d_nlist);
+AZB_API void azb_tile_cache_clear(void);
+
 /* ---- halo packing (SURVEY.md §8 e): d_out[e] = d_src[d_idx[e]] (+ d_shift[e].xyz when d_shift != NULL), Scalar4 rows.
  * Packs the boundary particles a neighbouring domain needs as ghosts into a contiguous send buffer; the periodic image
  * shift is applied on the sender so the receiver stores the message in place behind its local particles. */
