@@ -46,6 +46,8 @@ class TilePlan(C.Structure):
         ("d_uniq_count", C.c_void_p),
         ("d_uniq", C.c_void_p),
         ("d_slots", C.c_void_p),
+        ("d_row_count", C.c_void_p),
+        ("n_entries", C.c_size_t),
     ]
 
 
@@ -64,6 +66,12 @@ class TileBuildArgs(C.Structure):
         ("d_uniq", C.c_void_p),
         ("d_slots", C.c_void_p),
         ("d_status", C.c_void_p),
+        ("d_prune_pos", C.c_void_p),
+        ("d_prune_rsq", C.c_void_p),
+        ("prune_scalar_bits", C.c_int),
+        ("prune_ntypes", C.c_uint),
+        ("prune_box", Box),
+        ("d_row_count", C.c_void_p),
     ]
 
 
@@ -157,6 +165,7 @@ class NlistArgs(C.Structure):
         ("capacity", C.c_size_t),
         ("d_workspace", C.c_void_p),
         ("workspace_bytes", C.c_size_t),
+        ("row_stride_hint", C.c_uint),
     ]
 
 

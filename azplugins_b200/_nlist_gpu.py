@@ -33,6 +33,9 @@ def build_cell_nlist(nl, state, row_align=1):
     a.d_r_listsq = rlsq.data_ptr()
     a.ntypes = len(state.types)
     a.row_align = row_align
+    # one walk instead of two once the previous build has told how long rows get (azb_nlist_args.row_stride_hint)
+    prev_max = getattr(nl, "_row_max", 0)
+    a.row_stride_hint = (int(prev_max * 1.2) + 8) if (prev_max and getattr(nl, "single_walk", True)) else 0
     keep = [rlsq]
     if "bond" in nl.exclusions and state.has_bonds:
         d_head, d_lst = state.exclusions_device()
@@ -54,8 +57,11 @@ def build_cell_nlist(nl, state, row_align=1):
     torch.cuda.current_stream(dev).synchronize()
     del keep
     nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
+    nl._row_max = int(n_neigh.max().item()) if state.N else 0
     nl._tiles = {}
-    nl._last_pos = state.pos[: state.N].clone()  # reference point of the displacement check (md.Integrator)
+    # positions the list was built from (locals + ghosts): reference point of the displacement check (md.Integrator) and of
+    # the pruning test of force-specific tile plans
+    nl._last_pos = state.pos.clone()
     nl.launches = getattr(nl, "launches", 0) + 1
     return nl
 
@@ -63,13 +69,17 @@ def build_cell_nlist(nl, state, row_align=1):
 class TilePlanHandle:
     """Device arrays of one ``azb_tile_plan`` plus the C struct that points at them (kept alive together)."""
 
-    def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, lane_width, max_slot_span, uniq_count, uniq, slots, build_ms):
-        self.uniq_count, self.uniq, self.slots = uniq_count, uniq, slots
+    def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, lane_width, max_slot_span, uniq_count, uniq, slots, build_ms, row_count=None,
+                 entries=None):
+        self.uniq_count, self.uniq, self.slots, self.row_count = uniq_count, uniq, slots, row_count
         self.build_ms = build_ms
+        self.entries = entries  # list entries the plan's rows hold (fewer than the list's when pruned)
         self.c = _abi.TilePlan()
         self.c.tile_size, self.c.n_tiles, self.c.uniq_capacity, self.c.max_uniq = tile_size, n_tiles, uniq_capacity, max_uniq
         self.c.lane_width, self.c.max_slot_span = lane_width, max_slot_span
         self.c.d_uniq_count, self.c.d_uniq, self.c.d_slots = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr()
+        self.c.d_row_count = row_count.data_ptr() if row_count is not None else None
+        self.c.n_entries = int(entries) if (entries is not None and row_count is not None) else 0
 
     tile_size = property(lambda self: self.c.tile_size)
     n_tiles = property(lambda self: self.c.n_tiles)
@@ -82,8 +92,11 @@ class TilePlanHandle:
         return C.pointer(self.c)
 
 
-def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0):
-    """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles)."""
+def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None):
+    """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles).
+    ``prune = (state, keep_rsq)``: drop the entries that cannot come inside the force's cutoff before the next rebuild
+    (``keep_rsq``: device Scalar tensor [T*T] of (r_cut + buffer)^2; the state's positions must be the ones the list was built
+    from)."""
     dev = nl.n_neigh.device
     if dev.type != "cuda":
         raise RuntimeError("tile plans are built on a CUDA device only (no CPU fallback)")
@@ -100,6 +113,14 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     a.size_nlist, a.N, a.tile_size, a.uniq_capacity, a.lane_width = nl.size_nlist, N, tile_size, uniq_capacity, lane_width
     a.group_width = group_width
     a.d_uniq_count, a.d_uniq, a.d_slots, a.d_status = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr(), status.data_ptr()
+    row_count = None
+    if prune is not None:
+        state, keep_rsq = prune
+        row_count = torch.zeros(max(N, 1), dtype=torch.int32, device=dev)
+        a.d_prune_pos, a.d_prune_rsq = nl._last_pos.data_ptr(), keep_rsq.data_ptr()
+        a.prune_scalar_bits, a.prune_ntypes = state.scalar_bits, len(state.types)
+        a.prune_box = state.box.as_abi()
+        a.d_row_count = row_count.data_ptr()
     max_uniq, max_span, overflow = C.c_uint(0), C.c_uint(0), C.c_uint(0)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -109,5 +130,6 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     e1.synchronize()
     if overflow.value:
         return None
+    entries = int(row_count.sum().item()) if row_count is not None else nl.size_nlist
     return TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, lane_width, max_span.value, uniq_count, uniq, slots,
-                          e0.elapsed_time(e1))
+                          e0.elapsed_time(e1), row_count, entries)

@@ -21,7 +21,9 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
     unsigned int tpp = a.pair.threads_per_particle;
     if (tpp == 0)
         {
-        const double nbar = a.pair.N ? (double)a.pair.size_nlist / (double)a.pair.N : 0.0;
+        // rows of a pruned plan are shorter than the list's
+        const size_t entries = (a.pair.tiles && a.pair.tiles->n_entries) ? a.pair.tiles->n_entries : a.pair.size_nlist;
+        const double nbar = a.pair.N ? (double)entries / (double)a.pair.N : 0.0;
         tpp = nbar <= 8 ? 1 : (nbar <= 16 ? 2 : (nbar <= 96 ? 4 : (nbar <= 256 ? 8 : 16)));
         }
     if (a.pair.tiles && a.pair.threads_per_particle == 0)

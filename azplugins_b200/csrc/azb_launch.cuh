@@ -37,7 +37,8 @@ template<class S> inline PairArgsDev<S> make_pair_args(const azb_pair_args& a)
     d.N = a.N;
     d.pos = (const typename vec4<S>::type*)a.d_pos;
     d.box = make_box<S>(a.box);
-    d.n_neigh = a.d_n_neigh;
+    // the tile kernels take a row's length from n_neigh; a pruned plan carries its own (shorter) row lengths
+    d.n_neigh = (a.tiles && a.tiles->d_row_count) ? a.tiles->d_row_count : a.d_n_neigh;
     d.nlist = a.d_nlist;
     d.head_list = a.d_head_list;
     d.rcutsq = (const S*)a.d_rcutsq;

@@ -7,11 +7,15 @@
 //   1. cell index per particle (locals + ghosts)                      cell_index_kernel
 //   2. stable radix sort of (cell, particle index)                    cub::DeviceRadixSort (plumbing)
 //   3. cell offsets (empty cells included) + cell-ordered copy of the positions    cell_bounds_kernel
-//   4. count pass: one warp per local particle walks the 9 (y, z) rows of its 27 neighbouring cells — the three x-cells of
-//      a row are one contiguous range of the cell-ordered copy, so the 32 lanes stay busy even at 8 particles per cell —
-//      testing r_list^2(type_i, type_j) and the exclusion row                                              nlist_kernel<COUNT>
+//   4. the walk: a group of 16 or 32 lanes per local particle, in cell order, over the 9 (y, z) rows of its 27 neighbouring
+//      cells — the three x-cells of a row are one contiguous range of the cell-ordered copy, each range with its periodic
+//      image shift — testing r_list^2(type_i, type_j) and the exclusion row. With a row-length bound from the previous build
+//      (row_stride_hint) ONE walk counts and writes fixed-stride temporary rows       nlist_kernel<MODE_SINGLE>
+//      otherwise (first build, or a row outgrew the bound) count ...                     nlist_kernel<MODE_COUNT>
 //   5. exclusive scan of the (row_align-padded) counts -> head_list    cub::DeviceScan
-//   6. fill pass: same walk, warp-ballot compaction keeps rows in deterministic cell-traversal order      nlist_kernel<FILL>
+//   6. ... and fill: same walk again, rows straight into nlist                           nlist_kernel<MODE_FILL>
+//      or, after the single walk, a streaming compaction of the temporary rows            nlist_compact_kernel
+//   Rows keep the deterministic cell-traversal order in every mode (ballot compaction, no atomics).
 #include <cub/cub.cuh>
 #include <thrust/iterator/transform_iterator.h>
 #include <cuda_runtime.h>
@@ -73,10 +77,9 @@ __global__ void cell_bounds_kernel(const unsigned int* __restrict__ cell_sorted,
 
 template<class S> struct NlistDev
     {
-    const typename vec4<S>::type* pos;
     const typename vec4<S>::type* pos_sorted;
     const unsigned int* idx_sorted;
-    const unsigned int* cell_of;
+    const unsigned int* cell_sorted;
     const unsigned int* cell_begin;
     const S* r_listsq;
     const size_t* excl_head;
@@ -85,23 +88,50 @@ template<class S> struct NlistDev
     const size_t* head_list;
     unsigned int* nlist;
     size_t capacity;
+    unsigned int* tmp_rows; // MODE_SINGLE: [N * row_stride] rows of fixed capacity, compacted afterwards
+    unsigned int row_stride;
+    unsigned int* overflow; // MODE_SINGLE: set when a row does not fit row_stride
     Box<S> box;
     CellGrid grid;
-    unsigned int N, ntypes;
+    unsigned int N, n_max, ntypes;
     };
 
-// FAST: fully periodic orthorhombic box (straight-line minimum image); SINGLE: one particle type (r_list^2 is one number);
-// EXCL: an exclusion table is present
-template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
+enum
     {
-    const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const unsigned int lane = threadIdx.x & 31u;
-    if (warp >= a.N)
-        return;
-    const unsigned int i = warp;
-    const auto pi = ld4(a.pos + i);
-    const unsigned int trow = type_of(pi.w) * a.ntypes;
-    unsigned int c = a.cell_of[i];
+    MODE_COUNT = 0, // n_neigh only (first build: row lengths unknown)
+    MODE_FILL = 1,  // rows into nlist at head_list (after MODE_COUNT + scan)
+    MODE_SINGLE = 2 // n_neigh AND rows, into fixed-stride temporary rows: one walk per rebuild instead of two
+    };
+
+// A group of G lanes (16 or 32) builds the row of one particle; groups run over the particles in CELL order, so neighbouring
+// groups walk the same candidate ranges (L1 hits) and a group's own data is a coalesced read. The 27-cell neighbourhood is
+// 9 (y, z) rows; the three x-cells of a row are ONE contiguous range of the cell-ordered copy (two where the row wraps around
+// the periodic boundary). IMG: every range carries the periodic image shift of its cells, so a candidate costs three
+// additions instead of a minimum-image computation — exact same arithmetic result as rint(dx / L) for every pair that can
+// be inside r_list (which needs >= 3 cells along every periodic direction; otherwise the general minimum image is used).
+// SINGLE_TYPE: one particle type (r_list^2 is one number); EXCL: an exclusion table is present.
+template<class S, int MODE, bool IMG, bool SINGLE_TYPE, bool EXCL, int G>
+__global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
+    {
+    constexpr unsigned int FULL = 0xffffffffu;
+    const unsigned int gthread = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int s_own = gthread / G; // position in cell order
+    const unsigned int lane = threadIdx.x % G;
+    const unsigned int gshift = (threadIdx.x & 31u) & ~(unsigned int)(G - 1);
+    const unsigned int gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << gshift;
+    const unsigned int ltmask = ((1u << lane) - 1u) << gshift;
+    unsigned int i = 0xffffffffu;
+    if (s_own < a.n_max)
+        i = a.idx_sorted[s_own];
+    const bool active = i < a.N; // ghosts get no row
+    typename vec4<S>::type pi = {};
+    unsigned int c = 0;
+    if (active)
+        {
+        pi = ld4(a.pos_sorted + s_own);
+        c = a.cell_sorted[s_own];
+        }
+    const unsigned int trow = SINGLE_TYPE ? 0u : type_of(pi.w) * a.ntypes;
     const int cx = c % a.grid.nc[0];
     c /= a.grid.nc[0];
     const int cy = c % a.grid.nc[1];
@@ -117,31 +147,63 @@ template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void 
         hi_o[d] = (per && a.grid.nc[d] < 2) ? 0 : 1;
         }
     size_t ex0 = 0, ex1 = 0;
-    if (EXCL)
+    if (EXCL && active)
         {
         ex0 = a.excl_head[i];
         ex1 = a.excl_head[i + 1];
         }
-    const S rl_single = SINGLE ? a.r_listsq[0] : S(0);
+    const S rl_single = SINGLE_TYPE ? a.r_listsq[0] : S(0);
     unsigned int count = 0;
-    unsigned int* row = FILL ? a.nlist + a.head_list[i] : nullptr;
-    const size_t row_cap = FILL ? a.capacity - a.head_list[i] : 0;
+    unsigned int* row = nullptr;
+    size_t row_cap = 0;
+    if (MODE == MODE_FILL && active)
+        {
+        row = a.nlist + a.head_list[i];
+        row_cap = a.capacity - a.head_list[i];
+        }
+    if (MODE == MODE_SINGLE && active)
+        {
+        row = a.tmp_rows + (size_t)i * a.row_stride;
+        row_cap = a.row_stride;
+        }
 
-    // Lane r < 9 prepares the (y, z) row r = 3 (oz + 1) + (oy + 1) of the 27-cell neighbourhood: the cells x-1, x, x+1 of a row
-    // are consecutive in cell order, so a row is ONE range of the cell-ordered copy, or two where it wraps around the periodic
-    // boundary (visited x-1, x, x+1: the list's row order). All cell_begin loads of a particle are in flight together.
+    // Lane r < 9 prepares the (y, z) row r = 3 (oz + 1) + (oy + 1): ranges a (cells x-1.. in the list's row order) and b (the part
+    // of the row on the other side of the periodic boundary), with the image shifts of the row (y, z) and of each range (x).
     unsigned int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-    if (lane < 9u)
+    S shy = S(0), shz = S(0), shxa = S(0), shxb = S(0);
+    if (lane < 9u && active)
         {
         const int oz = (int)lane / 3 - 1, oy = (int)lane % 3 - 1;
         bool ok = oz >= lo_o[2] && oz <= hi_o[2] && oy >= lo_o[1] && oy <= hi_o[1];
         int z = ci[2] + oz, y = ci[1] + oy;
         if ((a.grid.periodic >> 2) & 1u)
-            z += z < 0 ? a.grid.nc[2] : (z >= a.grid.nc[2] ? -a.grid.nc[2] : 0);
+            {
+            if (z < 0)
+                {
+                z += a.grid.nc[2];
+                shz = a.box.Lz; // the cells sit one box length above their image next to me: d = (pi - pj) + L
+                }
+            else if (z >= a.grid.nc[2])
+                {
+                z -= a.grid.nc[2];
+                shz = -a.box.Lz;
+                }
+            }
         else
             ok = ok && z >= 0 && z < a.grid.nc[2];
         if ((a.grid.periodic >> 1) & 1u)
-            y += y < 0 ? a.grid.nc[1] : (y >= a.grid.nc[1] ? -a.grid.nc[1] : 0);
+            {
+            if (y < 0)
+                {
+                y += a.grid.nc[1];
+                shy = a.box.Ly;
+                }
+            else if (y >= a.grid.nc[1])
+                {
+                y -= a.grid.nc[1];
+                shy = -a.box.Ly;
+                }
+            }
         else
             ok = ok && y >= 0 && y < a.grid.nc[1];
         if (ok)
@@ -154,6 +216,7 @@ template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void 
                     {
                     a0 = a.cell_begin[rb + xlo + a.grid.nc[0]];
                     a1 = a.cell_begin[rb + a.grid.nc[0]];
+                    shxa = a.box.Lx;
                     b0 = a.cell_begin[rb];
                     b1 = a.cell_begin[rb + xhi + 1];
                     }
@@ -163,6 +226,7 @@ template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void 
                     a1 = a.cell_begin[rb + a.grid.nc[0]];
                     b0 = a.cell_begin[rb];
                     b1 = a.cell_begin[rb + xhi - a.grid.nc[0] + 1];
+                    shxb = -a.box.Lx;
                     }
                 else
                     {
@@ -179,66 +243,119 @@ template<class S, bool FILL, bool FAST, bool SINGLE, bool EXCL> __global__ void 
                 }
             }
         }
-    auto visit = [&](unsigned int s0, unsigned int s1)
+    auto visit = [&](unsigned int s0, unsigned int s1, const S sx, const S sy, const S sz)
     {
-        for (unsigned int base = s0; base < s1; base += 32)
+        // trip count uniform over the warp (two groups of 16 share it: the ballots below are warp-wide)
+        unsigned int len = s1 - s0;
+        if (G < 32)
+            len = max(len, __shfl_xor_sync(FULL, len, 16));
+        for (unsigned int off = 0; off < len; off += G)
             {
-            const unsigned int s = base + lane;
+            const unsigned int s = s0 + off + lane;
             bool take = false;
-            unsigned int j = 0;
             if (s < s1)
                 {
-                j = a.idx_sorted[s];
                 const auto pj = ld4(a.pos_sorted + s);
                 S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                if (FAST)
-                    min_image_ortho(a.box, dx, dy, dz);
+                if (IMG)
+                    {
+                    dx += sx;
+                    dy += sy;
+                    dz += sz;
+                    }
                 else
                     min_image(a.box, dx, dy, dz);
-                const S rl = SINGLE ? rl_single : a.r_listsq[trow + type_of(pj.w)];
-                take = (j != i) && (rl > S(0)) && (dx * dx + dy * dy + dz * dz < rl);
-                if (EXCL && take)
+                const S rl = SINGLE_TYPE ? rl_single : a.r_listsq[trow + type_of(pj.w)];
+                take = (s != s_own) && (rl > S(0)) && (dx * dx + dy * dy + dz * dz < rl);
+                }
+            unsigned int j = 0;
+            if ((MODE != MODE_COUNT || EXCL) && take)
+                {
+                j = a.idx_sorted[s];
+                if (EXCL)
                     for (size_t e = ex0; e < ex1; ++e)
                         if (a.excl_list[e] == j)
                             take = false;
                 }
-            const unsigned int m = __ballot_sync(0xffffffffu, take);
-            if constexpr (FILL)
+            const unsigned int m = __ballot_sync(FULL, take);
+            if (MODE != MODE_COUNT)
                 {
-                const unsigned int slot = count + __popc(m & ((1u << lane) - 1u));
+                const unsigned int slot = count + __popc(m & ltmask);
                 if (take && slot < row_cap)
                     row[slot] = j;
                 }
-            count += __popc(m);
+            count += __popc(m & gmask);
             }
     };
 #pragma unroll 1
     for (int r = 0; r < 9; ++r)
         {
-        visit(__shfl_sync(0xffffffffu, a0, r), __shfl_sync(0xffffffffu, a1, r));
-        visit(__shfl_sync(0xffffffffu, b0, r), __shfl_sync(0xffffffffu, b1, r));
+        const int src = (int)gshift + r;
+        const S sy = __shfl_sync(FULL, shy, src), sz = __shfl_sync(FULL, shz, src);
+        visit(__shfl_sync(FULL, a0, src), __shfl_sync(FULL, a1, src), __shfl_sync(FULL, shxa, src), sy, sz);
+        visit(__shfl_sync(FULL, b0, src), __shfl_sync(FULL, b1, src), __shfl_sync(FULL, shxb, src), sy, sz);
         }
-    if (!FILL && lane == 0)
+    if (MODE != MODE_FILL && lane == 0 && active)
+        {
         a.n_neigh[i] = count;
+        if (MODE == MODE_SINGLE && count > a.row_stride)
+            atomicExch(a.overflow, 1u);
+        }
     }
 
-template<class S, bool FILL> static void launch_nlist_kernel(const NlistDev<S>& d, unsigned int grid, cudaStream_t stream)
+// MODE_SINGLE, second half: fixed-stride temporary rows -> the packed HOOMD rows at head_list (pure streaming copy)
+__global__ void __launch_bounds__(256) nlist_compact_kernel(const unsigned int* __restrict__ tmp_rows, unsigned int row_stride,
+                                                            const unsigned int* __restrict__ n_neigh, const size_t* __restrict__ head_list,
+                                                            unsigned int N, unsigned int* __restrict__ nlist, size_t capacity)
     {
-    const bool fast = d.box.flags == 7u, single = d.ntypes == 1, excl = d.excl_head != nullptr;
-#define AZB_NL(F, T, E) nlist_kernel<S, FILL, F, T, E><<<grid, 128, 0, stream>>>(d)
+    const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (warp >= N)
+        return;
+    const unsigned int nn = n_neigh[warp];
+    const size_t head = head_list[warp];
+    const unsigned int* src = tmp_rows + (size_t)warp * row_stride;
+    for (unsigned int k = lane; k < nn; k += 32)
+        if (head + k < capacity)
+            nlist[head + k] = src[k];
+    }
+
+template<class S, int MODE> static void launch_nlist_kernel(const NlistDev<S>& d, bool img, double mean_range, cudaStream_t stream)
+    {
+    const bool single = d.ntypes == 1, excl = d.excl_head != nullptr;
+    // lanes per particle: 16 when a candidate range (three cells) holds fewer than ~48 particles, so that the tail of a range
+    // does not idle half a warp
+    const bool narrow = mean_range < 48.0;
+    const unsigned int g = narrow ? 16u : 32u;
+    const unsigned int grid = (unsigned int)(((size_t)d.n_max * g + 127) / 128);
+#define AZB_NL(I, T, E)                                                                   \
+    do                                                                                    \
+        {                                                                                 \
+        if (narrow)                                                                       \
+            nlist_kernel<S, MODE, I, T, E, 16><<<grid, 128, 0, stream>>>(d);              \
+        else                                                                              \
+            nlist_kernel<S, MODE, I, T, E, 32><<<grid, 128, 0, stream>>>(d);              \
+        } while (0)
     if (excl)
         {
-        if (fast)
-            single ? AZB_NL(true, true, true) : AZB_NL(true, false, true);
+        if (img && single)
+            AZB_NL(true, true, true);
+        else if (img)
+            AZB_NL(true, false, true);
+        else if (single)
+            AZB_NL(false, true, true);
         else
-            single ? AZB_NL(false, true, true) : AZB_NL(false, false, true);
+            AZB_NL(false, false, true);
         }
     else
         {
-        if (fast)
-            single ? AZB_NL(true, true, false) : AZB_NL(true, false, false);
+        if (img && single)
+            AZB_NL(true, true, false);
+        else if (img)
+            AZB_NL(true, false, false);
+        else if (single)
+            AZB_NL(false, true, false);
         else
-            single ? AZB_NL(false, true, false) : AZB_NL(false, false, false);
+            AZB_NL(false, false, false);
         }
 #undef AZB_NL
     }
@@ -268,6 +385,8 @@ struct Workspace
     unsigned int *cell, *idx, *cell_sorted, *idx_sorted, *cell_begin;
     void* pos_sorted;
     size_t* total;
+    unsigned int* flags;    // [0] overflow of a fixed-stride row, [1] 1 = the single-walk rows are valid (fill only compacts)
+    unsigned int* tmp_rows; // [N * row_stride] when row_stride_hint > 0
     void* cub_tmp;
     size_t cub_bytes;
     size_t bytes;
@@ -307,7 +426,16 @@ static int make_grid(const azb_nlist_args& a, CellGrid& g, size_t& ncell)
     return 0;
     }
 
-static Workspace carve(void* base, unsigned int n_max, size_t ncell, size_t scalar4_bytes, size_t cub_bytes)
+// image shifts per candidate range are the minimum image only with >= 3 cells along every periodic direction
+static bool image_shifts_ok(const CellGrid& g)
+    {
+    for (int d = 0; d < 3; ++d)
+        if (((g.periodic >> d) & 1u) && g.nc[d] < 3)
+            return false;
+    return true;
+    }
+
+static Workspace carve(void* base, unsigned int n_max, unsigned int N, size_t ncell, size_t scalar4_bytes, size_t cub_bytes, unsigned int row_stride)
     {
     Workspace w;
     char* p = (char*)base;
@@ -325,8 +453,10 @@ static Workspace carve(void* base, unsigned int n_max, size_t ncell, size_t scal
     w.cell_begin = (unsigned int*)take(4 * (ncell + 2));
     w.pos_sorted = take(scalar4_bytes * n);
     w.total = (size_t*)take(sizeof(size_t));
+    w.flags = (unsigned int*)take(2 * sizeof(unsigned int));
     w.cub_tmp = take(cub_bytes);
     w.cub_bytes = cub_bytes;
+    w.tmp_rows = row_stride ? (unsigned int*)take(4 * (size_t)row_stride * (N ? N : 1)) : nullptr;
     w.bytes = off;
     return w;
     }
@@ -341,6 +471,38 @@ static size_t cub_temp_bytes(unsigned int n_max, unsigned int N)
     return sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
     }
 
+template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Workspace& w, const CellGrid& g)
+    {
+    typedef typename vec4<S>::type s4;
+    NlistDev<S> d;
+    d.pos_sorted = (const s4*)w.pos_sorted;
+    d.idx_sorted = w.idx_sorted;
+    d.cell_sorted = w.cell_sorted;
+    d.cell_begin = w.cell_begin;
+    d.r_listsq = (const S*)a.d_r_listsq;
+    d.excl_head = a.d_excl_head;
+    d.excl_list = a.d_excl_list;
+    d.n_neigh = a.d_n_neigh;
+    d.head_list = a.d_head_list;
+    d.nlist = a.d_nlist;
+    d.capacity = a.capacity;
+    d.tmp_rows = w.tmp_rows;
+    d.row_stride = a.row_stride_hint;
+    d.overflow = w.flags;
+    d.box = make_box<S>(a.box);
+    d.grid = g;
+    d.N = a.N;
+    d.n_max = a.n_max;
+    d.ntypes = a.ntypes;
+    return d;
+    }
+
+static double mean_range_population(const azb_nlist_args& a, const CellGrid& g, size_t ncell)
+    {
+    const int span = g.nc[0] >= 3 ? 3 : g.nc[0];
+    return (double)a.n_max / (double)ncell * span;
+    }
+
 template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_total, cudaStream_t stream)
     {
     CellGrid g;
@@ -349,10 +511,13 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     if (rc)
         return rc;
     const size_t cub_bytes = cub_temp_bytes(a.n_max, a.N);
-    Workspace w = carve(a.d_workspace, a.n_max, ncell, sizeof(typename vec4<S>::type), cub_bytes);
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_bytes, a.row_stride_hint);
     if (w.bytes > a.workspace_bytes)
         return AZB_ERR_BAD_ARGUMENT;
     typedef typename vec4<S>::type s4;
+    cudaError_t e = cudaMemsetAsync(w.flags, 0, 2 * sizeof(unsigned int), stream);
+    if (e != cudaSuccess)
+        return (int)e;
     if (a.n_max)
         {
         const unsigned int blk = 256, grd = (a.n_max + blk - 1) / blk;
@@ -365,38 +530,38 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
         cell_bounds_kernel<S><<<grd, blk, 0, stream>>>(w.cell_sorted, w.idx_sorted, a.n_max, (const s4*)a.d_pos, (s4*)w.pos_sorted, w.cell_begin,
                                                         (unsigned int)ncell);
         }
-    NlistDev<S> d;
-    d.pos = (const s4*)a.d_pos;
-    d.pos_sorted = (const s4*)w.pos_sorted;
-    d.idx_sorted = w.idx_sorted;
-    d.cell_of = w.cell;
-    d.cell_begin = w.cell_begin;
-    d.r_listsq = (const S*)a.d_r_listsq;
-    d.excl_head = a.d_excl_head;
-    d.excl_list = a.d_excl_list;
-    d.n_neigh = a.d_n_neigh;
-    d.head_list = a.d_head_list;
-    d.nlist = a.d_nlist;
-    d.capacity = a.capacity;
-    d.box = make_box<S>(a.box);
-    d.grid = g;
-    d.N = a.N;
-    d.ntypes = a.ntypes;
+    const NlistDev<S> d = make_dev<S>(a, w, g);
+    const bool img = image_shifts_ok(g);
+    const double range = mean_range_population(a, g, ncell);
     const unsigned int align = a.row_align ? a.row_align : 1;
+    const bool single_walk = a.row_stride_hint > 0;
     if (a.N)
         {
-        const unsigned int grd = (a.N + 3) / 4;
-        launch_nlist_kernel<S, false>(d, grd, stream);
+        if (single_walk)
+            launch_nlist_kernel<S, MODE_SINGLE>(d, img, range, stream);
+        else
+            launch_nlist_kernel<S, MODE_COUNT>(d, img, range, stream);
         thrust::transform_iterator<PadTo, const unsigned int*, size_t> it(a.d_n_neigh, PadTo {align});
         size_t tmp = w.cub_bytes;
         cub::DeviceScan::ExclusiveSum(w.cub_tmp, tmp, it, a.d_head_list, (int)a.N, stream);
         }
     total_kernel<<<1, 32, 0, stream>>>(a.d_n_neigh, a.d_head_list, a.N, align, w.total);
-    cudaError_t e = cudaMemcpyAsync(h_total, w.total, sizeof(size_t), cudaMemcpyDeviceToHost, stream);
+    unsigned int h_flags[2] = {0, 0};
+    e = cudaMemcpyAsync(h_total, w.total, sizeof(size_t), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(h_flags, w.flags, sizeof(h_flags), cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess)
         e = cudaStreamSynchronize(stream);
     if (e == cudaSuccess)
         e = cudaGetLastError();
+    if (e == cudaSuccess && single_walk && a.N)
+        {
+        // rows that all fitted their fixed stride are final: azb_nlist_fill only compacts them. Otherwise it walks again.
+        const unsigned int valid = h_flags[0] ? 0u : 1u;
+        e = cudaMemcpyAsync(w.flags + 1, &valid, sizeof(valid), cudaMemcpyHostToDevice, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        }
     return (int)e;
     }
 
@@ -407,29 +572,28 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     int rc = make_grid(a, g, ncell);
     if (rc)
         return rc;
-    Workspace w = carve(a.d_workspace, a.n_max, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N));
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N), a.row_stride_hint);
     if (w.bytes > a.workspace_bytes || (a.N && !a.d_nlist))
         return AZB_ERR_BAD_ARGUMENT;
-    typedef typename vec4<S>::type s4;
-    NlistDev<S> d;
-    d.pos = (const s4*)a.d_pos;
-    d.pos_sorted = (const s4*)w.pos_sorted;
-    d.idx_sorted = w.idx_sorted;
-    d.cell_of = w.cell;
-    d.cell_begin = w.cell_begin;
-    d.r_listsq = (const S*)a.d_r_listsq;
-    d.excl_head = a.d_excl_head;
-    d.excl_list = a.d_excl_list;
-    d.n_neigh = a.d_n_neigh;
-    d.head_list = a.d_head_list;
-    d.nlist = a.d_nlist;
-    d.capacity = a.capacity;
-    d.box = make_box<S>(a.box);
-    d.grid = g;
-    d.N = a.N;
-    d.ntypes = a.ntypes;
-    if (a.N)
-        launch_nlist_kernel<S, true>(d, (a.N + 3) / 4, stream);
+    if (!a.N)
+        return 0;
+    unsigned int valid = 0;
+    if (a.row_stride_hint)
+        {
+        cudaError_t e = cudaMemcpyAsync(&valid, w.flags + 1, sizeof(valid), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess)
+            return (int)e;
+        }
+    if (valid)
+        {
+        const unsigned int grd = (unsigned int)(((size_t)a.N * 32 + 255) / 256);
+        nlist_compact_kernel<<<grd, 256, 0, stream>>>(w.tmp_rows, a.row_stride_hint, a.d_n_neigh, a.d_head_list, a.N, a.d_nlist, a.capacity);
+        return (int)cudaGetLastError();
+        }
+    const NlistDev<S> d = make_dev<S>(a, w, g);
+    launch_nlist_kernel<S, MODE_FILL>(d, image_shifts_ok(g), mean_range_population(a, g, ncell), stream);
     return (int)cudaGetLastError();
     }
     } // namespace azb
@@ -445,7 +609,7 @@ extern "C"
         const int rc = azb::make_grid(*a, g, ncell);
         if (rc)
             return rc;
-        *bytes = azb::carve(nullptr, a->n_max, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N)).bytes;
+        *bytes = azb::carve(nullptr, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint).bytes;
         return 0;
         }
 

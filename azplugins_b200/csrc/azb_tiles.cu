@@ -11,18 +11,71 @@
 #include <stdint.h>
 
 #include "azb200.h"
+#include "azb_launch.cuh"
+#include "azb_math.cuh"
 
 namespace azb
     {
 constexpr unsigned int EMPTY_KEY = 0xffffffffu;
+
+// Pruning test of one list entry (azb_tile_build_args.d_prune_pos): was the pair within r_cut(ti, tj) + r_buff when the list was
+// built? A hair of slack keeps the test conservative against the rounding of the cutoff test the force kernel will make.
+template<class S> struct PruneDev
+    {
+    const typename vec4<S>::type* pos;
+    const S* keep_rsq;
+    unsigned int ntypes;
+    Box<S> box;
+    };
+struct NoPrune
+    {
+    };
+template<class S> __device__ __forceinline__ bool keep_entry(const PruneDev<S>& p, const typename vec4<S>::type& pi, unsigned int trow, unsigned int j)
+    {
+    const auto pj = ld4(p.pos + j);
+    S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+    min_image(p.box, dx, dy, dz);
+    const S lim = p.keep_rsq[trow + type_of(pj.w)];
+    return dx * dx + dy * dy + dz * dz <= lim * S(1.00001);
+    }
 
 __device__ __forceinline__ unsigned int tile_hash(unsigned int j, unsigned int shift)
     {
     return (j * 2654435761u) >> shift;
     }
 
+struct NoOwn
+    {
+    };
+__device__ __forceinline__ NoOwn load_own(const NoPrune&, unsigned int)
+    {
+    return NoOwn();
+    }
+__device__ __forceinline__ bool kept(const NoPrune&, const NoOwn&, unsigned int)
+    {
+    return true;
+    }
+template<class S> struct Own
+    {
+    typename vec4<S>::type pi;
+    unsigned int trow;
+    };
+template<class S> __device__ __forceinline__ Own<S> load_own(const PruneDev<S>& p, unsigned int i)
+    {
+    Own<S> o;
+    o.pi = ld4(p.pos + i);
+    o.trow = type_of(o.pi.w) * p.ntypes;
+    return o;
+    }
+template<class S> __device__ __forceinline__ bool kept(const PruneDev<S>& p, const Own<S>& o, unsigned int j)
+    {
+    return keep_entry(p, o.pi, o.trow, j);
+    }
+
 // dynamic shared memory: keys[hcap] u32 | list[ucap] u32 | vals[hcap] u16
-__global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __restrict__ n_neigh,
+template<class Prune>
+__global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, unsigned int* __restrict__ row_count,
+                                                          const unsigned int* __restrict__ n_neigh,
                                                           const unsigned int* __restrict__ nlist,
                                                           const size_t* __restrict__ head_list,
                                                           const unsigned int N,
@@ -36,7 +89,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
                                                           uint16_t* __restrict__ slots,
                                                           unsigned int* __restrict__ status)
     {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(32) unsigned char smem_raw[];
     const unsigned int hcap = 1u << hcap_log2;
     const unsigned int hmask = hcap - 1u;
     const unsigned int hshift = 32u - hcap_log2;
@@ -64,17 +117,26 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         {
         const unsigned int nn = n_neigh[i];
         const unsigned int* row = nlist + head_list[i];
+        decltype(load_own(prune, i)) own = load_own(prune, i);
         for (unsigned int k = lane; k < nn; k += 32)
             {
             const unsigned int j = row[k];
+            if (!kept(prune, own, j))
+                continue;
             unsigned int h = tile_hash(j, hshift);
             while (*(volatile unsigned int*)&s_count <= ucap)
                 {
-                const unsigned int old = atomicCAS(&keys[h], EMPTY_KEY, j);
+                // most entries are repeats (every neighbour is shared by 6-12 rows of the tile): a plain read finds them
+                // without an atomic; only an empty cell is claimed with a CAS
+                unsigned int old = *(volatile unsigned int*)&keys[h];
                 if (old == EMPTY_KEY)
                     {
-                    atomicAdd(&s_count, 1u);
-                    break;
+                    old = atomicCAS(&keys[h], EMPTY_KEY, j);
+                    if (old == EMPTY_KEY)
+                        {
+                        atomicAdd(&s_count, 1u);
+                        break;
+                        }
                     }
                 if (old == j)
                     break;
@@ -164,21 +226,39 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const unsigned int* __
         const unsigned int nnp = (nn + M - 1u) / M * M;
         if (G == 0u)
             {
-            // plain order: slot row = list row
-            for (unsigned int e = lane; e < nnp; e += 32)
+            // plain order: slot row = list row (the kept entries of it, in list order, when pruning)
+            decltype(load_own(prune, i)) own = load_own(prune, i);
+            unsigned int out_n = 0;
+            for (unsigned int e0 = 0; e0 < nn; e0 += 32)
                 {
-                uint16_t v = 0;
+                const unsigned int e = e0 + lane;
+                unsigned int j = 0;
+                bool keep = false;
                 if (e < nn)
                     {
-                    const unsigned int j = nlist[head + e];
+                    j = nlist[head + e];
+                    keep = kept(prune, own, j);
+                    }
+                const unsigned int m = __ballot_sync(0xffffffffu, keep);
+                if (keep)
+                    {
                     unsigned int h = tile_hash(j, hshift);
                     while (keys[h] != j)
                         h = (h + 1u) & hmask;
-                    v = vals[h];
+                    const unsigned int o = out_n + __popc(m & ((1u << lane) - 1u));
+                    const unsigned int r = o % M;
+                    slots[shead + (o - r) + 4u * (r % W) + r / W] = vals[h];
                     }
-                const unsigned int r = e % M;
-                slots[shead + (e - r) + 4u * (r % W) + r / W] = v;
+                out_n += __popc(m);
                 }
+            const unsigned int out_p = (out_n + M - 1u) / M * M;
+            for (unsigned int o = out_n + lane; o < out_p; o += 32) // padding
+                {
+                const unsigned int r = o % M;
+                slots[shead + (o - r) + 4u * (r % W) + r / W] = 0;
+                }
+            if (row_count && lane == 0)
+                row_count[i] = out_n;
             }
         else
             {
@@ -287,15 +367,36 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
     cudaError_t err = cudaMemsetAsync(a->d_status, 0, 4 * sizeof(unsigned int), s);
     if (err != cudaSuccess)
         return (int)err;
-    if (smem > 48 * 1024)
-        {
-        err = cudaFuncSetAttribute(azb::tiles_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (err != cudaSuccess)
-            return (int)err;
-        }
     const unsigned int n_tiles = (a->N + ts - 1) / ts;
-    azb::tiles_build_kernel<<<n_tiles, 256, smem, s>>>(a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, ucap, hcap_log2, W, G, a->d_uniq_count,
-                                                      a->d_uniq, a->d_slots, a->d_status);
+    const bool prune = a->d_prune_pos != nullptr;
+    if (prune && (!a->d_prune_rsq || !a->d_row_count || a->prune_ntypes == 0 || G != 0u || (a->prune_scalar_bits != 32 && a->prune_scalar_bits != 64)))
+        return AZB_ERR_BAD_ARGUMENT;
+#define AZB_TILES_LAUNCH(PRUNE_T, PRUNE_V)                                                                                              \
+    do                                                                                                                                  \
+        {                                                                                                                               \
+        if (smem > 48 * 1024)                                                                                                           \
+            {                                                                                                                           \
+            err = cudaFuncSetAttribute(azb::tiles_build_kernel<PRUNE_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
+            if (err != cudaSuccess)                                                                                                     \
+                return (int)err;                                                                                                        \
+            }                                                                                                                           \
+        azb::tiles_build_kernel<PRUNE_T><<<n_tiles, 256, smem, s>>>(PRUNE_V, a->d_row_count, a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, \
+                                                                   ucap, hcap_log2, W, G, a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status); \
+        } while (0)
+    if (!prune)
+        AZB_TILES_LAUNCH(azb::NoPrune, azb::NoPrune());
+    else if (a->prune_scalar_bits == 32)
+        {
+        azb::PruneDev<float> p = {(const float4*)a->d_prune_pos, (const float*)a->d_prune_rsq, a->prune_ntypes, azb::make_box<float>(a->prune_box)};
+        AZB_TILES_LAUNCH(azb::PruneDev<float>, p);
+        }
+    else
+        {
+        azb::PruneDev<double> p = {(const azb::double4a*)a->d_prune_pos, (const double*)a->d_prune_rsq, a->prune_ntypes,
+                                   azb::make_box<double>(a->prune_box)};
+        AZB_TILES_LAUNCH(azb::PruneDev<double>, p);
+        }
+#undef AZB_TILES_LAUNCH
     err = cudaGetLastError();
     if (err != cudaSuccess)
         return (int)err;

@@ -151,8 +151,33 @@ class Pair(Force):
             return None
         st, nl = self._state, self.nlist
         nbar = nl.mean_neighbors(st.N)
+        prune, prune_key = self._prune_spec()
         return nl.tile_plan(st.N, self.tile_size or self._auto_tile_size(nbar), lane_width=self._slot_lane_width(nbar),
-                            group_width=self._group_width(nbar))
+                            group_width=self._group_width(nbar) if prune is None else 0, prune=prune, prune_key=prune_key)
+
+    # A force whose cutoffs are smaller than the list's (several forces sharing one list) walks a PRUNED view of it: entries
+    # that were farther apart than r_cut + buffer when the list was built cannot be inside r_cut before the next rebuild
+    # (HOOMD rebuilds before anything has moved buffer / 2). Only worth a plan of its own when it drops a fair share.
+    prune_lists = True
+    _PRUNE_MIN_GAIN = 0.85
+
+    def _prune_spec(self):
+        st, nl = self._state, self.nlist
+        if not self.prune_lists or os.environ.get("AZB_NO_PRUNE", "0") == "1" or st is None or getattr(nl, "_last_pos", None) is None:
+            return None, None
+        rc = self._r_cut_matrix(st.types)
+        rl = nl.r_list(st.types)  # r_cut_max + buffer over all consumers of the list
+        keep = np.where(rc > 0, rc + nl.buffer, 0.0)
+        active = rl > 0
+        if not np.any(active) or np.all(keep[active] ** 3 >= self._PRUNE_MIN_GAIN * rl[active] ** 3):
+            return None, None
+        cached = getattr(self, "_prune_cache", None)
+        key = (id(st), st.scalar_bits, tuple(np.round(keep.reshape(-1), 12)))
+        if cached is None or cached[0] != key:
+            ftype = scalar_dtype(st.scalar_bits)[0]
+            k = keep.astype(ftype)
+            self._prune_cache = (key, torch.from_numpy((k * k).reshape(-1)).to(st.device))
+        return (st, self._prune_cache[1]), key
 
     def _auto_tile_size(self, nbar):
         """128 particles per tile for every kernel family. (With 256-thread CTAs, 256-particle tiles were 2 % faster for

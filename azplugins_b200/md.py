@@ -111,7 +111,7 @@ class Integrator:
         self._flag.zero_()
         for nl in lists:
             last = getattr(nl, "_last_pos", None)
-            if nl.n_neigh is None or last is None or nl._state is not st or last.shape[0] != st.N:
+            if nl.n_neigh is None or last is None or nl._state is not st or last.shape[0] != st.pos.shape[0]:
                 continue  # the force builds it on first use
             box = st.box.as_abi()
             half = 0.5 * nl.buffer

@@ -32,20 +32,22 @@ class NeighborList:
     def invalidate(self):
         self.n_neigh = None
         self._tiles = {}
+        self._last_pos = None
 
-    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0):
+    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0, prune=None, prune_key=None):
         """Tile plan of the current arrays (``azb_tiles_build``), built once per list rebuild and cached; ``None`` when a
-        tile holds more than ``uniq_capacity`` distinct neighbours even at the smallest tile size. ``lane_width`` is the
+        tile holds more than ``uniq_capacity`` distinct neighbours even at the smallest tile size. ``prune`` /
+        ``prune_key``: see ``_nlist_gpu.build_tile_plan`` (a pruned plan is specific to the cutoffs of one force). ``lane_width`` is the
         slot-row layout: 1 for the DPD kernels, the lanes per particle for the pair kernels; ``group_width`` the lanes per
         particle of the kernel that walks the rows (bank rotation of the row order; 0 = ``lane_width``)."""
-        key = (int(tile_size), int(uniq_capacity), int(lane_width), int(group_width))
+        key = (int(tile_size), int(uniq_capacity), int(lane_width), int(group_width), prune_key)
         if key not in self._tiles:
             from . import _nlist_gpu
 
             plan = None
             ts = int(tile_size)
             while plan is None and ts >= 32:
-                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width))
+                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width), prune)
                 ts //= 2
             self._tiles[key] = plan
         return self._tiles[key]
@@ -68,6 +70,7 @@ class NeighborList:
         self.nlist = torch.from_numpy(nlist.view(np.int32) if nlist.size else np.zeros(1, np.int32)).to(device)
         self.size_nlist = int(nlist.size)
         self._tiles = {}
+        self._last_pos = None  # positions at build time unknown: no displacement check, no pruned plans
         return self
 
     def compute(self, state):

@@ -189,7 +189,7 @@ def make_workload(name, n_override, rank=0):
             return [d, y]
 
         return (f"C5 DPDGeneralWeight r_cut=1.0 + ExpandedYukawa r_cut=2.0 on one neighbour list, N={snap.N} rho=1.0 buffer=0.4 "
-                "(roofline: the DPD kernel)"), snap, setup, 0.4
+                "(roofline: the slower of the two kernels)"), snap, setup, 0.4
     raise ValueError(name)
 
 
@@ -591,10 +591,22 @@ class Rig:
                 nbar = float(st.bond_table()["n_bonds"].sum().item()) / max(st.N, 1)
             else:
                 nbar = self.nbar
+            plan = getattr(f, "_plan", None)
+            pruned = plan is not None and plan.row_count is not None
+            if pruned:
+                # a force walking a pruned view of the list (azb_tile_build_args.d_prune_pos) is charged for the entries its view
+                # holds, not for the list's: the conservative reading of SURVEY.md §8 d's "4 n" term
+                nbar = plan.entries / max(st.N, 1)
             bpp = algorithmic_bytes_per_particle(f, nbar, self.bits, self.virial)
             ms = float(kern_ms[..., fi].mean())
             ach = st.N * bpp / (ms * 1e-3) / 1e9
-            out.append({"kernel": type(f).__name__, "kernel_ms": ms, "bytes_per_particle": bpp, "achieved": ach, "frac": ach / peak})
+            rec = {"kernel": type(f).__name__, "kernel_ms": ms, "bytes_per_particle": bpp, "achieved": ach, "frac": ach / peak,
+                   "entries_per_particle": nbar}
+            if pruned:
+                full = algorithmic_bytes_per_particle(f, self.nbar, self.bits, self.virial)
+                rec["pruned_view"] = {"list_entries_per_particle": self.nbar, "bytes_per_particle_full_list": full,
+                                      "frac_full_list": st.N * full / (ms * 1e-3) / 1e9 / peak}
+            out.append(rec)
         return out
 
 
@@ -605,15 +617,17 @@ def hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def roofs_from_profile(workload, bits, roofline):
+def roofs_from_profile(workload, bits, roofline, kernel):
     """The other two roofs SURVEY.md §8 d asks for — instruction issue and the L1 / shared-memory data pipe — cannot be measured
     from inside the process; they are taken from the committed ncu capture of this workload's dominant kernel
     (profiles/roofs_<workload>_f<bits>.json, written by tools/ncu_roofs.py from an `ncu --set full` report). `bound` names the
     largest of the three utilisations."""
     path = os.path.join(ROOT, "profiles", f"roofs_{workload}_f{bits}.json")
     fracs = {"hbm": roofline["frac"]}
-    if os.path.exists(path):
-        r = json.load(open(path))
+    r = json.load(open(path)) if os.path.exists(path) else None
+    if r is not None and r.get("kernel_class") not in (None, kernel):
+        r = None  # the capture is of another force object of this workload
+    if r is not None:
         roofline["traffic"] = r.get("dram_bytes_per_launch")
         roofline["issue_frac"] = r.get("issue_active_pct", 0.0) / 100.0
         roofline["l1_smem_frac"] = r.get("l1_data_pipe_pct", 0.0) / 100.0
@@ -786,13 +800,13 @@ def run_b200(args):
     # ---- roofline of the dominant kernel (forces[0]) -------------------------------------------------------------------------
     peak, peak_src = hbm_peak()
     recs = rig.kernel_records(kern_ms, peak)
-    dom = recs[0]
+    dom = max(recs, key=lambda r: r["kernel_ms"])  # the dominant kernel of the step = the slowest launch
     roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": None,
                 "kernel": dom["kernel"], "bytes_per_particle": dom["bytes_per_particle"], "mean_neighbors": rig.nbar, "kernel_ms": dom["kernel_ms"],
                 "peak_source": peak_src, "pair_visits_per_s": rig.nbar * st.N / (dom["kernel_ms"] * 1e-3), "kernels": recs,
                 "step_bytes_per_particle": sum(r["bytes_per_particle"] for r in recs),
                 "step_frac": st.N * sum(r["bytes_per_particle"] for r in recs) / (sum(r["kernel_ms"] for r in recs) * 1e-3) / 1e9 / peak}
-    roofs_from_profile(args.workload, args.bits, roofline)
+    roofs_from_profile(args.workload, args.bits, roofline, dom["kernel"])
 
     plan = forces[0]._plan
     tile_note = ("gathered from global memory" if plan is None else

@@ -130,6 +130,10 @@ typedef struct azb_tile_plan
     const unsigned int* d_uniq_count; /* [n_tiles] */
     const unsigned int* d_uniq;       /* [n_tiles * uniq_capacity] */
     const uint16_t* d_slots;          /* [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */
+    const unsigned int* d_row_count;  /* [N] entries of each slot row, or NULL = the list's n_neigh. Shorter than n_neigh for a
+                                         PRUNED plan (azb_tile_build_args.d_prune_pos): entries that cannot come inside this
+                                         force's cutoff before the next list rebuild are left out of its slot rows */
+    size_t n_entries;                 /* sum of the rows' lengths (0 = the list's size_nlist); launchers size their lane groups by it */
     } azb_tile_plan;
 
 /* mirrors HOOMD pair_args_t */
@@ -270,6 +274,11 @@ typedef struct azb_nlist_args
     size_t capacity;
     void* d_workspace;               /* >= azb_nlist_workspace_size bytes, 256-byte aligned */
     size_t workspace_bytes;
+    unsigned int row_stride_hint;    /* 0: two walks (count, then fill). > 0: an upper bound on the row length, e.g. 1.2 x the longest
+                                        row of the previous build: azb_nlist_count then counts AND writes fixed-stride rows into the
+                                        workspace in ONE walk and azb_nlist_fill only compacts them; a row that outgrows the bound
+                                        makes azb_nlist_fill walk again (same result, deterministic row order either way). The
+                                        workspace grows by 4 * N * row_stride_hint bytes. */
     } azb_nlist_args;
 
 AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
@@ -298,6 +307,18 @@ typedef struct azb_tile_build_args
     unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
     uint16_t* d_slots;               /* out [AZB_SLOTS_SIZE(size_nlist, N, lane_width)] */
     unsigned int* d_status;          /* scratch, 4 x u32 on the device */
+    /* Optional pruning for a force whose cutoff is smaller than the list's (C5: DPD r_cut 1.0 on a list built for 2.0).
+     * A neighbour list is rebuilt before any particle has moved r_buff / 2 (HOOMD: NeighborList::distanceCheck), so a listed pair
+     * that was farther apart than r_cut(ti, tj) + r_buff WHEN THE LIST WAS BUILT cannot be inside r_cut before the next rebuild:
+     * its entry is dropped from this force's slot rows (the rows keep their start and their order; d_row_count holds the new
+     * lengths). The forces are bit-identical to the unpruned plan's; the walk just skips entries that could only fail the
+     * cutoff test. d_prune_pos = NULL: no pruning. The plan must be built from the positions the list was built from. */
+    const void* d_prune_pos;         /* Scalar4[n_max] positions at list-build time (x, y, z, type) */
+    const void* d_prune_rsq;         /* Scalar[ntypes * ntypes]: (r_cut + r_buff)^2 per type pair; <= 0 drops the type pair */
+    int prune_scalar_bits;           /* 32 or 64 */
+    unsigned int prune_ntypes;
+    azb_box prune_box;
+    unsigned int* d_row_count;       /* out [N], required with d_prune_pos */
     } azb_tile_build_args;
 
 AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,

@@ -44,11 +44,23 @@ def test_cell_nlist_matches_oracle(n, rho, rcut, bits):
     assert np.array_equal(nn[:n], hs.n_neigh[:n])
     for i in range(n):
         assert np.array_equal(got[i], want[i]), i
-    # rebuilding is deterministic (same row order, not just the same sets)
-    first = cell.nlist.clone()
+    # rebuilding is deterministic (same row order, not just the same sets). The first build walked twice (count, fill); the
+    # second knows how long rows get and walks ONCE into fixed-stride rows (azb_nlist_args.row_stride_hint): same arrays.
+    first = (cell.nlist.clone(), cell.n_neigh.clone(), cell.head_list.clone())
+    assert cell._row_max == int(hs.n_neigh[:n].max())
     cell.invalidate()
     cell.compute(st)
-    assert bool((first == cell.nlist).all())
+    assert bool((first[0] == cell.nlist).all()) and bool((first[1] == cell.n_neigh).all()) and bool((first[2] == cell.head_list).all())
+    # a bound that is too small (rows outgrew it): the fill pass walks again, same arrays
+    cell._row_max = 3
+    cell.invalidate()
+    cell.compute(st)
+    assert bool((first[0] == cell.nlist).all()) and bool((first[1] == cell.n_neigh).all()) and bool((first[2] == cell.head_list).all())
+    # and the classic two-walk build on request
+    cell.single_walk = False
+    cell.invalidate()
+    cell.compute(st)
+    assert bool((first[0] == cell.nlist).all())
 
 
 def test_cell_nlist_bond_exclusions_and_force_through_cell():

@@ -85,3 +85,59 @@ def test_tile_plan_is_rebuilt_with_the_list():
     assert nl.tile_plan(n, 128) is p0  # cached while the arrays are unchanged
     nl.set_arrays(hs.n_neigh[:n], hs.head_list[:n], hs.nlist, "cuda")
     assert nl.tile_plan(n, 128) is not p0
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_pruned_plan_gives_bit_identical_forces(bits):
+    """Two forces on one list (C5): the DPD force (r_cut 1.0) walks a view of the list (built for 2.0 + 0.4) without the entries
+    that were beyond r_cut + buffer when the list was built. Same pair set inside the cutoff, same order, so the forces must
+    equal the unpruned plan's bit for bit — also after every particle has moved by up to buffer / 2."""
+    import torch
+
+    from azplugins_b200 import pair, workloads as W
+
+    snap = W.yukawa_dpd_fluid(n=20000, seed=21, jitter=0.15)
+    st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
+    cell = nlist.Cell(buffer=0.4)
+    forces = []
+    for prune in (True, False):
+        d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
+        d.dt = 0.01
+        d.params[("A", "A")] = W.C5_DPD_PARAMS[("A", "A")]
+        d.prune_lists = prune
+        d.threads_per_particle = 4  # same lanes per particle = same summation order (left to itself the pruned view, with its
+        forces.append(d)            # shorter rows, would pick narrower groups: equal to rounding only)
+    y = pair.ExpandedYukawa(nlist=cell, default_r_cut=2.0)
+    y.params[("A", "A")] = W.EY_PARAMS[("A", "A")]
+    for f in forces + [y]:
+        f._attach(st)
+        f.compute(3)
+    pruned, full = forces
+    assert pruned._plan.row_count is not None and full._plan.row_count is None and y._plan.row_count is None
+    assert pruned._plan is not full._plan
+    # the view holds exactly the entries within r_cut + buffer = 1.4 at build time
+    nn = cell.n_neigh.cpu().numpy().view(np.uint32).astype(np.int64)
+    head = cell.head_list.cpu().numpy().view(np.uint64).astype(np.int64)
+    lst = cell.nlist.cpu().numpy().view(np.uint32).astype(np.int64)
+    pos = st.pos[:, :3].double().cpu().numpy()
+    L = snap.box.L
+    i_idx = np.repeat(np.arange(st.N), nn)
+    j_idx = lst[np.repeat(head, nn) + (np.arange(len(i_idx)) - np.repeat(np.cumsum(nn) - nn, nn))]
+    d = pos[i_idx] - pos[j_idx]
+    d -= L * np.rint(d / L)
+    rsq = np.sum(d * d, axis=1)
+    sure_in, maybe = rsq <= 1.4**2 * (1 - 1e-4), rsq <= 1.4**2 * (1 + 1e-4)
+    rows = pruned._plan.row_count.cpu().numpy().astype(np.int64)
+    assert np.all(rows >= np.bincount(i_idx[sure_in], minlength=st.N)) and np.all(rows <= np.bincount(i_idx[maybe], minlength=st.N))
+    assert pruned._plan.entries == rows.sum() and pruned._plan.entries < 0.35 * cell.size_nlist
+    assert torch.equal(pruned._force, full._force) and torch.equal(pruned._virial, full._virial)
+    # move everything by up to buffer / 2 (the most a particle may move before HOOMD rebuilds the list): still identical
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    step = torch.rand((st.N, 3), generator=gen, dtype=torch.float64) * 2 - 1
+    step = 0.199 * step / step.norm(dim=1, keepdim=True).clamp(min=1.0)
+    st.pos[: st.N, :3] += step.to(st.pos)
+    for f in forces:
+        f.compute(4)
+    assert pruned._plan.row_count is not None  # same plans: the list was not rebuilt
+    assert torch.equal(pruned._force, full._force) and torch.equal(pruned._virial, full._virial)
+    assert float(pruned._force[:, :3].abs().sum()) > 0

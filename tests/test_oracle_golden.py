@@ -110,3 +110,38 @@ def test_dpd_alpha_range_and_symmetry():
             fn = getattr(O.ref(), f"azref{bits}_dpd_alpha")
             for i, j in tags[:50]:
                 assert fn(int(i), int(j), 99, 7) == O.port().azo_dpd_alpha(bits, int(i), int(j), 99, 7)
+
+
+def test_oracle_cell_list_against_brute_force_scan():
+    """The oracle's cell-list neighbour builder (the checker of the GPU builder) pinned by an O(N^2) numpy scan: 2 000 particles,
+    two types with per-pair r_list (one pair switched off), periodic in y and z only, ghosts beyond N as candidates."""
+    import azplugins_b200 as az
+
+    rng = np.random.default_rng(17)
+    n_local, n_ghost = 2000, 300
+    L = np.array([9.0, 11.0, 10.0])
+    pos = rng.uniform(-0.5, 0.5, size=(n_local + n_ghost, 3)) * L
+    pos[n_local:, 0] = np.where(rng.random(n_ghost) < 0.5, rng.uniform(-L[0] / 2 - 1.5, -L[0] / 2, n_ghost), rng.uniform(L[0] / 2, L[0] / 2 + 1.5, n_ghost))
+    typeid = rng.integers(0, 2, size=len(pos))
+    r_list = np.array([[1.5, 1.1], [1.1, 0.0]])
+    box = az.Box(*L, periodic=(False, True, True))
+    for bits in (32, 64):
+        hs = O.HostSystem(box, pos, typeid, 2, bits, n_local=n_local).build_nlist(r_list)
+        p = hs.pos[:, :3].astype(np.float64)  # the coordinates the builder saw (rounded to Scalar)
+        total = 0
+        for i in range(n_local):
+            d = p[i] - p
+            d[:, 1:] -= L[1:] * np.rint(d[:, 1:] / L[1:])
+            rsq = np.sum(d * d, axis=1)
+            rl = r_list[typeid[i], typeid]
+            near = (rl > 0) & (rsq < rl * rl)
+            near[i] = False
+            # pairs within float rounding of the list radius may go either way
+            edge = (rl > 0) & (np.abs(rsq - rl * rl) < (1e-5 if bits == 32 else 1e-12) * rl * rl)
+            row = hs.nlist[int(hs.head_list[i]) : int(hs.head_list[i]) + int(hs.n_neigh[i])]
+            got = np.zeros(len(p), dtype=bool)
+            got[row] = True
+            assert len(np.unique(row)) == len(row)
+            assert np.array_equal(got & ~edge, near & ~edge), (bits, i)
+            total += len(row)
+        assert total == hs.nlist.size and total > 10 * n_local

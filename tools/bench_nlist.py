@@ -14,7 +14,15 @@ from azplugins_b200 import md, nlist, pair, workloads
 def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "dpd"
     cell = nlist.Cell(buffer=0.4)
-    if which == "dpd":
+    f2 = None
+    if which == "eydpd":
+        snap = workloads.yukawa_dpd_fluid()
+        f = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
+        f.params[("A", "A")] = workloads.C5_DPD_PARAMS[("A", "A")]
+        f2 = pair.ExpandedYukawa(nlist=cell, default_r_cut=2.0)
+        f2.params[("A", "A")] = workloads.EY_PARAMS[("A", "A")]
+        dt = 0.01
+    elif which == "dpd":
         snap = workloads.dpd_fluid()
         f = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
         for k, v in workloads.DPD_PARAMS.items():
@@ -26,8 +34,10 @@ def main():
         f.params[("A", "A")] = workloads.PLJ_PARAMS[("A", "A")]
         dt = 0.005
     st = az.State(snap, device="cuda", scalar_bits=32, seed=42)
-    f._attach(st)
-    f.compute(0)
+    forces = [f] + ([f2] if f2 is not None else [])
+    for g in forces:
+        g._attach(st)
+        g.compute(0)
     torch.cuda.synchronize()
     for what in ("list", "list+plan"):
         ts = []
@@ -37,11 +47,12 @@ def main():
             t0 = time.perf_counter()
             cell.compute(st)
             if what == "list+plan":
-                f._current_plan()
+                for g in forces:
+                    g._current_plan()
             torch.cuda.synchronize()
             ts.append(time.perf_counter() - t0)
         print(f"{which}: N={st.N} nbar={cell.mean_neighbors(st.N):.1f} rebuild {what}: min {min(ts) * 1e3:.3f} ms  median {sorted(ts)[2] * 1e3:.3f} ms")
-    ig = md.Integrator(dt=dt, methods=[md.ConstantVolume()], forces=[f]).attach(st)
+    ig = md.Integrator(dt=dt, methods=[md.ConstantVolume()], forces=forces).attach(st)
     ig.run(20)
     torch.cuda.synchronize()
     r0 = ig.nlist_rebuilds
