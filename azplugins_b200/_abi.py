@@ -305,7 +305,11 @@ class HostStepArgs(C.Structure):
         ("stream_out", C.c_void_p),
         ("n_more", C.c_uint),
         ("more", C.POINTER(HostForce)),
+        ("flags", C.c_uint),
     ]
+
+
+HOST_STEP_NO_SYNC = 1
 
 
 _lib = None

@@ -179,6 +179,8 @@ extern "C" AZB_API int azb_host_step(const azb_host_step_args* a)
     const auto t_begin = std::chrono::steady_clock::now();
     rc = issue(a, calls, cur, s_in, s_out);
     const auto t_issued = std::chrono::steady_clock::now();
+    if (rc == 0 && (a->flags & AZB_HOST_STEP_NO_SYNC))
+        return 0;
     // the host waits for the last output row — and, after an error in the middle of the sequence, for whatever copies and
     // launches were already queued: the caller's buffers must not be written behind its back
     const int e_in = (int)cudaStreamSynchronize(s_in), e_out = (int)cudaStreamSynchronize(s_out), e_cur = (int)cudaStreamSynchronize(cur);

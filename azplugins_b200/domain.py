@@ -589,6 +589,13 @@ class HaloExchange:
         self._order_cache = (plan, order, n_interior)
         return order, n_interior
 
+    def _comm(self):
+        """High-priority side stream: the pack / push / flag kernels (and the boundary tiles behind them) must get SM slots
+        ahead of the queued CTAs of the ghost-free launch."""
+        if getattr(self, "_comm_stream", None) is None:
+            self._comm_stream = torch.cuda.Stream(self.state.device, priority=-1)
+        return self._comm_stream
+
     def step(self, force, timestep):
         """One force evaluation of a decomposed system: the ghost refresh runs on a side stream while the tiles that read
         no ghost are evaluated; the tiles on the domain boundary follow once the halo has arrived. Without a tile plan:
@@ -601,10 +608,7 @@ class HaloExchange:
             return
         order, n_interior = self.tile_order(plan)
         cur = torch.cuda.current_stream(self.state.device)
-        if getattr(self, "_comm_stream", None) is None:
-            # high priority: the pack and NCCL kernels must get SM slots ahead of the queued CTAs of the force kernel
-            self._comm_stream = torch.cuda.Stream(self.state.device, priority=-1)
-        comm = self._comm_stream
+        comm = self._comm()
         if self.transport == "peer":
             s_cur, s_comm = C.c_void_p(cur.cuda_stream), C.c_void_p(comm.cuda_stream)
             self._peer_begin(s_cur)  # acknowledge: the previous step's kernels are done with the old ghosts

@@ -23,7 +23,7 @@ import torch
 from . import _abi
 
 
-def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
+def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8, late=None):
     """Pure host logic of the pipelined step (no device access; tests/test_hostio_schedule.py).
 
     ``hi[t]`` is the highest particle index tile t reads, ``in_edges`` the ascending row boundaries of the K input chunks.
@@ -32,13 +32,20 @@ def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
     boundary, whose neighbours sit at the far end of the index range, fall into the last launch. Outputs go back in blocks
     of consecutive tiles, each after the last launch that writes into it; neighbouring blocks finished by the same launch
     travel as one copy. Returns ``(order, launches, outs)`` with launches = [(wait_chunk, first_position, n_tiles)] and
-    outs = [(launch_index, row_lo, row_hi)] sorted by launch index."""
+    outs = [(launch_index, row_lo, row_hi)] sorted by launch index.
+
+    ``late`` (bool per tile): tiles that cannot run from the host inputs alone — in a decomposed run, the tiles that read ghost
+    particles. They go to the END of ``order`` (positions ``[n_tiles - n_late, n_tiles)``), belong to no launch, and the output
+    blocks they touch are returned separately: the result is then ``(order, launches, outs, late_outs)`` with late_outs =
+    [(row_lo, row_hi)]."""
     hi = np.asarray(hi, dtype=np.int64)
     n_tiles = len(hi)
     K = len(in_edges) - 1
     ready = np.clip(np.searchsorted(in_edges, hi, side="right") - 1, 0, K - 1)
+    if late is not None:
+        ready = np.where(np.asarray(late, dtype=bool), K, ready)
     order = np.argsort(ready, kind="stable")
-    per_class = np.bincount(ready, minlength=K)
+    per_class = np.bincount(ready, minlength=K + 1)
     sched, launch_of_class, at = [], {}, 0
     for e in range(K):
         if per_class[e]:
@@ -47,11 +54,15 @@ def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
             at += int(per_class[e])
     B = max(1, min(out_blocks_per_chunk * K, n_tiles))
     tile_edges = np.linspace(0, n_tiles, B + 1).astype(np.int64)
-    outs = []
+    outs, late_outs = [], []
     for b in range(B):
         tb, te = int(tile_edges[b]), int(tile_edges[b + 1])
         if te > tb:
-            outs.append((launch_of_class[int(ready[tb:te].max())], tb * tile_size, min(te * tile_size, N)))
+            cls = int(ready[tb:te].max())
+            if cls == K:
+                late_outs.append((tb * tile_size, min(te * tile_size, N)))
+            else:
+                outs.append((launch_of_class[cls], tb * tile_size, min(te * tile_size, N)))
     outs.sort(key=lambda x: (x[0], x[1]))
     merged = []
     for o in outs:
@@ -59,15 +70,27 @@ def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8):
             merged[-1] = (o[0], merged[-1][1], o[2])
         else:
             merged.append(o)
-    return order, sched, merged
+    if late is None:
+        return order, sched, merged
+    late_merged = []
+    for lo, up in late_outs:
+        if late_merged and late_merged[-1][1] == lo:
+            late_merged[-1] = (late_merged[-1][0], up)
+        else:
+            late_merged.append((lo, up))
+    return order, sched, merged, late_merged
 
 
 class HostStep:
     """``HostStep(force_or_forces, chunks)``: several tile-staged force objects over the same particles and the same neighbour
     list (C5: DPD + ExpandedYukawa) are evaluated by the same launch ranges of one ``azb_host_step`` call."""
 
-    def __init__(self, force, chunks=8):
+    def __init__(self, force, chunks=8, halo=None):
+        """``halo``: the ``domain.HaloExchange`` of a decomposed state. The step then pipelines across the ghost exchange too:
+        the tiles that read no ghost run as their host inputs arrive, the halo waits only for the last input chunk, and the
+        tiles on the domain boundary (and the output rows they own) follow behind it on a side stream."""
         forces = list(force) if isinstance(force, (list, tuple)) else [force]
+        self.halo = halo
         if not forces or any(f._state is None for f in forces):
             raise RuntimeError("force is not attached to a state")
         if any(f._state is not forces[0]._state for f in forces):
@@ -79,11 +102,8 @@ class HostStep:
         dev = st.device
         self.s_in = torch.cuda.Stream(dev)
         self.s_out = torch.cuda.Stream(dev)
-        self.inputs = [st.pos]
-        if any(f._kind == _abi.KIND_DPD for f in forces):
-            self.inputs.append(st.vel)
-        if any(f._kind == _abi.KIND_ANISO for f in forces):
-            self.inputs.append(st.orientation)
+        self._input_names = ["pos"] + (["vel"] if any(f._kind == _abi.KIND_DPD for f in forces) else []) + (
+            ["orientation"] if any(f._kind == _abi.KIND_ANISO for f in forces) else [])
         self.outputs = []
         for f in forces:
             self.outputs.append(f._force)
@@ -93,6 +113,12 @@ class HostStep:
             raise ValueError("HostStep: at most 8 output arrays")
         self._plans = None
         self._schedule = None
+
+    @property
+    def inputs(self):
+        """The local rows of the device arrays the host writes every step (ghost rows are the halo's)."""
+        st = self.force._state
+        return [getattr(st, name)[: st.N] for name in self._input_names]
 
     # bytes moved per step (the bench reports them)
     @property
@@ -138,15 +164,24 @@ class HostStep:
             return
         plan = plans[0]
         K = max(1, min(self.chunks, plan.n_tiles))
-        n_rows = st.pos.shape[0]
-        in_edges = np.linspace(0, n_rows, K + 1).astype(np.int64)
+        in_edges = np.linspace(0, st.N, K + 1).astype(np.int64)
         hi = self._tile_hi(plan, st.N)
         for p in plans[1:]:
             if p.uniq is not plan.uniq:
                 hi = np.maximum(hi, self._tile_hi(p, st.N))
-        order, sched, merged = plan_schedule(hi, in_edges, plan.tile_size, st.N)
+        late_outs, n_late, d_order_holder = [], 0, [None]
+        if st.n_ghost:
+            if self.halo is None:
+                raise RuntimeError("HostStep: a decomposed state (ghost particles) needs its HaloExchange passed as `halo`")
+            late = hi >= st.N  # the tile reads a ghost row
+            n_late = int(late.sum())
+            order, sched, merged, late_outs = plan_schedule(hi, in_edges, plan.tile_size, st.N, late=late)
+        else:
+            order, sched, merged = plan_schedule(hi, in_edges, plan.tile_size, st.N)
+        self._late = (n_late, late_outs, d_order_holder)
         # the native call's tables, built once per plan: a step only patches the timestep and the host pointers
         d_order = torch.from_numpy(order.astype(np.int32)).to(st.device)
+        d_order_holder[0] = d_order
         wholes = [g._build_args(0, tile_order=d_order) for g in self.forces]
         hs = _abi.HostStepArgs()
         hs.kind = f._kind
@@ -171,6 +206,7 @@ class HostStep:
         out_ranges = (_abi.HostOutRange * len(merged))()
         for k, (after, lo, up) in enumerate(merged):
             out_ranges[k].after_launch, out_ranges[k].row_lo, out_ranges[k].row_hi = after, lo, up
+        hs.flags = _abi.HOST_STEP_NO_SYNC if n_late else 0
         hs.n_in_chunks, hs.in_edges = K, edges
         hs.n_launches, hs.launches = len(sched), launches
         hs.n_outs, hs.outs = len(merged), out_ranges
@@ -195,9 +231,11 @@ class HostStep:
         if self._schedule is None or stale:
             self._make_schedule(plans)
         if self._schedule is None:
-            # no tile plan (e.g. a kernel family without a tiled flavour): plain copy - compute - copy
+            # no tile plan (e.g. a kernel family without a tiled flavour): plain copy - (exchange) - compute - copy
             for dst, src in zip(self.inputs, host_in):
                 dst.copy_(src, non_blocking=True)
+            if self.halo is not None:
+                self.halo.update()
             for g in self.forces:
                 g.compute(timestep)
             for dst, src in zip(host_out, self.outputs):
@@ -212,9 +250,41 @@ class HostStep:
         for k, t in enumerate(host_out):
             hs.outputs[k].h_ptr = t.data_ptr()
         hs.stream = cur.cuda_stream
+        n_late, late_outs, order = self._late[0], self._late[1], self._late[2][0]
+        halo = self.halo
+        if n_late and halo.transport == "peer":
+            halo._peer_begin(C.c_void_p(cur.cuda_stream))  # acknowledge: the previous step's kernels are done with the old ghosts
         _abi.check(f._lib.azb_host_step(C.byref(hs)), "azb_host_step")
         for g in self.forces:
             g.launches += len(sched)
+        if not n_late:
+            return
+        # ---- behind the (unsynchronised) native call: ghost exchange, the tiles that read ghosts, their output rows -----------
+        plan = self._plans[0]
+        comm = halo._comm()
+        inputs_in = torch.cuda.Event()
+        inputs_in.record(self.s_in)  # every input chunk of this step has been queued on s_in before this point
+        comm.wait_event(inputs_in)
+        with torch.cuda.stream(comm):
+            if halo.transport == "peer":
+                s_comm = C.c_void_p(comm.cuda_stream)
+                halo._peer_push(s_comm)
+                halo._peer_arrived(s_comm)
+            else:
+                halo.update()
+            for g in self.forces:
+                g.compute(timestep, tile_range=(plan.n_tiles - n_late, n_late), tile_order=order)
+            boundary_done = torch.cuda.Event()
+            boundary_done.record(comm)
+        self.s_out.wait_event(boundary_done)
+        with torch.cuda.stream(self.s_out):
+            for lo, up in late_outs:
+                for dst, src in zip(host_out, self.outputs):
+                    dst[lo:up].copy_(src[lo:up], non_blocking=True)
+        cur.wait_stream(comm)
+        self.s_out.synchronize()
+        cur.synchronize()
+        halo._poll()
 
     def release(self):
         """Drop the native call's per-thread event pool (``azb_host_step_release``) and the cached schedule."""

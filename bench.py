@@ -837,8 +837,8 @@ def run_b200(args):
 
     tiled = [f for f in forces if getattr(f, "_plan", None) is not None]
     plain = [f for f in forces if f not in tiled]
-    pipelined = world == 1 and args.e2e_chunks > 1 and len(tiled) >= 1
-    hs = HostStep(tiled if pipelined else forces[:1], chunks=args.e2e_chunks)
+    pipelined = args.e2e_chunks > 1 and len(tiled) >= 1
+    hs = HostStep(tiled if pipelined else forces[:1], chunks=args.e2e_chunks, halo=halo)
     rest = plain if pipelined else forces[1:]
     extra_out = [f._force for f in rest]
     pinned_in = hs.pinned_inputs()
@@ -888,7 +888,9 @@ def run_b200(args):
     line["e2e"] = {"value": n_total * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": e2e_ms / K,
                    "note": (f"pipelined in {args.e2e_chunks} chunks: pinned host pos(+vel/orientation) -> device, tile-range launches of "
-                            f"{len(tiled)} force object(s) as inputs arrive, force(+torque) arrays -> pinned host; checked bit-identical to the plain launches"
+                            f"{len(tiled)} force object(s) as inputs arrive"
+                            + (", ghost exchange behind the last input chunk, then the tiles that read ghosts" if halo is not None else "")
+                            + ", force(+torque) arrays -> pinned host; checked bit-identical to the plain launches"
                             if pipelined else
                             "pinned host pos(+vel/orientation) -> device, (ghost exchange,) kernel(s), force(+torque) -> pinned host, every step")}
 

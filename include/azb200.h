@@ -510,7 +510,11 @@ typedef struct azb_host_step_args
     void* stream_out; /* D2H copies */
     unsigned int n_more;       /* further force objects evaluated by the same launches (<= 7) */
     const azb_host_force* more; /* host array */
+    unsigned int flags;        /* AZB_HOST_STEP_NO_SYNC: return once everything is queued; the caller orders later work behind
+                                  `stream` / `stream_out` and synchronises them itself (a decomposed run queues its ghost exchange and
+                                  the tiles that read ghosts behind this call: azplugins_b200/hostio.py) */
     } azb_host_step_args;
+#define AZB_HOST_STEP_NO_SYNC 1u
 
 /* Frees the per-thread event pool azb_host_step keeps between calls (optional; call from the thread that ran the steps). */
 AZB_API void azb_host_step_release(void);

@@ -50,7 +50,7 @@ def run_case(kind, steps, dt, dev, rank, world):
     from azplugins_b200 import md, nlist, workloads as W
     from azplugins_b200.domain import Decomposition, HaloExchange
 
-    snap = W.lj_fluid(m=20, seed=1001) if kind == "lj" else W.polymer_melt(n_chains=320, seed=3001)
+    snap = W.lj_fluid(m=20, seed=1001, jitter=0.05) if kind == "lj" else W.polymer_melt(n_chains=320, seed=3001)
     if kind == "melt":
         snap.velocity = np.random.default_rng(7).normal(scale=0.5, size=(snap.N, 3))
         snap.tag = np.random.default_rng(8).permutation(snap.N).astype(np.uint32)
