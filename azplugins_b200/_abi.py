@@ -145,6 +145,14 @@ class BondArgs(C.Structure):
     ]
 
 
+class NlistView(C.Structure):
+    _fields_ = [("lane_width", C.c_uint), ("d_keep_rsq", C.c_void_p), ("d_slots", C.c_void_p), ("d_row_count", C.c_void_p)]
+
+
+class NlistPlanStatus(C.Structure):
+    _fields_ = [("ok", C.c_uint), ("max_uniq", C.c_uint), ("max_slot_span", C.c_uint * 4), ("n_entries", C.c_size_t * 4)]
+
+
 class NlistArgs(C.Structure):
     _fields_ = [
         ("d_pos", C.c_void_p),
@@ -166,6 +174,13 @@ class NlistArgs(C.Structure):
         ("d_workspace", C.c_void_p),
         ("workspace_bytes", C.c_size_t),
         ("row_stride_hint", C.c_uint),
+        ("n_views", C.c_uint),
+        ("views", NlistView * 4),
+        ("tile_size", C.c_uint),
+        ("uniq_capacity", C.c_uint),
+        ("d_uniq_count", C.c_void_p),
+        ("d_uniq", C.c_void_p),
+        ("d_uniq_max", C.c_void_p),
     ]
 
 
@@ -187,6 +202,7 @@ EXPORTS = (
     "azb_nlist_workspace_size",
     "azb_nlist_count",
     "azb_nlist_fill",
+    "azb_nlist_plan_result",
     "azb_gather_scalar4",
     "azb_tiles_build",
     "azb_barrier_forces",
@@ -347,6 +363,8 @@ def load():
     lib.azb_nlist_count.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(C.c_size_t), C.c_void_p]
     lib.azb_nlist_fill.restype = C.c_int
     lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
+    lib.azb_nlist_plan_result.restype = C.c_int
+    lib.azb_nlist_plan_result.argtypes = [C.POINTER(NlistArgs), C.POINTER(NlistPlanStatus), C.c_void_p]
     lib.azb_gather_scalar4.restype = C.c_int
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.azb_tiles_build.restype = C.c_int

@@ -36,6 +36,28 @@ def build_cell_nlist(nl, state, row_align=1):
     # one walk instead of two once the previous build has told how long rows get (azb_nlist_args.row_stride_hint)
     prev_max = getattr(nl, "_row_max", 0)
     a.row_stride_hint = (int(prev_max * 1.2) + 8) if (prev_max and getattr(nl, "single_walk", True)) else 0
+    # tile plans the consumers will ask for, emitted by the same walk (views of azb_nlist_args)
+    requests = nl.plan_requests(state) if a.row_stride_hint else {}
+    usable = {k: r for k, r in requests.items() if k[3] == 0}
+    if len(usable) > 4 or len({k[0] for k in usable}) > 1:
+        usable = {}
+    view_keys = list(usable)
+    uniq_count = uniq = uniq_max = None
+    if view_keys:
+        a.n_views, a.tile_size, a.uniq_capacity = len(view_keys), view_keys[0][0], 2048
+        n_tiles = (state.N + a.tile_size - 1) // a.tile_size
+        uniq_count = torch.zeros(n_tiles, dtype=torch.int32, device=dev)
+        uniq = torch.empty(n_tiles * 2048, dtype=torch.int32, device=dev)
+        uniq_max = torch.zeros(n_tiles, dtype=torch.int32, device=dev)
+        a.d_uniq_count, a.d_uniq, a.d_uniq_max = uniq_count.data_ptr(), uniq.data_ptr(), uniq_max.data_ptr()
+        view_rows = []
+        for v, key in enumerate(view_keys):
+            prune = usable[key]["prune"]
+            a.views[v].lane_width = key[2]
+            rc_t = torch.zeros(max(state.N, 1), dtype=torch.int32, device=dev) if prune is not None else None
+            a.views[v].d_keep_rsq = prune[1].data_ptr() if prune is not None else None
+            a.views[v].d_row_count = rc_t.data_ptr() if rc_t is not None else None
+            view_rows.append(rc_t)
     keep = [rlsq]
     if "bond" in nl.exclusions and state.has_bonds:
         d_head, d_lst = state.exclusions_device()
@@ -53,12 +75,26 @@ def build_cell_nlist(nl, state, row_align=1):
     _abi.check(lib.azb_nlist_count(state.scalar_bits, C.byref(a), C.byref(total), stream), "azb_nlist_count")
     nlist = torch.zeros(max(total.value, 1), dtype=torch.int32, device=dev)
     a.d_nlist, a.capacity = nlist.data_ptr(), max(total.value, 1)
+    view_slots = []
+    for v, key in enumerate(view_keys):
+        lw = key[2]
+        sl = torch.zeros(total.value + max(4 * lw, 8) * (state.N + 1), dtype=torch.int16, device=dev)  # AZB_SLOTS_SIZE
+        a.views[v].d_slots = sl.data_ptr()
+        view_slots.append(sl)
     _abi.check(lib.azb_nlist_fill(state.scalar_bits, C.byref(a), stream), "azb_nlist_fill")
+    plans = {}
+    if view_keys:
+        status = _abi.NlistPlanStatus()
+        _abi.check(lib.azb_nlist_plan_result(C.byref(a), C.byref(status), stream), "azb_nlist_plan_result")
+        if status.ok:
+            for v, key in enumerate(view_keys):
+                plans[key] = TilePlanHandle(key[0], (state.N + key[0] - 1) // key[0], 2048, status.max_uniq, key[2], status.max_slot_span[v], uniq_count,
+                                            uniq, view_slots[v], 0.0, view_rows[v], int(status.n_entries[v]), uniq_max=uniq_max)
     torch.cuda.current_stream(dev).synchronize()
     del keep
     nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
     nl._row_max = int(n_neigh.max().item()) if state.N else 0
-    nl._tiles = {}
+    nl._tiles = plans  # plans the build emitted itself; anything else is built on demand (azb_tiles_build)
     # positions the list was built from (locals + ghosts): reference point of the displacement check (md.Integrator) and of
     # the pruning test of force-specific tile plans
     nl._last_pos = state.pos.clone()
@@ -70,8 +106,10 @@ class TilePlanHandle:
     """Device arrays of one ``azb_tile_plan`` plus the C struct that points at them (kept alive together)."""
 
     def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, lane_width, max_slot_span, uniq_count, uniq, slots, build_ms, row_count=None,
-                 entries=None):
+                 entries=None, uniq_max=None):
         self.uniq_count, self.uniq, self.slots, self.row_count = uniq_count, uniq, slots, row_count
+        self.uniq_max = uniq_max  # plans emitted by the list build: the staged sets are not ascending, the largest index is kept apart
+        self.from_list_build = uniq_max is not None
         self.build_ms = build_ms
         self.entries = entries  # list entries the plan's rows hold (fewer than the list's when pruned)
         self.c = _abi.TilePlan()
@@ -90,6 +128,15 @@ class TilePlanHandle:
 
     def pointer(self):
         return C.pointer(self.c)
+
+    def tile_max(self):
+        """int64 tensor [n_tiles]: the largest particle index each tile stages (it reads a ghost iff that is >= N)."""
+        if self.uniq_max is not None:
+            return self.uniq_max.long()
+        count = self.uniq_count.long()
+        t = torch.arange(self.n_tiles, device=count.device, dtype=torch.int64)
+        last = self.uniq[t * self.uniq_capacity + torch.clamp(count - 1, min=0)].long()  # ascending list: the last entry
+        return torch.where(count > 0, last, torch.zeros_like(last))
 
 
 def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None):

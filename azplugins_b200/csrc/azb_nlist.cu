@@ -75,6 +75,183 @@ __global__ void cell_bounds_kernel(const unsigned int* __restrict__ cell_sorted,
     st4(pos_sorted + s, p.x, p.y, p.z, p.w);
     }
 
+// ---- tile plans from the cell structure (azb_nlist_args.views) ----------------------------------------------------------------
+// The staged set of a tile = the cells of its particles, one cell further in every direction: (y, z) rows of cells, each row a
+// contiguous range of the cell-ordered array, split in up to three segments where it crosses the periodic x boundary (cells
+// reached through the low face, cells inside, cells reached through the high face). Slot of a particle = offset of its
+// segment in the tile's staging order + its position in the segment.
+constexpr unsigned int PLAN_ROWS_MAX = 32;
+struct TileTable
+    {
+    int x0, y0, z0;       // first cell of the box in unwrapped coordinates (may be negative / beyond the grid along periodic axes)
+    unsigned int ny, nz;  // rows of the box; 0 = unusable tile
+    unsigned int total;   // staged particles
+    unsigned int begin[PLAN_ROWS_MAX * 3];      // first position (cell order) of every segment
+    unsigned int offset[PLAN_ROWS_MAX * 3 + 1]; // slot of the segment's first particle; [rows * 3] = total
+    };
+
+__device__ __forceinline__ int pos_mod(int a, int n)
+    {
+    const int r = a % n;
+    return r < 0 ? r + n : r;
+    }
+
+// one warp per tile
+__global__ void __launch_bounds__(128) tile_table_kernel(const unsigned int* __restrict__ cell_of, unsigned int N, unsigned int tile_size,
+                                                         unsigned int n_tiles, CellGrid g, const unsigned int* __restrict__ cell_begin,
+                                                         unsigned int ucap, TileTable* __restrict__ tables, unsigned int* __restrict__ uniq_count,
+                                                         unsigned int* __restrict__ status)
+    {
+    constexpr unsigned int FULL = 0xffffffffu;
+    const unsigned int T = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (T >= n_tiles)
+        return;
+    const unsigned int i0 = T * tile_size, i1 = min(i0 + tile_size, N);
+    int cref[3];
+        {
+        unsigned int c = cell_of[i0];
+        cref[0] = c % g.nc[0];
+        c /= g.nc[0];
+        cref[1] = c % g.nc[1];
+        cref[2] = c / g.nc[1];
+        }
+    int lo[3] = {1 << 30, 1 << 30, 1 << 30}, hi[3] = {-(1 << 30), -(1 << 30), -(1 << 30)};
+    for (unsigned int i = i0 + lane; i < i1; i += 32)
+        {
+        unsigned int c = cell_of[i];
+        int cc[3];
+        cc[0] = c % g.nc[0];
+        c /= g.nc[0];
+        cc[1] = c % g.nc[1];
+        cc[2] = c / g.nc[1];
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            {
+            int rel = cc[d] - cref[d];
+            if ((g.periodic >> d) & 1u)
+                {
+                if (rel > g.nc[d] / 2)
+                    rel -= g.nc[d];
+                else if (rel < -(g.nc[d] / 2))
+                    rel += g.nc[d];
+                }
+            lo[d] = min(lo[d], rel);
+            hi[d] = max(hi[d], rel);
+            }
+        }
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+        {
+        lo[d] = __reduce_min_sync(FULL, lo[d]) - 1;
+        hi[d] = __reduce_max_sync(FULL, hi[d]) + 1;
+        if ((g.periodic >> d) & 1u)
+            {
+            if (hi[d] - lo[d] + 1 >= g.nc[d]) // the box wraps onto itself: the whole axis, every cell once
+                {
+                lo[d] = -cref[d];
+                hi[d] = lo[d] + g.nc[d] - 1;
+                }
+            }
+        else
+            {
+            lo[d] = max(lo[d], -cref[d]);
+            hi[d] = min(hi[d], g.nc[d] - 1 - cref[d]);
+            }
+        }
+    const unsigned int ny = (unsigned int)(hi[1] - lo[1] + 1), nz = (unsigned int)(hi[2] - lo[2] + 1);
+    const unsigned int rows = ny * nz;
+    bool ok = rows <= PLAN_ROWS_MAX;
+    const int X0 = cref[0] + lo[0], X1 = cref[0] + hi[0];
+    TileTable& tt = tables[T];
+    unsigned int b[3] = {0, 0, 0}, len[3] = {0, 0, 0};
+    if (ok && lane < rows)
+        {
+        const int y = pos_mod(cref[1] + lo[1] + (int)(lane % ny), g.nc[1]);
+        const int z = pos_mod(cref[2] + lo[2] + (int)(lane / ny), g.nc[2]);
+        const unsigned int rb = (unsigned int)((z * g.nc[1] + y) * g.nc[0]);
+        const int nx = g.nc[0];
+        // low: unwrapped cells [X0, min(X1, -1)] live at +nx; main: [max(X0, 0), min(X1, nx - 1)]; high: [max(X0, nx), X1] at -nx
+        const int sa[3] = {X0, max(X0, 0), max(X0, nx)}, sb[3] = {min(X1, -1), min(X1, nx - 1), X1}, sh[3] = {nx, 0, -nx};
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (sa[k] <= sb[k])
+                {
+                b[k] = cell_begin[rb + sa[k] + sh[k]];
+                len[k] = cell_begin[rb + sb[k] + sh[k] + 1] - b[k];
+                }
+        }
+    // exclusive scan of the row totals over the lanes
+    const unsigned int mine = len[0] + len[1] + len[2];
+    unsigned int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+        {
+        const unsigned int v = __shfl_up_sync(FULL, incl, o);
+        if ((int)lane >= o)
+            incl += v;
+        }
+    const unsigned int total = __shfl_sync(FULL, incl, 31);
+    ok = ok && total <= ucap;
+    if (ok && lane < rows)
+        {
+        unsigned int off = incl - mine;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            {
+            tt.begin[lane * 3 + k] = b[k];
+            tt.offset[lane * 3 + k] = off;
+            off += len[k];
+            }
+        }
+    if (lane == 0)
+        {
+        tt.x0 = X0;
+        tt.y0 = cref[1] + lo[1];
+        tt.z0 = cref[2] + lo[2];
+        tt.ny = ok ? ny : 0u;
+        tt.nz = ok ? nz : 0u;
+        tt.total = ok ? total : 0u;
+        if (ok)
+            tt.offset[rows * 3] = total;
+        uniq_count[T] = ok ? total : 0xffffffffu;
+        if (ok)
+            atomicMax(status + 0, total);
+        else
+            atomicExch(status + 1, 1u);
+        }
+    }
+
+// one CTA per tile: the staged set in staging order (a streaming copy of ranges of the cell-ordered index array)
+__global__ void __launch_bounds__(128) tile_uniq_kernel(const TileTable* __restrict__ tables, const unsigned int* __restrict__ idx_sorted,
+                                                        unsigned int ucap, unsigned int* __restrict__ uniq, unsigned int* __restrict__ uniq_max)
+    {
+    const TileTable& tt = tables[blockIdx.x];
+    const unsigned int segs = tt.ny * tt.nz * 3u;
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    unsigned int* out = uniq + (size_t)blockIdx.x * ucap;
+    unsigned int mx = 0;
+    for (unsigned int f = warp; f < segs; f += 4)
+        {
+        const unsigned int off = tt.offset[f], len = tt.offset[f + 1] - off, b = tt.begin[f];
+        for (unsigned int k = lane; k < len; k += 32)
+            {
+            const unsigned int j = idx_sorted[b + k];
+            out[off + k] = j;
+            mx = max(mx, j);
+            }
+        }
+    __shared__ unsigned int s_max;
+    if (threadIdx.x == 0)
+        s_max = 0;
+    __syncthreads();
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0)
+        atomicMax(&s_max, mx);
+    __syncthreads();
+    if (threadIdx.x == 0)
+        uniq_max[blockIdx.x] = s_max;
+    }
+
 template<class S> struct NlistDev
     {
     const typename vec4<S>::type* pos_sorted;
@@ -91,6 +268,11 @@ template<class S> struct NlistDev
     unsigned int* tmp_rows; // MODE_SINGLE: [N * row_stride] rows of fixed capacity, compacted afterwards
     unsigned int row_stride;
     unsigned int* overflow; // MODE_SINGLE: set when a row does not fit row_stride
+    // tile-plan views (MODE_SINGLE only): slot | view mask << 12 per accepted entry, next to the temporary list rows
+    unsigned int n_views, tile_size;
+    const TileTable* tables;
+    uint16_t* tmp_slots;
+    const S* keep_rsq[4];
     Box<S> box;
     CellGrid grid;
     unsigned int N, n_max, ntypes;
@@ -171,6 +353,12 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
     // of the row on the other side of the periodic boundary), with the image shifts of the row (y, z) and of each range (x).
     unsigned int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
     S shy = S(0), shz = S(0), shxa = S(0), shxb = S(0);
+    const bool plan = MODE == MODE_SINGLE && a.n_views > 0;
+    unsigned int slot_a = 0, slot_b = 0; // slot of the first particle of range a / b in the staging order of my tile
+    int xa_cell = 0, xb_cell = 0;        // first cell (actual x) of range a / b
+    uint16_t* srow = nullptr;
+    if (plan && active)
+        srow = a.tmp_slots + (size_t)i * a.row_stride;
     if (lane < 9u && active)
         {
         const int oz = (int)lane / 3 - 1, oy = (int)lane % 3 - 1;
@@ -217,21 +405,26 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                     a0 = a.cell_begin[rb + xlo + a.grid.nc[0]];
                     a1 = a.cell_begin[rb + a.grid.nc[0]];
                     shxa = a.box.Lx;
+                    xa_cell = xlo + a.grid.nc[0];
                     b0 = a.cell_begin[rb];
                     b1 = a.cell_begin[rb + xhi + 1];
+                    xb_cell = 0;
                     }
                 else if (xhi >= a.grid.nc[0])
                     {
                     a0 = a.cell_begin[rb + xlo];
                     a1 = a.cell_begin[rb + a.grid.nc[0]];
+                    xa_cell = xlo;
                     b0 = a.cell_begin[rb];
                     b1 = a.cell_begin[rb + xhi - a.grid.nc[0] + 1];
                     shxb = -a.box.Lx;
+                    xb_cell = 0;
                     }
                 else
                     {
                     a0 = a.cell_begin[rb + xlo];
                     a1 = a.cell_begin[rb + xhi + 1];
+                    xa_cell = xlo;
                     }
                 }
             else
@@ -240,10 +433,37 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                 xhi = xhi >= a.grid.nc[0] ? a.grid.nc[0] - 1 : xhi;
                 a0 = a.cell_begin[rb + xlo];
                 a1 = a.cell_begin[rb + xhi + 1];
+                xa_cell = xlo;
+                }
+            if (plan)
+                {
+                // my tile's table: row of (y, z) in the tile's cell box, segment of the range's first cell
+                const TileTable& tt = a.tables[i / a.tile_size];
+                int ry = ci[1] + oy - tt.y0, rz = ci[2] + oz - tt.z0;
+                if ((a.grid.periodic >> 1) & 1u)
+                    ry = pos_mod(ry, a.grid.nc[1]);
+                if ((a.grid.periodic >> 2) & 1u)
+                    rz = pos_mod(rz, a.grid.nc[2]);
+                const unsigned int trw = ((unsigned int)rz * tt.ny + (unsigned int)ry) * 3u;
+                auto slot_of = [&](int x_cell, unsigned int first) -> unsigned int
+                {
+                    int xu = x_cell; // the cell's coordinate in the tile's unwrapped frame [x0, x0 + nc)
+                    if (a.grid.periodic & 1u)
+                        xu = tt.x0 + pos_mod(x_cell - tt.x0, a.grid.nc[0]);
+                    const unsigned int sg = trw + (xu < 0 ? 0u : (xu >= a.grid.nc[0] ? 2u : 1u));
+                    return tt.offset[sg] + (first - tt.begin[sg]);
+                };
+                if (tt.ny != 0u) // (an unusable tile voids the plans: azb_nlist_plan_status.ok = 0)
+                    {
+                    if (a1 > a0)
+                        slot_a = slot_of(xa_cell, a0);
+                    if (b1 > b0)
+                        slot_b = slot_of(xb_cell, b0);
+                    }
                 }
             }
         }
-    auto visit = [&](unsigned int s0, unsigned int s1, const S sx, const S sy, const S sz)
+    auto visit = [&](unsigned int s0, unsigned int s1, const S sx, const S sy, const S sz, const unsigned int slot0)
     {
         // trip count uniform over the warp (two groups of 16 share it: the ballots below are warp-wide)
         unsigned int len = s1 - s0;
@@ -253,6 +473,7 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
             {
             const unsigned int s = s0 + off + lane;
             bool take = false;
+            unsigned int packed = 0; // slot | view mask << 12
             if (s < s1)
                 {
                 const auto pj = ld4(a.pos_sorted + s);
@@ -265,8 +486,18 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                     }
                 else
                     min_image(a.box, dx, dy, dz);
-                const S rl = SINGLE_TYPE ? rl_single : a.r_listsq[trow + type_of(pj.w)];
-                take = (s != s_own) && (rl > S(0)) && (dx * dx + dy * dy + dz * dz < rl);
+                const unsigned int tp = SINGLE_TYPE ? 0u : trow + type_of(pj.w);
+                const S rl = SINGLE_TYPE ? rl_single : a.r_listsq[tp];
+                const S rsq = dx * dx + dy * dy + dz * dz;
+                take = (s != s_own) && (rl > S(0)) && (rsq < rl);
+                if (plan)
+                    {
+                    packed = slot0 + (s - s0);
+#pragma unroll
+                    for (unsigned int v = 0; v < 4; ++v)
+                        if (v < a.n_views && (a.keep_rsq[v] == nullptr || rsq <= a.keep_rsq[v][tp] * S(1.00001)))
+                            packed |= 0x1000u << v;
+                    }
                 }
             unsigned int j = 0;
             if ((MODE != MODE_COUNT || EXCL) && take)
@@ -282,7 +513,11 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                 {
                 const unsigned int slot = count + __popc(m & ltmask);
                 if (take && slot < row_cap)
+                    {
                     row[slot] = j;
+                    if (plan)
+                        srow[slot] = (uint16_t)packed;
+                    }
                 }
             count += __popc(m & gmask);
             }
@@ -292,8 +527,8 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
         {
         const int src = (int)gshift + r;
         const S sy = __shfl_sync(FULL, shy, src), sz = __shfl_sync(FULL, shz, src);
-        visit(__shfl_sync(FULL, a0, src), __shfl_sync(FULL, a1, src), __shfl_sync(FULL, shxa, src), sy, sz);
-        visit(__shfl_sync(FULL, b0, src), __shfl_sync(FULL, b1, src), __shfl_sync(FULL, shxb, src), sy, sz);
+        visit(__shfl_sync(FULL, a0, src), __shfl_sync(FULL, a1, src), __shfl_sync(FULL, shxa, src), sy, sz, __shfl_sync(FULL, slot_a, src));
+        visit(__shfl_sync(FULL, b0, src), __shfl_sync(FULL, b1, src), __shfl_sync(FULL, shxb, src), sy, sz, __shfl_sync(FULL, slot_b, src));
         }
     if (MODE != MODE_FILL && lane == 0 && active)
         {
@@ -303,20 +538,75 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
         }
     }
 
-// MODE_SINGLE, second half: fixed-stride temporary rows -> the packed HOOMD rows at head_list (pure streaming copy)
+// MODE_SINGLE, second half: fixed-stride temporary rows -> the packed HOOMD rows at head_list (pure streaming copy), and the
+// slot rows of every tile-plan view in its lane-transposed, padded layout (AZB_SLOT_HEAD), filtered by the view's mask bit.
+struct ViewOut
+    {
+    uint16_t* slots[4];
+    unsigned int* row_count[4];
+    unsigned int lane_width[4];
+    unsigned int n_views, tile_size;
+    const uint16_t* tmp_slots;
+    unsigned int* status; // [4 + v] max slot span, [8 + 2 v] entries (64 bit)
+    };
+
 __global__ void __launch_bounds__(256) nlist_compact_kernel(const unsigned int* __restrict__ tmp_rows, unsigned int row_stride,
                                                             const unsigned int* __restrict__ n_neigh, const size_t* __restrict__ head_list,
-                                                            unsigned int N, unsigned int* __restrict__ nlist, size_t capacity)
+                                                            unsigned int N, unsigned int* __restrict__ nlist, size_t capacity, const ViewOut vo)
     {
     const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (warp >= N)
         return;
-    const unsigned int nn = n_neigh[warp];
-    const size_t head = head_list[warp];
-    const unsigned int* src = tmp_rows + (size_t)warp * row_stride;
+    const unsigned int i = warp;
+    const unsigned int nn = n_neigh[i];
+    const size_t head = head_list[i];
+    const unsigned int* src = tmp_rows + (size_t)i * row_stride;
     for (unsigned int k = lane; k < nn; k += 32)
         if (head + k < capacity)
             nlist[head + k] = src[k];
+    for (unsigned int v = 0; v < vo.n_views; ++v)
+        {
+        const unsigned int W = vo.lane_width[v], M = 4u * W;
+        const uint16_t* ssrc = vo.tmp_slots + (size_t)i * row_stride;
+        const size_t shead = AZB_SLOT_HEAD(head, i, W);
+        uint16_t* out = vo.slots[v];
+        unsigned int out_n = 0;
+        for (unsigned int k0 = 0; k0 < nn; k0 += 32)
+            {
+            const unsigned int k = k0 + lane;
+            unsigned int p = 0;
+            if (k < nn)
+                p = ssrc[k];
+            const bool keep = (p >> (12u + v)) & 1u;
+            const unsigned int m = __ballot_sync(0xffffffffu, keep);
+            if (keep)
+                {
+                const unsigned int o = out_n + __popc(m & ((1u << lane) - 1u));
+                const unsigned int r = o % M;
+                out[shead + (o - r) + 4u * (r % W) + r / W] = (uint16_t)(p & 0xfffu);
+                }
+            out_n += __popc(m);
+            }
+        const unsigned int out_p = (out_n + M - 1u) / M * M;
+        for (unsigned int o = out_n + lane; o < out_p; o += 32) // padding
+            {
+            const unsigned int r = o % M;
+            out[shead + (o - r) + 4u * (r % W) + r / W] = 0;
+            }
+        if (lane == 0)
+            {
+            if (vo.row_count[v])
+                vo.row_count[v][i] = out_n;
+            atomicAdd((unsigned long long*)(vo.status + 8 + 2 * v), (unsigned long long)out_n);
+            // extent of the tile's slot rows (kernels that stage them size their buffer by it): written by the tile's last row
+            if ((i + 1) % vo.tile_size == 0 || i + 1 == N)
+                {
+                const unsigned int first = (i / vo.tile_size) * vo.tile_size;
+                const unsigned int nnp = (nn + M - 1u) / M * M;
+                atomicMax(vo.status + 4 + v, (unsigned int)(shead + nnp - AZB_SLOT_HEAD(head_list[first], first, W)));
+                }
+            }
+        }
     }
 
 template<class S, int MODE> static void launch_nlist_kernel(const NlistDev<S>& d, bool img, double mean_range, cudaStream_t stream)
@@ -387,6 +677,9 @@ struct Workspace
     size_t* total;
     unsigned int* flags;    // [0] overflow of a fixed-stride row, [1] 1 = the single-walk rows are valid (fill only compacts)
     unsigned int* tmp_rows; // [N * row_stride] when row_stride_hint > 0
+    unsigned int* plan_status; // 16 words: [0] max staged set, [1] unusable tile seen, [4 + v] max slot span, [8 + 2 v] entries (u64)
+    TileTable* tables;         // [n_tiles] when views are requested
+    uint16_t* tmp_slots;       // [N * row_stride] when views are requested
     void* cub_tmp;
     size_t cub_bytes;
     size_t bytes;
@@ -435,7 +728,8 @@ static bool image_shifts_ok(const CellGrid& g)
     return true;
     }
 
-static Workspace carve(void* base, unsigned int n_max, unsigned int N, size_t ncell, size_t scalar4_bytes, size_t cub_bytes, unsigned int row_stride)
+static Workspace carve(void* base, unsigned int n_max, unsigned int N, size_t ncell, size_t scalar4_bytes, size_t cub_bytes, unsigned int row_stride,
+                       unsigned int n_tiles = 0)
     {
     Workspace w;
     char* p = (char*)base;
@@ -457,6 +751,9 @@ static Workspace carve(void* base, unsigned int n_max, unsigned int N, size_t nc
     w.cub_tmp = take(cub_bytes);
     w.cub_bytes = cub_bytes;
     w.tmp_rows = row_stride ? (unsigned int*)take(4 * (size_t)row_stride * (N ? N : 1)) : nullptr;
+    w.plan_status = (unsigned int*)take(16 * sizeof(unsigned int));
+    w.tables = (row_stride && n_tiles) ? (TileTable*)take(sizeof(TileTable) * (size_t)n_tiles) : nullptr;
+    w.tmp_slots = (row_stride && n_tiles) ? (uint16_t*)take(2 * (size_t)row_stride * (N ? N : 1)) : nullptr;
     w.bytes = off;
     return w;
     }
@@ -469,6 +766,30 @@ static size_t cub_temp_bytes(unsigned int n_max, unsigned int N)
     thrust::transform_iterator<PadTo, const unsigned int*, size_t> it((const unsigned int*)nullptr, PadTo {1});
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, it, (size_t*)nullptr, (int)N);
     return sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
+    }
+
+// tile-plan views ride on the single walk only
+static unsigned int plan_tiles(const azb_nlist_args& a)
+    {
+    if (a.n_views == 0 || a.row_stride_hint == 0 || a.N == 0)
+        return 0;
+    return (a.N + a.tile_size - 1) / a.tile_size;
+    }
+static int check_views(const azb_nlist_args& a)
+    {
+    if (a.n_views == 0)
+        return 0;
+    const unsigned int ts = a.tile_size, ucap = a.uniq_capacity;
+    if (a.n_views > 4 || !(ts == 32 || ts == 64 || ts == 128 || ts == 256) || ucap < 32 || ucap > 4096 || (ucap & (ucap - 1u)) || !a.d_uniq_count
+        || !a.d_uniq || !a.d_uniq_max)
+        return AZB_ERR_BAD_ARGUMENT;
+    for (unsigned int v = 0; v < a.n_views; ++v)
+        {
+        const unsigned int W = a.views[v].lane_width;
+        if (!(W == 1 || W == 2 || W == 4 || W == 8 || W == 16) || (a.views[v].d_keep_rsq && !a.views[v].d_row_count))
+            return AZB_ERR_BAD_ARGUMENT;
+        }
+    return 0;
     }
 
 template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Workspace& w, const CellGrid& g)
@@ -489,6 +810,12 @@ template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Wor
     d.tmp_rows = w.tmp_rows;
     d.row_stride = a.row_stride_hint;
     d.overflow = w.flags;
+    d.n_views = w.tables ? a.n_views : 0u;
+    d.tile_size = a.tile_size ? a.tile_size : 128u;
+    d.tables = w.tables;
+    d.tmp_slots = w.tmp_slots;
+    for (unsigned int v = 0; v < 4; ++v)
+        d.keep_rsq[v] = v < a.n_views ? (const S*)a.views[v].d_keep_rsq : nullptr;
     d.box = make_box<S>(a.box);
     d.grid = g;
     d.N = a.N;
@@ -511,11 +838,16 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     if (rc)
         return rc;
     const size_t cub_bytes = cub_temp_bytes(a.n_max, a.N);
-    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_bytes, a.row_stride_hint);
+    if ((rc = check_views(a)))
+        return rc;
+    const unsigned int n_tiles = plan_tiles(a);
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_bytes, a.row_stride_hint, n_tiles);
     if (w.bytes > a.workspace_bytes)
         return AZB_ERR_BAD_ARGUMENT;
     typedef typename vec4<S>::type s4;
     cudaError_t e = cudaMemsetAsync(w.flags, 0, 2 * sizeof(unsigned int), stream);
+    if (e == cudaSuccess)
+        e = cudaMemsetAsync(w.plan_status, 0, 16 * sizeof(unsigned int), stream);
     if (e != cudaSuccess)
         return (int)e;
     if (a.n_max)
@@ -529,6 +861,13 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
         cub::DeviceRadixSort::SortPairs(w.cub_tmp, tmp, w.cell, w.cell_sorted, w.idx, w.idx_sorted, (int)a.n_max, 0, bits, stream);
         cell_bounds_kernel<S><<<grd, blk, 0, stream>>>(w.cell_sorted, w.idx_sorted, a.n_max, (const s4*)a.d_pos, (s4*)w.pos_sorted, w.cell_begin,
                                                         (unsigned int)ncell);
+        }
+    if (n_tiles)
+        {
+        // the tiles' cell boxes and staging order first: the walk reads them to turn every accepted entry into a slot
+        tile_table_kernel<<<(n_tiles * 32 + 127) / 128, 128, 0, stream>>>(w.cell, a.N, a.tile_size, n_tiles, g, w.cell_begin, a.uniq_capacity, w.tables,
+                                                                          a.d_uniq_count, w.plan_status);
+        tile_uniq_kernel<<<n_tiles, 128, 0, stream>>>(w.tables, w.idx_sorted, a.uniq_capacity, a.d_uniq, a.d_uniq_max);
         }
     const NlistDev<S> d = make_dev<S>(a, w, g);
     const bool img = image_shifts_ok(g);
@@ -572,7 +911,10 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     int rc = make_grid(a, g, ncell);
     if (rc)
         return rc;
-    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N), a.row_stride_hint);
+    if ((rc = check_views(a)))
+        return rc;
+    const unsigned int n_tiles = plan_tiles(a);
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N), a.row_stride_hint, n_tiles);
     if (w.bytes > a.workspace_bytes || (a.N && !a.d_nlist))
         return AZB_ERR_BAD_ARGUMENT;
     if (!a.N)
@@ -588,8 +930,26 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
         }
     if (valid)
         {
+        ViewOut vo = {};
+        vo.n_views = n_tiles ? a.n_views : 0u;
+        vo.tile_size = a.tile_size ? a.tile_size : 128u;
+        vo.tmp_slots = w.tmp_slots;
+        vo.status = w.plan_status;
+        for (unsigned int v = 0; v < vo.n_views; ++v)
+            {
+            if (!a.views[v].d_slots)
+                return AZB_ERR_BAD_ARGUMENT;
+            vo.slots[v] = a.views[v].d_slots;
+            vo.row_count[v] = a.views[v].d_row_count;
+            vo.lane_width[v] = a.views[v].lane_width;
+            }
         const unsigned int grd = (unsigned int)(((size_t)a.N * 32 + 255) / 256);
-        nlist_compact_kernel<<<grd, 256, 0, stream>>>(w.tmp_rows, a.row_stride_hint, a.d_n_neigh, a.d_head_list, a.N, a.d_nlist, a.capacity);
+        nlist_compact_kernel<<<grd, 256, 0, stream>>>(w.tmp_rows, a.row_stride_hint, a.d_n_neigh, a.d_head_list, a.N, a.d_nlist, a.capacity, vo);
+        if (n_tiles)
+            {
+            const unsigned int one = 1u; // the views are complete (unless the table kernel flagged a tile: plan_status[1])
+            cudaMemcpyAsync(w.plan_status + 2, &one, sizeof(one), cudaMemcpyHostToDevice, stream);
+            }
         return (int)cudaGetLastError();
         }
     const NlistDev<S> d = make_dev<S>(a, w, g);
@@ -609,7 +969,37 @@ extern "C"
         const int rc = azb::make_grid(*a, g, ncell);
         if (rc)
             return rc;
-        *bytes = azb::carve(nullptr, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint).bytes;
+        *bytes = azb::carve(nullptr, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint, azb::plan_tiles(*a)).bytes;
+        return 0;
+        }
+
+    int azb_nlist_plan_result(const azb_nlist_args* a, azb_nlist_plan_status* st, void* stream)
+        {
+        if (!a || !st || !a->d_workspace)
+            return AZB_ERR_BAD_ARGUMENT;
+        *st = azb_nlist_plan_status();
+        const unsigned int n_tiles = azb::plan_tiles(*a);
+        if (!n_tiles)
+            return 0;
+        azb::CellGrid g;
+        size_t ncell;
+        const int rc = azb::make_grid(*a, g, ncell);
+        if (rc)
+            return rc;
+        const azb::Workspace w = azb::carve(a->d_workspace, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint, n_tiles);
+        unsigned int h[16];
+        cudaError_t e = cudaMemcpyAsync(h, w.plan_status, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize((cudaStream_t)stream);
+        if (e != cudaSuccess)
+            return (int)e;
+        st->ok = (h[2] == 1u && h[1] == 0u) ? 1u : 0u;
+        st->max_uniq = h[0];
+        for (unsigned int v = 0; v < 4; ++v)
+            {
+            st->max_slot_span[v] = h[4 + v];
+            st->n_entries[v] = (size_t)h[8 + 2 * v] | ((size_t)h[9 + 2 * v] << 32);
+            }
         return 0;
         }
 

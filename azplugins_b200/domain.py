@@ -580,10 +580,7 @@ class HaloExchange:
         if cached is not None and cached[0] is plan:
             return cached[1], cached[2]
         N = self.state.N
-        count = plan.uniq_count.long()
-        t = torch.arange(plan.n_tiles, device=count.device, dtype=torch.int64)
-        last = plan.uniq[t * plan.uniq_capacity + torch.clamp(count - 1, min=0)].long()
-        boundary = (count > 0) & (last >= N)
+        boundary = plan.tile_max() >= N
         order = torch.cat([torch.nonzero(~boundary).flatten(), torch.nonzero(boundary).flatten()]).to(torch.int32).contiguous()
         n_interior = int((~boundary).sum().item())
         self._order_cache = (plan, order, n_interior)

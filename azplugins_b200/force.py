@@ -145,15 +145,19 @@ class Pair(Force):
             return self.threads_per_particle
         return 2 if nbar <= 200 else 4
 
+    def _plan_request(self, nbar, require_built=True):
+        """What this force asks of a tile plan of its list: ``nl.tile_plan`` keyword arguments. The list build itself can emit
+        the plan when it knows the request beforehand (``nlist.NeighborList.build`` collects them from its consumers)."""
+        prune, prune_key = self._prune_spec(require_built)
+        return dict(tile_size=self.tile_size or self._auto_tile_size(nbar), lane_width=self._slot_lane_width(nbar),
+                    group_width=self._group_width(nbar) if prune is None else 0, prune=prune, prune_key=prune_key)
+
     def _current_plan(self):
         """Tile plan of the current neighbour list for this force's kernel (None: gather from global memory)."""
         if not (self.use_tiles and self._tiled_kernels) or self._state is None:
             return None
         st, nl = self._state, self.nlist
-        nbar = nl.mean_neighbors(st.N)
-        prune, prune_key = self._prune_spec()
-        return nl.tile_plan(st.N, self.tile_size or self._auto_tile_size(nbar), lane_width=self._slot_lane_width(nbar),
-                            group_width=self._group_width(nbar) if prune is None else 0, prune=prune, prune_key=prune_key)
+        return nl.tile_plan(st.N, **self._plan_request(nl.mean_neighbors(st.N)))
 
     # A force whose cutoffs are smaller than the list's (several forces sharing one list) walks a PRUNED view of it: entries
     # that were farther apart than r_cut + buffer when the list was built cannot be inside r_cut before the next rebuild
@@ -161,10 +165,12 @@ class Pair(Force):
     prune_lists = True
     _PRUNE_MIN_GAIN = 0.85
 
-    def _prune_spec(self):
+    def _prune_spec(self, require_built=True):
         st, nl = self._state, self.nlist
-        if not self.prune_lists or os.environ.get("AZB_NO_PRUNE", "0") == "1" or st is None or getattr(nl, "_last_pos", None) is None:
+        if not self.prune_lists or os.environ.get("AZB_NO_PRUNE", "0") == "1" or st is None:
             return None, None
+        if require_built and getattr(nl, "_last_pos", None) is None:
+            return None, None  # positions at build time unknown (externally built list)
         rc = self._r_cut_matrix(st.types)
         rl = nl.r_list(st.types)  # r_cut_max + buffer over all consumers of the list
         keep = np.where(rc > 0, rc + nl.buffer, 0.0)
@@ -177,7 +183,7 @@ class Pair(Force):
             ftype = scalar_dtype(st.scalar_bits)[0]
             k = keep.astype(ftype)
             self._prune_cache = (key, torch.from_numpy((k * k).reshape(-1)).to(st.device))
-        return (st, self._prune_cache[1]), key
+        return (st, self._prune_cache[1]), key[1:]
 
     def _auto_tile_size(self, nbar):
         """128 particles per tile for every kernel family. (With 256-thread CTAs, 256-particle tiles were 2 % faster for

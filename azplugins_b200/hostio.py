@@ -145,12 +145,8 @@ class HostStep:
 
     @staticmethod
     def _tile_hi(plan, N):
-        """Highest particle index a tile reads: its own last particle, or the last (largest) entry of its ascending uniq list."""
-        count = plan.uniq_count.cpu().numpy().astype(np.int64)
-        last = torch.arange(plan.n_tiles, device=plan.uniq.device, dtype=torch.int64) * plan.uniq_capacity + torch.from_numpy(
-            np.maximum(count - 1, 0)).to(plan.uniq.device)
-        hi = plan.uniq[last].cpu().numpy().astype(np.int64)
-        hi = np.where(count > 0, hi, 0)
+        """Highest particle index a tile reads: its own last particle, or the largest index it stages."""
+        hi = plan.tile_max().cpu().numpy().astype(np.int64)
         own_hi = np.minimum((np.arange(plan.n_tiles) + 1) * plan.tile_size, N) - 1
         return np.maximum(hi, own_hi)
 

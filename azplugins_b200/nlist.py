@@ -5,6 +5,8 @@
 ``pair_args_t`` (SURVEY.md §8 b); how it is produced is outside the reference (HOOMD's NeighborListGPU*).
 """
 
+import os
+
 import numpy as np
 import torch
 
@@ -33,6 +35,23 @@ class NeighborList:
         self.n_neigh = None
         self._tiles = {}
         self._last_pos = None
+
+    def plan_requests(self, state):
+        """Tile plans the consumers attached to ``state`` will ask for, by cache key — known BEFORE the list is built (from the
+        previous build's mean row length), so that the build can emit them from its own walk (``_nlist_gpu.build_cell_nlist``)."""
+        if not self.size_nlist or os.environ.get("AZB_NO_FUSED_PLANS", "0") == "1" or not getattr(self, "fused_plans", True):
+            return {}
+        nbar = self.size_nlist / max(state.N, 1)
+        out = {}
+        for f in self._consumers:
+            if getattr(f, "_state", None) is not state or not getattr(f, "use_tiles", False) or not getattr(f, "_tiled_kernels", False):
+                continue
+            req = f._plan_request(nbar, require_built=False)
+            if req["prune"] is not None and os.environ.get("AZB_FUSED_PRUNED", "1") != "1":
+                continue  # A/B switch: pruned views from the hash builder (tighter staged sets) instead of from the list build
+            key = (int(req["tile_size"]), 2048, int(req["lane_width"]), int(req["group_width"]), req["prune_key"])
+            out[key] = req
+        return out
 
     def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0, prune=None, prune_key=None):
         """Tile plan of the current arrays (``azb_tiles_build``), built once per list rebuild and cached; ``None`` when a

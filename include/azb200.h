@@ -255,6 +255,16 @@ AZB_API int azb_bond_forces(int potential,
  *                    synchronises the stream);
  *   azb_nlist_fill : writes d_nlist[capacity >= *h_total]; must follow azb_nlist_count with the same arguments and the
  *                    same workspace contents. Row order is deterministic (cell traversal, then particle index). */
+/* A tile-plan view emitted by the list build itself (azb_nlist_args.views): the slot rows of one consumer of the list. */
+typedef struct azb_nlist_view
+    {
+    unsigned int lane_width;   /* W of the slot-row layout (1: DPD kernels; else the pair kernel's lanes per particle) */
+    const void* d_keep_rsq;    /* NULL: every list entry. Else Scalar[ntypes*ntypes] of (r_cut + r_buff)^2 of THIS consumer: entries
+                                  beyond it are left out of its rows (pruned view, see azb_tile_build_args.d_prune_pos) */
+    uint16_t* d_slots;         /* out [AZB_SLOTS_SIZE(capacity, N, lane_width)]; needed by azb_nlist_fill only */
+    unsigned int* d_row_count; /* out [N] row lengths of this view (required when d_keep_rsq is set, optional otherwise) */
+    } azb_nlist_view;
+
 typedef struct azb_nlist_args
     {
     const void* d_pos;               /* Scalar4[n_max] */
@@ -279,11 +289,37 @@ typedef struct azb_nlist_args
                                         workspace in ONE walk and azb_nlist_fill only compacts them; a row that outgrows the bound
                                         makes azb_nlist_fill walk again (same result, deterministic row order either way). The
                                         workspace grows by 4 * N * row_stride_hint bytes. */
+    /* Tile plans from the same walk (optional; needs row_stride_hint > 0). The staged set of a tile of tile_size consecutive
+     * particles is taken from the cell structure instead of from a hash of its list entries: the cells of the tile's particles,
+     * one cell further in every direction, as contiguous ranges of the cell-ordered particle array; the walk then knows the slot
+     * of every entry it accepts (offset of its cell range in the tile's staging order + position in the range) at the cost of
+     * one addition, and azb_nlist_fill writes the slot rows of every view while it compacts the list rows. The staged set is a
+     * superset of the tile's distinct neighbours (about as large when particle order is spatially compact, e.g. HOOMD's SFC
+     * order); d_uniq is NOT ascending (d_uniq_max holds each tile's largest index). A tile whose set exceeds uniq_capacity, or
+     * whose cell box spans more than 32 (y, z) rows, makes the plans unusable (azb_nlist_plan_status.ok = 0): use
+     * azb_tiles_build then. */
+    unsigned int n_views;            /* 0..4 */
+    azb_nlist_view views[4];
+    unsigned int tile_size;          /* 32, 64, 128 or 256 */
+    unsigned int uniq_capacity;      /* power of two <= 4096 */
+    unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
+    unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
+    unsigned int* d_uniq_max;        /* out [ceil(N / tile_size)] largest particle index the tile stages */
     } azb_nlist_args;
+
+typedef struct azb_nlist_plan_status
+    {
+    unsigned int ok;            /* 1: the views of the last azb_nlist_count / azb_nlist_fill pair are complete */
+    unsigned int max_uniq;      /* largest staged set */
+    unsigned int max_slot_span[4]; /* per view: azb_tile_plan.max_slot_span */
+    size_t n_entries[4];        /* per view: sum of its row lengths */
+    } azb_nlist_plan_status;
 
 AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
 AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
+/* after azb_nlist_fill (synchronises the stream): outcome of the tile-plan views requested in args */
+AZB_API int azb_nlist_plan_result(const azb_nlist_args* args, azb_nlist_plan_status* status, void* stream);
 
 /* ---- tile plan builder: one call per neighbour-list rebuild (the host class calls it when HOOMD's
  * NeighborList::hasBeenUpdated(timestep) reports a rebuild). Writes d_uniq_count / d_uniq / d_slots and returns the

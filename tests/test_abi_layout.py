@@ -21,6 +21,8 @@ MIRRORS = {
     "azb_dpd_args": _abi.DPDArgs,
     "azb_aniso_args": _abi.AnisoArgs,
     "azb_bond_args": _abi.BondArgs,
+    "azb_nlist_view": _abi.NlistView,
+    "azb_nlist_plan_status": _abi.NlistPlanStatus,
     "azb_nlist_args": _abi.NlistArgs,
     "azb_nve_args": _abi.NveArgs,
     "azb_barrier_args": _abi.BarrierArgs,

@@ -141,3 +141,71 @@ def test_pruned_plan_gives_bit_identical_forces(bits):
     assert pruned._plan.row_count is not None  # same plans: the list was not rebuilt
     assert torch.equal(pruned._force, full._force) and torch.equal(pruned._virial, full._virial)
     assert float(pruned._force[:, :3].abs().sum()) > 0
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("periodic", [(True, True, True), (False, True, True)])
+def test_plans_emitted_by_the_list_build(bits, periodic):
+    """From the second build on the list is built in one walk and emits the tile plans its consumers ask for (cell-box staging
+    order instead of a hash of the entries): every slot must name the listed neighbour, pruned views must hold the rows the
+    hash builder's pruned plan holds, and the forces must equal the hash-built plans' bit for bit."""
+    import torch
+
+    from azplugins_b200 import pair, workloads as W
+
+    snap = W.yukawa_dpd_fluid(n=30000, seed=31, jitter=0.15)
+    if not all(periodic):
+        snap.box = az.Box(snap.box.Lx, snap.box.Ly, snap.box.Lz, periodic=periodic)
+    st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
+    cell = nlist.Cell(buffer=0.4)
+    d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
+    d.dt = 0.01
+    d.params[("A", "A")] = W.C5_DPD_PARAMS[("A", "A")]
+    d.threads_per_particle = 4
+    y = pair.ExpandedYukawa(nlist=cell, default_r_cut=2.0)
+    y.params[("A", "A")] = W.EY_PARAMS[("A", "A")]
+    for f in (d, y):
+        f._attach(st)
+        f.compute(2)  # first build: two walks, plans from azb_tiles_build
+    assert not d._plan.from_list_build and not y._plan.from_list_build and d._plan.row_count is not None
+    want = [(f._force.clone(), f._virial.clone(), None if f._plan.row_count is None else f._plan.row_count.clone()) for f in (d, y)]
+    cell.invalidate()
+    for f in (d, y):
+        f.compute(2)  # second build: one walk that also emits both views
+    n = st.N
+    nn = cell.n_neigh.cpu().numpy().view(np.uint32).astype(np.int64)
+    head = cell.head_list.cpu().numpy().view(np.uint64).astype(np.int64)
+    lst = cell.nlist.cpu().numpy().view(np.uint32).astype(np.int64)
+    for f, (force, virial, rows) in zip((d, y), want):
+        plan = f._plan
+        assert plan.from_list_build and plan.uniq is d._plan.uniq
+        W_, M = plan.lane_width, 4 * plan.lane_width
+        A = max(M, 8)
+        count = plan.uniq_count.cpu().numpy().view(np.uint32)
+        uniq = plan.uniq.cpu().numpy().view(np.uint32).reshape(plan.n_tiles, plan.uniq_capacity).astype(np.int64)
+        slots = plan.slots.cpu().numpy().view(np.uint16).astype(np.int64)
+        rc = nn if plan.row_count is None else plan.row_count.cpu().numpy().astype(np.int64)
+        if rows is not None:
+            assert np.array_equal(rc, rows.cpu().numpy())  # the pruned view holds the rows the hash builder's pruned plan holds
+        assert plan.entries == rc.sum() and plan.max_uniq == count.max() <= plan.uniq_capacity
+        tmax = plan.tile_max().cpu().numpy()
+        for t in range(0, plan.n_tiles, 7):
+            assert tmax[t] == uniq[t, : count[t]].max()
+            for i in range(t * plan.tile_size, min((t + 1) * plan.tile_size, n)):
+                sh = (head[i] + A * i) & ~(A - 1)
+                e = np.arange((rc[i] + M - 1) // M * M)
+                r = e % M
+                stored = slots[sh + (e - r) + 4 * (r % W_) + r // W_]
+                assert np.all(stored[rc[i]:] == 0) and np.all(stored[: rc[i]] < count[t])
+                named = uniq[t, stored[: rc[i]]]
+                row = lst[head[i] : head[i] + nn[i]]
+                if plan.row_count is None:
+                    assert np.array_equal(named, row)  # slot -> the listed neighbour, in list order
+                else:
+                    assert np.all(np.isin(named, row)) and len(np.unique(named)) == len(named)
+        assert torch.equal(f._force, force) and torch.equal(f._virial, virial)
+    # the A/B switch: same list, plans from the hash builder
+    cell.fused_plans = False
+    cell.invalidate()
+    d.compute(2)
+    assert not d._plan.from_list_build and torch.equal(d._force, want[0][0])
