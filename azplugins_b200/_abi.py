@@ -48,6 +48,7 @@ class TilePlan(C.Structure):
         ("d_slots", C.c_void_p),
         ("d_row_count", C.c_void_p),
         ("n_entries", C.c_size_t),
+        ("slot_row_stride", C.c_uint),
     ]
 
 
@@ -72,6 +73,10 @@ class TileBuildArgs(C.Structure):
         ("prune_ntypes", C.c_uint),
         ("prune_box", Box),
         ("d_row_count", C.c_void_p),
+        ("prune_full_set", C.c_uint),
+        ("d_tile_list", C.c_void_p),
+        ("n_tile_list", C.c_uint),
+        ("slot_row_stride", C.c_uint),
     ]
 
 
@@ -150,7 +155,7 @@ class NlistView(C.Structure):
 
 
 class NlistPlanStatus(C.Structure):
-    _fields_ = [("ok", C.c_uint), ("max_uniq", C.c_uint), ("max_slot_span", C.c_uint * 4), ("n_entries", C.c_size_t * 4)]
+    _fields_ = [("ok", C.c_uint), ("max_uniq", C.c_uint), ("max_slot_span", C.c_uint * 4), ("n_bad_tiles", C.c_uint)]
 
 
 class NlistArgs(C.Structure):
@@ -364,7 +369,7 @@ def load():
     lib.azb_nlist_fill.restype = C.c_int
     lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
     lib.azb_nlist_plan_result.restype = C.c_int
-    lib.azb_nlist_plan_result.argtypes = [C.POINTER(NlistArgs), C.POINTER(NlistPlanStatus), C.c_void_p]
+    lib.azb_nlist_plan_result.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(NlistPlanStatus), C.c_void_p]
     lib.azb_gather_scalar4.restype = C.c_int
     lib.azb_gather_scalar4.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.azb_tiles_build.restype = C.c_int

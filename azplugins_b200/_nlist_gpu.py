@@ -50,10 +50,16 @@ def build_cell_nlist(nl, state, row_align=1):
         uniq = torch.empty(n_tiles * 2048, dtype=torch.int32, device=dev)
         uniq_max = torch.zeros(n_tiles, dtype=torch.int32, device=dev)
         a.d_uniq_count, a.d_uniq, a.d_uniq_max = uniq_count.data_ptr(), uniq.data_ptr(), uniq_max.data_ptr()
-        view_rows = []
+        view_rows, view_slots, view_strides = [], [], []
         for v, key in enumerate(view_keys):
             prune = usable[key]["prune"]
             a.views[v].lane_width = key[2]
+            align = max(4 * key[2], 8)  # AZB_SLOT_ROW_ALIGN
+            stride = (a.row_stride_hint + align - 1) // align * align  # AZB_VIEW_SLOT_STRIDE
+            sl = torch.empty(max(state.N, 1) * stride, dtype=torch.int16, device=dev)
+            a.views[v].d_slots = sl.data_ptr()
+            view_slots.append(sl)
+            view_strides.append(stride)
             rc_t = torch.zeros(max(state.N, 1), dtype=torch.int32, device=dev) if prune is not None else None
             a.views[v].d_keep_rsq = prune[1].data_ptr() if prune is not None else None
             a.views[v].d_row_count = rc_t.data_ptr() if rc_t is not None else None
@@ -75,21 +81,43 @@ def build_cell_nlist(nl, state, row_align=1):
     _abi.check(lib.azb_nlist_count(state.scalar_bits, C.byref(a), C.byref(total), stream), "azb_nlist_count")
     nlist = torch.zeros(max(total.value, 1), dtype=torch.int32, device=dev)
     a.d_nlist, a.capacity = nlist.data_ptr(), max(total.value, 1)
-    view_slots = []
-    for v, key in enumerate(view_keys):
-        lw = key[2]
-        sl = torch.zeros(total.value + max(4 * lw, 8) * (state.N + 1), dtype=torch.int16, device=dev)  # AZB_SLOTS_SIZE
-        a.views[v].d_slots = sl.data_ptr()
-        view_slots.append(sl)
     _abi.check(lib.azb_nlist_fill(state.scalar_bits, C.byref(a), stream), "azb_nlist_fill")
     plans = {}
     if view_keys:
         status = _abi.NlistPlanStatus()
-        _abi.check(lib.azb_nlist_plan_result(C.byref(a), C.byref(status), stream), "azb_nlist_plan_result")
-        if status.ok:
+        _abi.check(lib.azb_nlist_plan_result(state.scalar_bits, C.byref(a), C.byref(status), stream), "azb_nlist_plan_result")
+        n_tiles = (state.N + a.tile_size - 1) // a.tile_size
+        good = bool(status.ok) and status.n_bad_tiles <= max(8, n_tiles // 5)
+        max_uniq = status.max_uniq
+        if good and status.n_bad_tiles:
+            # tiles whose particles sit in distant clumps (cell box too large): their rows come from the hash builder, with the
+            # distinct set of ALL their list entries so that every view can share it
+            bad = torch.nonzero(uniq_count == -1).flatten().to(torch.int32).contiguous()
+            scratch = torch.zeros(4, dtype=torch.int32, device=dev)
             for v, key in enumerate(view_keys):
-                plans[key] = TilePlanHandle(key[0], (state.N + key[0] - 1) // key[0], 2048, status.max_uniq, key[2], status.max_slot_span[v], uniq_count,
-                                            uniq, view_slots[v], 0.0, view_rows[v], int(status.n_entries[v]), uniq_max=uniq_max)
+                b = _abi.TileBuildArgs()
+                b.d_n_neigh, b.d_nlist, b.d_head_list = n_neigh.data_ptr(), nlist.data_ptr(), head_list.data_ptr()
+                b.size_nlist, b.N, b.tile_size, b.uniq_capacity, b.lane_width = int(total.value), state.N, key[0], 2048, key[2]
+                b.d_uniq_count, b.d_uniq, b.d_slots, b.d_status = uniq_count.data_ptr(), uniq.data_ptr(), view_slots[v].data_ptr(), scratch.data_ptr()
+                b.d_tile_list, b.n_tile_list = bad.data_ptr(), int(bad.numel())
+                b.slot_row_stride = view_strides[v]
+                prune = usable[key]["prune"]
+                if prune is not None:
+                    b.d_prune_pos, b.d_prune_rsq = state.pos.data_ptr(), prune[1].data_ptr()
+                    b.prune_scalar_bits, b.prune_ntypes, b.prune_box = state.scalar_bits, len(state.types), state.box.as_abi()
+                    b.d_row_count, b.prune_full_set = view_rows[v].data_ptr(), 1
+                mu, ms, ov = C.c_uint(0), C.c_uint(0), C.c_uint(0)
+                _abi.check(lib.azb_tiles_build(C.byref(b), C.byref(mu), C.byref(ms), C.byref(ov), stream), "azb_tiles_build")
+                good = good and not ov.value
+                max_uniq = max(max_uniq, mu.value)
+            if good:
+                cnt = uniq_count[bad.long()].long()
+                uniq_max[bad.long()] = uniq[bad.long() * 2048 + torch.clamp(cnt - 1, min=0)]  # ascending there: the last entry
+        if good:
+            for v, key in enumerate(view_keys):
+                entries = int(view_rows[v].sum().item()) if view_rows[v] is not None else int(total.value)
+                plans[key] = TilePlanHandle(key[0], n_tiles, 2048, max_uniq, key[2], status.max_slot_span[v], uniq_count, uniq, view_slots[v], 0.0,
+                                            view_rows[v], entries, uniq_max=uniq_max, slot_row_stride=view_strides[v])
     torch.cuda.current_stream(dev).synchronize()
     del keep
     nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
@@ -106,7 +134,7 @@ class TilePlanHandle:
     """Device arrays of one ``azb_tile_plan`` plus the C struct that points at them (kept alive together)."""
 
     def __init__(self, tile_size, n_tiles, uniq_capacity, max_uniq, lane_width, max_slot_span, uniq_count, uniq, slots, build_ms, row_count=None,
-                 entries=None, uniq_max=None):
+                 entries=None, uniq_max=None, slot_row_stride=0):
         self.uniq_count, self.uniq, self.slots, self.row_count = uniq_count, uniq, slots, row_count
         self.uniq_max = uniq_max  # plans emitted by the list build: the staged sets are not ascending, the largest index is kept apart
         self.from_list_build = uniq_max is not None
@@ -118,6 +146,7 @@ class TilePlanHandle:
         self.c.d_uniq_count, self.c.d_uniq, self.c.d_slots = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr()
         self.c.d_row_count = row_count.data_ptr() if row_count is not None else None
         self.c.n_entries = int(entries) if (entries is not None and row_count is not None) else 0
+        self.c.slot_row_stride = int(slot_row_stride)
 
     tile_size = property(lambda self: self.c.tile_size)
     n_tiles = property(lambda self: self.c.n_tiles)
@@ -125,6 +154,7 @@ class TilePlanHandle:
     max_uniq = property(lambda self: self.c.max_uniq)
     lane_width = property(lambda self: self.c.lane_width)
     max_slot_span = property(lambda self: self.c.max_slot_span)
+    slot_row_stride = property(lambda self: self.c.slot_row_stride)
 
     def pointer(self):
         return C.pointer(self.c)

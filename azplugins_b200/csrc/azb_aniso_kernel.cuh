@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(256)
         if (active)
             {
             const unsigned int nn = __ldg(a.n_neigh + idx);
-            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
+            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + slot_row_begin(plan, a.head_list, idx, TPP)) + lane;
             const V4 pi = ld4(a.pos + idx);
             const V4 qi = ld4(d.orientation + idx);
             S nix, niy, niz;

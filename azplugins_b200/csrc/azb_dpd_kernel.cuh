@@ -416,7 +416,7 @@ __global__ void AZB_DPD_TILE_BOUNDS
         if (idx < a.N)
             {
             const unsigned int nn = __ldg(a.n_neigh + idx);
-            const char* r = reinterpret_cast<const char*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, 1));
+            const char* r = reinterpret_cast<const char*>(plan.slots + slot_row_begin(plan, a.head_list, idx, 1));
             for (unsigned int off = 0; off < nn * 2u; off += 128u)
                 prefetch_l2(r + off);
             if (p % 8u == 0u)
@@ -472,7 +472,7 @@ __global__ void AZB_DPD_TILE_BOUNDS
         if (active)
             {
             nn = __ldg(a.n_neigh + idx);
-            src.row = plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, 1);
+            src.row = plan.slots + slot_row_begin(plan, a.head_list, idx, 1);
             pi = ld4(a.pos + idx);
             vi = ld4(d.vel + idx);
             tag_i = __ldg(d.tag + idx);

@@ -124,6 +124,7 @@ inline int make_tile_plan(const azb_pair_args& a, unsigned int tpp, unsigned int
     plan.uniq_count = t.d_uniq_count;
     plan.uniq = t.d_uniq;
     plan.slots = t.d_slots;
+    plan.slot_stride = t.slot_row_stride;
     block = a.block_size ? pick_block(a.block_size) : default_block;
     if (block > ts * tpp)
         block = ts * tpp;

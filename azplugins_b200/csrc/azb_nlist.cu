@@ -80,7 +80,7 @@ __global__ void cell_bounds_kernel(const unsigned int* __restrict__ cell_sorted,
 // contiguous range of the cell-ordered array, split in up to three segments where it crosses the periodic x boundary (cells
 // reached through the low face, cells inside, cells reached through the high face). Slot of a particle = offset of its
 // segment in the tile's staging order + its position in the segment.
-constexpr unsigned int PLAN_ROWS_MAX = 32;
+constexpr unsigned int PLAN_ROWS_MAX = 64;
 struct TileTable
     {
     int x0, y0, z0;       // first cell of the box in unwrapped coordinates (may be negative / beyond the grid along periodic axes)
@@ -163,44 +163,63 @@ __global__ void __launch_bounds__(128) tile_table_kernel(const unsigned int* __r
     bool ok = rows <= PLAN_ROWS_MAX;
     const int X0 = cref[0] + lo[0], X1 = cref[0] + hi[0];
     TileTable& tt = tables[T];
-    unsigned int b[3] = {0, 0, 0}, len[3] = {0, 0, 0};
-    if (ok && lane < rows)
-        {
-        const int y = pos_mod(cref[1] + lo[1] + (int)(lane % ny), g.nc[1]);
-        const int z = pos_mod(cref[2] + lo[2] + (int)(lane / ny), g.nc[2]);
-        const unsigned int rb = (unsigned int)((z * g.nc[1] + y) * g.nc[0]);
-        const int nx = g.nc[0];
-        // low: unwrapped cells [X0, min(X1, -1)] live at +nx; main: [max(X0, 0), min(X1, nx - 1)]; high: [max(X0, nx), X1] at -nx
-        const int sa[3] = {X0, max(X0, 0), max(X0, nx)}, sb[3] = {min(X1, -1), min(X1, nx - 1), X1}, sh[3] = {nx, 0, -nx};
+    // lane l prepares rows l and l + 32
+    unsigned int b[2][3] = {{0, 0, 0}, {0, 0, 0}}, len[2][3] = {{0, 0, 0}, {0, 0, 0}};
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
-            if (sa[k] <= sb[k])
-                {
-                b[k] = cell_begin[rb + sa[k] + sh[k]];
-                len[k] = cell_begin[rb + sb[k] + sh[k] + 1] - b[k];
-                }
-        }
-    // exclusive scan of the row totals over the lanes
-    const unsigned int mine = len[0] + len[1] + len[2];
-    unsigned int incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1)
+    for (int h = 0; h < 2; ++h)
         {
-        const unsigned int v = __shfl_up_sync(FULL, incl, o);
-        if ((int)lane >= o)
-            incl += v;
-        }
-    const unsigned int total = __shfl_sync(FULL, incl, 31);
-    ok = ok && total <= ucap;
-    if (ok && lane < rows)
-        {
-        unsigned int off = incl - mine;
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
+        const unsigned int r = lane + 32u * h;
+        if (ok && r < rows)
             {
-            tt.begin[lane * 3 + k] = b[k];
-            tt.offset[lane * 3 + k] = off;
-            off += len[k];
+            const int y = pos_mod(cref[1] + lo[1] + (int)(r % ny), g.nc[1]);
+            const int z = pos_mod(cref[2] + lo[2] + (int)(r / ny), g.nc[2]);
+            const unsigned int rb = (unsigned int)((z * g.nc[1] + y) * g.nc[0]);
+            const int nx = g.nc[0];
+            // low: unwrapped cells [X0, min(X1, -1)] live at +nx; main: [max(X0, 0), min(X1, nx - 1)]; high: [max(X0, nx), X1] at -nx
+            const int sa[3] = {X0, max(X0, 0), max(X0, nx)}, sb[3] = {min(X1, -1), min(X1, nx - 1), X1}, sh[3] = {nx, 0, -nx};
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                if (sa[k] <= sb[k])
+                    {
+                    b[h][k] = cell_begin[rb + sa[k] + sh[k]];
+                    len[h][k] = cell_begin[rb + sb[k] + sh[k] + 1] - b[h][k];
+                    }
+            }
+        }
+    // exclusive scan of the row totals: rows 0..31 over the lanes, then rows 32..63 behind them
+    unsigned int base = 0, total = 0;
+    unsigned int off_row[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+        {
+        const unsigned int mine = len[h][0] + len[h][1] + len[h][2];
+        unsigned int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+            {
+            const unsigned int v = __shfl_up_sync(FULL, incl, o);
+            if ((int)lane >= o)
+                incl += v;
+            }
+        off_row[h] = base + incl - mine;
+        base += __shfl_sync(FULL, incl, 31);
+        }
+    total = base;
+    ok = ok && total <= ucap;
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+        {
+        const unsigned int r = lane + 32u * h;
+        if (ok && r < rows)
+            {
+            unsigned int off = off_row[h];
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                {
+                tt.begin[r * 3 + k] = b[h][k];
+                tt.offset[r * 3 + k] = off;
+                off += len[h][k];
+                }
             }
         }
     if (lane == 0)
@@ -217,7 +236,7 @@ __global__ void __launch_bounds__(128) tile_table_kernel(const unsigned int* __r
         if (ok)
             atomicMax(status + 0, total);
         else
-            atomicExch(status + 1, 1u);
+            atomicAdd(status + 1, 1u); // tiles left to azb_tiles_build (azb_tile_build_args.d_tile_list)
         }
     }
 
@@ -268,11 +287,13 @@ template<class S> struct NlistDev
     unsigned int* tmp_rows; // MODE_SINGLE: [N * row_stride] rows of fixed capacity, compacted afterwards
     unsigned int row_stride;
     unsigned int* overflow; // MODE_SINGLE: set when a row does not fit row_stride
-    // tile-plan views (MODE_SINGLE only): slot | view mask << 12 per accepted entry, next to the temporary list rows
+    // tile-plan views (MODE_SINGLE only): every view's slot rows are written straight from the walk, at a fixed stride
     unsigned int n_views, tile_size;
     const TileTable* tables;
-    uint16_t* tmp_slots;
     const S* keep_rsq[4];
+    uint16_t* view_slots[4];
+    unsigned int* view_rows[4];
+    unsigned int view_stride[4], view_w[4];
     Box<S> box;
     CellGrid grid;
     unsigned int N, n_max, ntypes;
@@ -356,9 +377,7 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
     const bool plan = MODE == MODE_SINGLE && a.n_views > 0;
     unsigned int slot_a = 0, slot_b = 0; // slot of the first particle of range a / b in the staging order of my tile
     int xa_cell = 0, xb_cell = 0;        // first cell (actual x) of range a / b
-    uint16_t* srow = nullptr;
-    if (plan && active)
-        srow = a.tmp_slots + (size_t)i * a.row_stride;
+    unsigned int vcount[4] = {0, 0, 0, 0}; // entries written to each view's slot row so far
     if (lane < 9u && active)
         {
         const int oz = (int)lane / 3 - 1, oy = (int)lane % 3 - 1;
@@ -453,7 +472,7 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                     const unsigned int sg = trw + (xu < 0 ? 0u : (xu >= a.grid.nc[0] ? 2u : 1u));
                     return tt.offset[sg] + (first - tt.begin[sg]);
                 };
-                if (tt.ny != 0u) // (an unusable tile voids the plans: azb_nlist_plan_status.ok = 0)
+                if (tt.ny != 0u) // (a tile with too large a cell box gets its slots from azb_tiles_build afterwards)
                     {
                     if (a1 > a0)
                         slot_a = slot_of(xa_cell, a0);
@@ -495,8 +514,8 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                     packed = slot0 + (s - s0);
 #pragma unroll
                     for (unsigned int v = 0; v < 4; ++v)
-                        if (v < a.n_views && (a.keep_rsq[v] == nullptr || rsq <= a.keep_rsq[v][tp] * S(1.00001)))
-                            packed |= 0x1000u << v;
+                        if (v < a.n_views && a.keep_rsq[v] != nullptr && rsq <= a.keep_rsq[v][tp] * S(1.00001))
+                            packed |= 0x1000u << v; // inside this (pruned) view's radius
                     }
                 }
             unsigned int j = 0;
@@ -513,11 +532,25 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                 {
                 const unsigned int slot = count + __popc(m & ltmask);
                 if (take && slot < row_cap)
-                    {
                     row[slot] = j;
-                    if (plan)
-                        srow[slot] = (uint16_t)packed;
-                    }
+                }
+            if (plan)
+                {
+#pragma unroll
+                for (unsigned int v = 0; v < 4; ++v)
+                    if (v < a.n_views)
+                        {
+                        // an unpruned view holds every accepted entry (same ballot as the list row); a pruned one its subset
+                        const bool kv = take && (a.keep_rsq[v] == nullptr || ((packed >> (12u + v)) & 1u));
+                        const unsigned int mv = a.keep_rsq[v] == nullptr ? m : __ballot_sync(FULL, kv);
+                        const unsigned int o = vcount[v] + __popc(mv & ltmask);
+                        if (kv && o < a.view_stride[v])
+                            {
+                            const unsigned int W = a.view_w[v], M = 4u * W, r = o % M;
+                            a.view_slots[v][(size_t)i * a.view_stride[v] + (o - r) + 4u * (r % W) + r / W] = (uint16_t)(packed & 0xfffu);
+                            }
+                        vcount[v] += __popc(mv & gmask);
+                        }
                 }
             count += __popc(m & gmask);
             }
@@ -536,76 +569,57 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
         if (MODE == MODE_SINGLE && count > a.row_stride)
             atomicExch(a.overflow, 1u);
         }
+    if (plan && active)
+        {
+#pragma unroll
+        for (unsigned int v = 0; v < 4; ++v)
+            if (v < a.n_views)
+                {
+                const unsigned int W = a.view_w[v], M = 4u * W;
+                const unsigned int n = min(vcount[v], a.view_stride[v]), np = (n + M - 1u) / M * M;
+                for (unsigned int o = n + lane; o < np; o += G) // pad the row to a whole block of 4 W entries with slot 0
+                    {
+                    const unsigned int r = o % M;
+                    a.view_slots[v][(size_t)i * a.view_stride[v] + (o - r) + 4u * (r % W) + r / W] = 0;
+                    }
+                if (lane == 0 && a.view_rows[v])
+                    a.view_rows[v][i] = n;
+                }
+        }
     }
 
-// MODE_SINGLE, second half: fixed-stride temporary rows -> the packed HOOMD rows at head_list (pure streaming copy), and the
-// slot rows of every tile-plan view in its lane-transposed, padded layout (AZB_SLOT_HEAD), filtered by the view's mask bit.
-struct ViewOut
-    {
-    uint16_t* slots[4];
-    unsigned int* row_count[4];
-    unsigned int lane_width[4];
-    unsigned int n_views, tile_size;
-    const uint16_t* tmp_slots;
-    unsigned int* status; // [4 + v] max slot span, [8 + 2 v] entries (64 bit)
-    };
-
+// MODE_SINGLE, second half: fixed-stride temporary rows -> the packed HOOMD rows at head_list. A pure streaming copy; each warp
+// moves four rows at a time so that their loads are in flight together (a row is only ~2 warp-wide loads long).
 __global__ void __launch_bounds__(256) nlist_compact_kernel(const unsigned int* __restrict__ tmp_rows, unsigned int row_stride,
                                                             const unsigned int* __restrict__ n_neigh, const size_t* __restrict__ head_list,
-                                                            unsigned int N, unsigned int* __restrict__ nlist, size_t capacity, const ViewOut vo)
+                                                            unsigned int N, unsigned int* __restrict__ nlist, size_t capacity)
     {
     const unsigned int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-    if (warp >= N)
+    const unsigned int i0 = warp * 4u;
+    if (i0 >= N)
         return;
-    const unsigned int i = warp;
-    const unsigned int nn = n_neigh[i];
-    const size_t head = head_list[i];
-    const unsigned int* src = tmp_rows + (size_t)i * row_stride;
-    for (unsigned int k = lane; k < nn; k += 32)
-        if (head + k < capacity)
-            nlist[head + k] = src[k];
-    for (unsigned int v = 0; v < vo.n_views; ++v)
+    unsigned int nn[4];
+    size_t head[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
         {
-        const unsigned int W = vo.lane_width[v], M = 4u * W;
-        const uint16_t* ssrc = vo.tmp_slots + (size_t)i * row_stride;
-        const size_t shead = AZB_SLOT_HEAD(head, i, W);
-        uint16_t* out = vo.slots[v];
-        unsigned int out_n = 0;
-        for (unsigned int k0 = 0; k0 < nn; k0 += 32)
-            {
-            const unsigned int k = k0 + lane;
-            unsigned int p = 0;
-            if (k < nn)
-                p = ssrc[k];
-            const bool keep = (p >> (12u + v)) & 1u;
-            const unsigned int m = __ballot_sync(0xffffffffu, keep);
-            if (keep)
-                {
-                const unsigned int o = out_n + __popc(m & ((1u << lane) - 1u));
-                const unsigned int r = o % M;
-                out[shead + (o - r) + 4u * (r % W) + r / W] = (uint16_t)(p & 0xfffu);
-                }
-            out_n += __popc(m);
-            }
-        const unsigned int out_p = (out_n + M - 1u) / M * M;
-        for (unsigned int o = out_n + lane; o < out_p; o += 32) // padding
-            {
-            const unsigned int r = o % M;
-            out[shead + (o - r) + 4u * (r % W) + r / W] = 0;
-            }
-        if (lane == 0)
-            {
-            if (vo.row_count[v])
-                vo.row_count[v][i] = out_n;
-            atomicAdd((unsigned long long*)(vo.status + 8 + 2 * v), (unsigned long long)out_n);
-            // extent of the tile's slot rows (kernels that stage them size their buffer by it): written by the tile's last row
-            if ((i + 1) % vo.tile_size == 0 || i + 1 == N)
-                {
-                const unsigned int first = (i / vo.tile_size) * vo.tile_size;
-                const unsigned int nnp = (nn + M - 1u) / M * M;
-                atomicMax(vo.status + 4 + v, (unsigned int)(shead + nnp - AZB_SLOT_HEAD(head_list[first], first, W)));
-                }
-            }
+        const bool in = i0 + u < N;
+        nn[u] = in ? n_neigh[i0 + u] : 0u;
+        head[u] = in ? head_list[i0 + u] : 0;
+        }
+    const unsigned int longest = max(max(nn[0], nn[1]), max(nn[2], nn[3]));
+    for (unsigned int k0 = 0; k0 < longest; k0 += 32)
+        {
+        const unsigned int k = k0 + lane;
+        unsigned int v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (k < nn[u])
+                v[u] = tmp_rows[(size_t)(i0 + u) * row_stride + k];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (k < nn[u] && head[u] + k < capacity)
+                nlist[head[u] + k] = v[u];
         }
     }
 
@@ -677,9 +691,8 @@ struct Workspace
     size_t* total;
     unsigned int* flags;    // [0] overflow of a fixed-stride row, [1] 1 = the single-walk rows are valid (fill only compacts)
     unsigned int* tmp_rows; // [N * row_stride] when row_stride_hint > 0
-    unsigned int* plan_status; // 16 words: [0] max staged set, [1] unusable tile seen, [4 + v] max slot span, [8 + 2 v] entries (u64)
+    unsigned int* plan_status; // 16 words: [0] max staged set, [1] tiles with too large a cell box, [2] views written, [4 + v] max slot span
     TileTable* tables;         // [n_tiles] when views are requested
-    uint16_t* tmp_slots;       // [N * row_stride] when views are requested
     void* cub_tmp;
     size_t cub_bytes;
     size_t bytes;
@@ -753,7 +766,6 @@ static Workspace carve(void* base, unsigned int n_max, unsigned int N, size_t nc
     w.tmp_rows = row_stride ? (unsigned int*)take(4 * (size_t)row_stride * (N ? N : 1)) : nullptr;
     w.plan_status = (unsigned int*)take(16 * sizeof(unsigned int));
     w.tables = (row_stride && n_tiles) ? (TileTable*)take(sizeof(TileTable) * (size_t)n_tiles) : nullptr;
-    w.tmp_slots = (row_stride && n_tiles) ? (uint16_t*)take(2 * (size_t)row_stride * (N ? N : 1)) : nullptr;
     w.bytes = off;
     return w;
     }
@@ -786,7 +798,8 @@ static int check_views(const azb_nlist_args& a)
     for (unsigned int v = 0; v < a.n_views; ++v)
         {
         const unsigned int W = a.views[v].lane_width;
-        if (!(W == 1 || W == 2 || W == 4 || W == 8 || W == 16) || (a.views[v].d_keep_rsq && !a.views[v].d_row_count))
+        if (!(W == 1 || W == 2 || W == 4 || W == 8 || W == 16) || (a.views[v].d_keep_rsq && !a.views[v].d_row_count)
+            || (a.row_stride_hint && !a.views[v].d_slots))
             return AZB_ERR_BAD_ARGUMENT;
         }
     return 0;
@@ -813,9 +826,15 @@ template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Wor
     d.n_views = w.tables ? a.n_views : 0u;
     d.tile_size = a.tile_size ? a.tile_size : 128u;
     d.tables = w.tables;
-    d.tmp_slots = w.tmp_slots;
     for (unsigned int v = 0; v < 4; ++v)
-        d.keep_rsq[v] = v < a.n_views ? (const S*)a.views[v].d_keep_rsq : nullptr;
+        {
+        const bool on = v < d.n_views;
+        d.keep_rsq[v] = on ? (const S*)a.views[v].d_keep_rsq : nullptr;
+        d.view_slots[v] = on ? a.views[v].d_slots : nullptr;
+        d.view_rows[v] = on ? a.views[v].d_row_count : nullptr;
+        d.view_w[v] = on ? a.views[v].lane_width : 1u;
+        d.view_stride[v] = on ? (unsigned int)AZB_VIEW_SLOT_STRIDE(a.row_stride_hint, a.views[v].lane_width) : 0u;
+        }
     d.box = make_box<S>(a.box);
     d.grid = g;
     d.N = a.N;
@@ -930,21 +949,8 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
         }
     if (valid)
         {
-        ViewOut vo = {};
-        vo.n_views = n_tiles ? a.n_views : 0u;
-        vo.tile_size = a.tile_size ? a.tile_size : 128u;
-        vo.tmp_slots = w.tmp_slots;
-        vo.status = w.plan_status;
-        for (unsigned int v = 0; v < vo.n_views; ++v)
-            {
-            if (!a.views[v].d_slots)
-                return AZB_ERR_BAD_ARGUMENT;
-            vo.slots[v] = a.views[v].d_slots;
-            vo.row_count[v] = a.views[v].d_row_count;
-            vo.lane_width[v] = a.views[v].lane_width;
-            }
-        const unsigned int grd = (unsigned int)(((size_t)a.N * 32 + 255) / 256);
-        nlist_compact_kernel<<<grd, 256, 0, stream>>>(w.tmp_rows, a.row_stride_hint, a.d_n_neigh, a.d_head_list, a.N, a.d_nlist, a.capacity, vo);
+        const unsigned int grd = (unsigned int)((((size_t)a.N + 3) / 4 * 32 + 255) / 256);
+        nlist_compact_kernel<<<grd, 256, 0, stream>>>(w.tmp_rows, a.row_stride_hint, a.d_n_neigh, a.d_head_list, a.N, a.d_nlist, a.capacity);
         if (n_tiles)
             {
             const unsigned int one = 1u; // the views are complete (unless the table kernel flagged a tile: plan_status[1])
@@ -973,10 +979,12 @@ extern "C"
         return 0;
         }
 
-    int azb_nlist_plan_result(const azb_nlist_args* a, azb_nlist_plan_status* st, void* stream)
+    int azb_nlist_plan_result(int scalar_bits, const azb_nlist_args* a, azb_nlist_plan_status* st, void* stream)
         {
         if (!a || !st || !a->d_workspace)
             return AZB_ERR_BAD_ARGUMENT;
+        if (scalar_bits != 32 && scalar_bits != 64)
+            return AZB_ERR_BAD_SCALAR;
         *st = azb_nlist_plan_status();
         const unsigned int n_tiles = azb::plan_tiles(*a);
         if (!n_tiles)
@@ -986,20 +994,20 @@ extern "C"
         const int rc = azb::make_grid(*a, g, ncell);
         if (rc)
             return rc;
-        const azb::Workspace w = azb::carve(a->d_workspace, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint, n_tiles);
+        // (the same carve as azb_nlist_count / azb_nlist_fill: the workspace layout depends on sizeof(Scalar4))
+        const azb::Workspace w = azb::carve(a->d_workspace, a->n_max, a->N, ncell, scalar_bits == 32 ? 16 : 32, azb::cub_temp_bytes(a->n_max, a->N),
+                                            a->row_stride_hint, n_tiles);
         unsigned int h[16];
         cudaError_t e = cudaMemcpyAsync(h, w.plan_status, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
         if (e == cudaSuccess)
             e = cudaStreamSynchronize((cudaStream_t)stream);
         if (e != cudaSuccess)
             return (int)e;
-        st->ok = (h[2] == 1u && h[1] == 0u) ? 1u : 0u;
+        st->ok = h[2] == 1u ? 1u : 0u;
+        st->n_bad_tiles = h[1];
         st->max_uniq = h[0];
         for (unsigned int v = 0; v < 4; ++v)
-            {
-            st->max_slot_span[v] = h[4 + v];
-            st->n_entries[v] = (size_t)h[8 + 2 * v] | ((size_t)h[9 + 2 * v] << 32);
-            }
+            st->max_slot_span[v] = v < a->n_views ? (unsigned int)(a->tile_size * AZB_VIEW_SLOT_STRIDE(a->row_stride_hint, a->views[v].lane_width)) : 0u;
         return 0;
         }
 

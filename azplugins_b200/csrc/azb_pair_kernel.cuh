@@ -46,7 +46,16 @@ struct TilePlanDev
     const unsigned int* uniq_count;
     const unsigned int* uniq;
     const uint16_t* slots;
+    unsigned int slot_stride; // > 0: the slot row of particle i starts at i * slot_stride instead of AZB_SLOT_HEAD(head_list[i], i, W)
     };
+
+// first entry of a particle's slot row
+__device__ __forceinline__ size_t slot_row_begin(const TilePlanDev& plan, const size_t* __restrict__ head_list, unsigned int idx, unsigned int W)
+    {
+    if (plan.slot_stride)
+        return (size_t)idx * plan.slot_stride;
+    return AZB_SLOT_HEAD(__ldg(head_list + idx), idx, W);
+    }
 
 template<int TPP, class S> __device__ __forceinline__ S group_sum(S v)
     {
@@ -271,7 +280,7 @@ __device__ __forceinline__ void warm_tile_rows(const PairArgsDev<S>& a, const Ti
         if (idx < a.N)
             {
             const unsigned int nn = __ldg(a.n_neigh + idx);
-            const char* r = reinterpret_cast<const char*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, W));
+            const char* r = reinterpret_cast<const char*>(plan.slots + slot_row_begin(plan, a.head_list, idx, W));
             for (unsigned int off = 0; off < nn * 2u; off += 128u)
                 prefetch_l2(r + off);
             if (p % (128u / (unsigned int)sizeof(typename vec4<S>::type)) == 0u)
@@ -352,7 +361,7 @@ __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, 
         if (active)
             {
             const unsigned int nn = __ldg(a.n_neigh + idx);
-            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
+            const uint2* row = reinterpret_cast<const uint2*>(plan.slots + slot_row_begin(plan, a.head_list, idx, TPP)) + lane;
             const V4 pi = ld4(a.pos + idx);
             const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
 

@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256, 4) plj_packed_tile_kernel(const PairArgsD
         if (p < plan.tile_size && idx < a.N)
             {
             nn_next = __ldg(a.n_neigh + idx);
-            row_next = reinterpret_cast<const uint2*>(plan.slots + AZB_SLOT_HEAD(__ldg(a.head_list + idx), idx, TPP)) + lane;
+            row_next = reinterpret_cast<const uint2*>(plan.slots + slot_row_begin(plan, a.head_list, idx, TPP)) + lane;
             pi_next = ld4(a.pos + idx);
             if (nn_next)
                 pkt_next = __ldg(row_next);

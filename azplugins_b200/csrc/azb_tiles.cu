@@ -74,7 +74,8 @@ template<class S> __device__ __forceinline__ bool kept(const PruneDev<S>& p, con
 
 // dynamic shared memory: keys[hcap] u32 | list[ucap] u32 | vals[hcap] u16
 template<class Prune>
-__global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, unsigned int* __restrict__ row_count,
+__global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, const bool full_set, const unsigned int* __restrict__ tile_list,
+                                                          const unsigned int slot_stride, unsigned int* __restrict__ row_count,
                                                           const unsigned int* __restrict__ n_neigh,
                                                           const unsigned int* __restrict__ nlist,
                                                           const size_t* __restrict__ head_list,
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, uns
     uint16_t* vals = reinterpret_cast<uint16_t*>(list + ucap);
     __shared__ unsigned int s_count, s_fill;
 
-    const unsigned int tile = blockIdx.x;
+    const unsigned int tile = tile_list ? tile_list[blockIdx.x] : blockIdx.x;
     const unsigned int first = tile * tile_size;
     const unsigned int last = min(first + tile_size, N);
     const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, uns
         for (unsigned int k = lane; k < nn; k += 32)
             {
             const unsigned int j = row[k];
-            if (!kept(prune, own, j))
+            if (!full_set && !kept(prune, own, j))
                 continue;
             unsigned int h = tile_hash(j, hshift);
             while (*(volatile unsigned int*)&s_count <= ucap)
@@ -222,7 +223,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, uns
         {
         const unsigned int nn = n_neigh[i];
         const size_t head = head_list[i];
-        const size_t shead = AZB_SLOT_HEAD(head, i, W);
+        const size_t shead = slot_stride ? (size_t)i * slot_stride : AZB_SLOT_HEAD(head, i, W);
         const unsigned int nnp = (nn + M - 1u) / M * M;
         if (G == 0u)
             {
@@ -335,7 +336,7 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, uns
         if (lane == 0 && i + 1 < N && head_list[i + 1] < head + nn)
             atomicExch(status + 1, 2u);
         if (lane == 0 && i + 1 == last) // extent of the tile's slot rows (kernels that stage them size their buffer by it)
-            atomicMax(status + 2, (unsigned int)(shead + nnp - AZB_SLOT_HEAD(head_list[first], first, W)));
+            atomicMax(status + 2, (unsigned int)(shead + nnp - (slot_stride ? (size_t)first * slot_stride : AZB_SLOT_HEAD(head_list[first], first, W))));
         }
     }
     } // namespace azb
@@ -367,7 +368,9 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
     cudaError_t err = cudaMemsetAsync(a->d_status, 0, 4 * sizeof(unsigned int), s);
     if (err != cudaSuccess)
         return (int)err;
-    const unsigned int n_tiles = (a->N + ts - 1) / ts;
+    const unsigned int n_tiles = a->d_tile_list ? a->n_tile_list : (a->N + ts - 1) / ts;
+    if (n_tiles == 0)
+        return 0;
     const bool prune = a->d_prune_pos != nullptr;
     if (prune && (!a->d_prune_rsq || !a->d_row_count || a->prune_ntypes == 0 || G != 0u || (a->prune_scalar_bits != 32 && a->prune_scalar_bits != 64)))
         return AZB_ERR_BAD_ARGUMENT;
@@ -380,7 +383,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
             if (err != cudaSuccess)                                                                                                     \
                 return (int)err;                                                                                                        \
             }                                                                                                                           \
-        azb::tiles_build_kernel<PRUNE_T><<<n_tiles, 256, smem, s>>>(PRUNE_V, a->d_row_count, a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, \
+        azb::tiles_build_kernel<PRUNE_T><<<n_tiles, 256, smem, s>>>(PRUNE_V, a->prune_full_set != 0, a->d_tile_list, a->slot_row_stride, a->d_row_count, a->d_n_neigh, a->d_nlist, a->d_head_list, a->N, ts, \
                                                                    ucap, hcap_log2, W, G, a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status); \
         } while (0)
     if (!prune)

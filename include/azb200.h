@@ -134,7 +134,10 @@ typedef struct azb_tile_plan
                                          PRUNED plan (azb_tile_build_args.d_prune_pos): entries that cannot come inside this
                                          force's cutoff before the next list rebuild are left out of its slot rows */
     size_t n_entries;                 /* sum of the rows' lengths (0 = the list's size_nlist); launchers size their lane groups by it */
+    unsigned int slot_row_stride;     /* 0: the slot row of particle i starts at AZB_SLOT_HEAD(head_list[i], i, W). > 0: at i * slot_row_stride
+                                         (plans emitted by the list build write fixed-stride slot rows straight from the walk) */
     } azb_tile_plan;
+#define AZB_VIEW_SLOT_STRIDE(row_stride, W) ((((size_t)(row_stride) + AZB_SLOT_ROW_ALIGN(W) - 1) / AZB_SLOT_ROW_ALIGN(W)) * AZB_SLOT_ROW_ALIGN(W))
 
 /* mirrors HOOMD pair_args_t */
 typedef struct azb_pair_args
@@ -261,7 +264,8 @@ typedef struct azb_nlist_view
     unsigned int lane_width;   /* W of the slot-row layout (1: DPD kernels; else the pair kernel's lanes per particle) */
     const void* d_keep_rsq;    /* NULL: every list entry. Else Scalar[ntypes*ntypes] of (r_cut + r_buff)^2 of THIS consumer: entries
                                   beyond it are left out of its rows (pruned view, see azb_tile_build_args.d_prune_pos) */
-    uint16_t* d_slots;         /* out [AZB_SLOTS_SIZE(capacity, N, lane_width)]; needed by azb_nlist_fill only */
+    uint16_t* d_slots;         /* out [N * AZB_VIEW_SLOT_STRIDE(row_stride_hint, lane_width)]: fixed-stride slot rows
+                                  (azb_tile_plan.slot_row_stride), written by azb_nlist_count */
     unsigned int* d_row_count; /* out [N] row lengths of this view (required when d_keep_rsq is set, optional otherwise) */
     } azb_nlist_view;
 
@@ -296,8 +300,8 @@ typedef struct azb_nlist_args
      * one addition, and azb_nlist_fill writes the slot rows of every view while it compacts the list rows. The staged set is a
      * superset of the tile's distinct neighbours (about as large when particle order is spatially compact, e.g. HOOMD's SFC
      * order); d_uniq is NOT ascending (d_uniq_max holds each tile's largest index). A tile whose set exceeds uniq_capacity, or
-     * whose cell box spans more than 32 (y, z) rows, makes the plans unusable (azb_nlist_plan_status.ok = 0): use
-     * azb_tiles_build then. */
+     * whose cell box spans more than 64 (y, z) rows (a tile whose particles sit in two distant clumps), gets
+     * d_uniq_count = 0xffffffff and is left to azb_tiles_build (d_tile_list); azb_nlist_plan_status counts them. */
     unsigned int n_views;            /* 0..4 */
     azb_nlist_view views[4];
     unsigned int tile_size;          /* 32, 64, 128 or 256 */
@@ -309,17 +313,18 @@ typedef struct azb_nlist_args
 
 typedef struct azb_nlist_plan_status
     {
-    unsigned int ok;            /* 1: the views of the last azb_nlist_count / azb_nlist_fill pair are complete */
+    unsigned int ok;            /* 1: the views of the last azb_nlist_count / azb_nlist_fill pair were written (single walk succeeded) */
     unsigned int max_uniq;      /* largest staged set */
     unsigned int max_slot_span[4]; /* per view: azb_tile_plan.max_slot_span */
-    size_t n_entries[4];        /* per view: sum of its row lengths */
+    unsigned int n_bad_tiles;   /* tiles whose cell box was too large (their uniq_count is 0xffffffff): give them to
+                                   azb_tiles_build through azb_tile_build_args.d_tile_list and the views are complete */
     } azb_nlist_plan_status;
 
 AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
 AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
 /* after azb_nlist_fill (synchronises the stream): outcome of the tile-plan views requested in args */
-AZB_API int azb_nlist_plan_result(const azb_nlist_args* args, azb_nlist_plan_status* status, void* stream);
+AZB_API int azb_nlist_plan_result(int scalar_bits, const azb_nlist_args* args, azb_nlist_plan_status* status, void* stream);
 
 /* ---- tile plan builder: one call per neighbour-list rebuild (the host class calls it when HOOMD's
  * NeighborList::hasBeenUpdated(timestep) reports a rebuild). Writes d_uniq_count / d_uniq / d_slots and returns the
@@ -355,6 +360,13 @@ typedef struct azb_tile_build_args
     unsigned int prune_ntypes;
     azb_box prune_box;
     unsigned int* d_row_count;       /* out [N], required with d_prune_pos */
+    unsigned int prune_full_set;     /* 1: prune the slot rows but stage the distinct neighbours of ALL list entries (views of one list
+                                        that share d_uniq) */
+    const unsigned int* d_tile_list; /* NULL: every tile. Else device array of the n_tile_list tiles to (re)build; the other tiles'
+                                        rows of d_uniq_count / d_uniq / d_slots / d_row_count are left alone (the tiles the list
+                                        build could not plan itself: azb_nlist_plan_status.n_bad_tiles) */
+    unsigned int n_tile_list;
+    unsigned int slot_row_stride;    /* 0: slot rows at AZB_SLOT_HEAD(head_list[i], i, lane_width); > 0: at i * slot_row_stride */
     } azb_tile_build_args;
 
 AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,

@@ -192,7 +192,7 @@ def test_plans_emitted_by_the_list_build(bits, periodic):
         for t in range(0, plan.n_tiles, 7):
             assert tmax[t] == uniq[t, : count[t]].max()
             for i in range(t * plan.tile_size, min((t + 1) * plan.tile_size, n)):
-                sh = (head[i] + A * i) & ~(A - 1)
+                sh = i * plan.slot_row_stride if plan.slot_row_stride else (head[i] + A * i) & ~(A - 1)
                 e = np.arange((rc[i] + M - 1) // M * M)
                 r = e % M
                 stored = slots[sh + (e - r) + 4 * (r % W_) + r // W_]
