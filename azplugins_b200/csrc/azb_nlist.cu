@@ -293,7 +293,7 @@ template<class S> struct NlistDev
     const S* keep_rsq[4];
     uint16_t* view_slots[4];
     unsigned int* view_rows[4];
-    unsigned int view_stride[4], view_w[4];
+    unsigned int view_stride[4], view_wlog[4]; // slot-row stride (entries); log2 of the lane width W of the row layout
     Box<S> box;
     CellGrid grid;
     unsigned int N, n_max, ntypes;
@@ -378,6 +378,14 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
     unsigned int slot_a = 0, slot_b = 0; // slot of the first particle of range a / b in the staging order of my tile
     int xa_cell = 0, xb_cell = 0;        // first cell (actual x) of range a / b
     unsigned int vcount[4] = {0, 0, 0, 0}; // entries written to each view's slot row so far
+    uint16_t* vrow[4] = {nullptr, nullptr, nullptr, nullptr};
+    if (plan && active)
+        {
+#pragma unroll
+        for (unsigned int v = 0; v < 4; ++v)
+            if (v < a.n_views)
+                vrow[v] = a.view_slots[v] + (size_t)i * a.view_stride[v];
+        }
     if (lane < 9u && active)
         {
         const int oz = (int)lane / 3 - 1, oy = (int)lane % 3 - 1;
@@ -546,8 +554,9 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                         const unsigned int o = vcount[v] + __popc(mv & ltmask);
                         if (kv && o < a.view_stride[v])
                             {
-                            const unsigned int W = a.view_w[v], M = 4u * W, r = o % M;
-                            a.view_slots[v][(size_t)i * a.view_stride[v] + (o - r) + 4u * (r % W) + r / W] = (uint16_t)(packed & 0xfffu);
+                            // lane-transposed block layout (include/azb200.h): entry o = b * 4W + u * W + l sits at b * 4W + 4 l + u
+                            const unsigned int wl = a.view_wlog[v], r = o & ((4u << wl) - 1u);
+                            vrow[v][(o - r) + 4u * (r & ((1u << wl) - 1u)) + (r >> wl)] = (uint16_t)(packed & 0xfffu);
                             }
                         vcount[v] += __popc(mv & gmask);
                         }
@@ -575,12 +584,12 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
         for (unsigned int v = 0; v < 4; ++v)
             if (v < a.n_views)
                 {
-                const unsigned int W = a.view_w[v], M = 4u * W;
-                const unsigned int n = min(vcount[v], a.view_stride[v]), np = (n + M - 1u) / M * M;
+                const unsigned int wl = a.view_wlog[v], M = 4u << wl;
+                const unsigned int n = min(vcount[v], a.view_stride[v]), np = (n + M - 1u) & ~(M - 1u);
                 for (unsigned int o = n + lane; o < np; o += G) // pad the row to a whole block of 4 W entries with slot 0
                     {
-                    const unsigned int r = o % M;
-                    a.view_slots[v][(size_t)i * a.view_stride[v] + (o - r) + 4u * (r % W) + r / W] = 0;
+                    const unsigned int r = o & (M - 1u);
+                    vrow[v][(o - r) + 4u * (r & ((1u << wl) - 1u)) + (r >> wl)] = 0;
                     }
                 if (lane == 0 && a.view_rows[v])
                     a.view_rows[v][i] = n;
@@ -832,7 +841,10 @@ template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Wor
         d.keep_rsq[v] = on ? (const S*)a.views[v].d_keep_rsq : nullptr;
         d.view_slots[v] = on ? a.views[v].d_slots : nullptr;
         d.view_rows[v] = on ? a.views[v].d_row_count : nullptr;
-        d.view_w[v] = on ? a.views[v].lane_width : 1u;
+        unsigned int wl = 0;
+        while (on && (1u << wl) < a.views[v].lane_width)
+            ++wl;
+        d.view_wlog[v] = wl;
         d.view_stride[v] = on ? (unsigned int)AZB_VIEW_SLOT_STRIDE(a.row_stride_hint, a.views[v].lane_width) : 0u;
         }
     d.box = make_box<S>(a.box);
@@ -1032,4 +1044,5 @@ extern "C"
             return azb::nlist_fill<double>(*a, (cudaStream_t)stream);
         return AZB_ERR_BAD_SCALAR;
         }
+
     }

@@ -39,7 +39,14 @@ class NeighborList:
     def plan_requests(self, state):
         """Tile plans the consumers attached to ``state`` will ask for, by cache key — known BEFORE the list is built (from the
         previous build's mean row length), so that the build can emit them from its own walk (``_nlist_gpu.build_cell_nlist``)."""
-        if not self.size_nlist or os.environ.get("AZB_NO_FUSED_PLANS", "0") == "1" or not getattr(self, "fused_plans", True):
+        # OFF by default (opt in: ``cell.fused_plans = True`` or AZB_FUSED_PLANS=1). Measured on B200 (profiles/r2_rebuild_paths.txt):
+        # the list build + plans get cheaper (C5 8 M: 24.0 ms against 13.6 + 14.6 ms; LJ 4 M: 16.9 against 15.0 + 7.0 ms) but the
+        # cell-box staged sets are supersets of the hash builder's distinct sets, the force kernels stage more and lose
+        # occupancy, and a whole MD step gets SLOWER (C5: 11.6 against 10.7 ms per step; DPD 1 M: 1.45 against 1.24 ms).
+        on = getattr(self, "fused_plans", None)
+        if on is None:
+            on = os.environ.get("AZB_FUSED_PLANS", "0") == "1"
+        if not self.size_nlist or os.environ.get("AZB_NO_FUSED_PLANS", "0") == "1" or not on:
             return {}
         nbar = self.size_nlist / max(state.N, 1)
         out = {}

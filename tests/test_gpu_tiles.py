@@ -158,6 +158,7 @@ def test_plans_emitted_by_the_list_build(bits, periodic):
         snap.box = az.Box(snap.box.Lx, snap.box.Ly, snap.box.Lz, periodic=periodic)
     st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
     cell = nlist.Cell(buffer=0.4)
+    cell.fused_plans = True  # opt-in (off by default: see nlist.NeighborList.plan_requests)
     d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
     d.dt = 0.01
     d.params[("A", "A")] = W.C5_DPD_PARAMS[("A", "A")]

@@ -19,6 +19,7 @@ def main():
     snap = W.yukawa_dpd_fluid(n=32000, seed=3)
     st = az.State(snap, device="cuda", scalar_bits=32, seed=42)
     cell = nlist.Cell(buffer=0.4)
+    cell.fused_plans = True
     d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
     d.dt = 0.01
     d.params[("A", "A")] = W.C5_DPD_PARAMS[("A", "A")]
