@@ -13,6 +13,8 @@ ABI_VERSION = 3
 ERR_BAD_POTENTIAL = 10001
 ERR_BAD_SCALAR = 10002
 ERR_BAD_ARGUMENT = 10003
+ERR_STATIC_SCRATCH_TOO_SMALL = 10005
+STATIC_WORKSPACE_BYTES = 16 * 1024 * 1024
 
 KIND_PAIR, KIND_DPD, KIND_ANISO, KIND_BOND = 0, 1, 2, 3
 PAIR_PERTURBED_LENNARD_JONES, PAIR_COLLOID, PAIR_EXPANDED_YUKAWA, PAIR_HERTZ, PAIR_DPD_CONSERVATIVE = range(5)
@@ -208,6 +210,7 @@ EXPORTS = (
     "azb_nlist_count",
     "azb_nlist_fill",
     "azb_nlist_plan_result",
+    "azb_nlist_build_static",
     "azb_gather_scalar4",
     "azb_tiles_build",
     "azb_barrier_forces",
@@ -368,6 +371,8 @@ def load():
     lib.azb_nlist_count.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(C.c_size_t), C.c_void_p]
     lib.azb_nlist_fill.restype = C.c_int
     lib.azb_nlist_fill.argtypes = [C.c_int, C.POINTER(NlistArgs), C.c_void_p]
+    lib.azb_nlist_build_static.restype = C.c_int
+    lib.azb_nlist_build_static.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(C.c_size_t), C.c_void_p]
     lib.azb_nlist_plan_result.restype = C.c_int
     lib.azb_nlist_plan_result.argtypes = [C.c_int, C.POINTER(NlistArgs), C.POINTER(NlistPlanStatus), C.c_void_p]
     lib.azb_gather_scalar4.restype = C.c_int
@@ -411,5 +416,6 @@ def check(code, what):
     """Turn a C-ABI return code into an exception (the ABI itself never throws)."""
     if code == 0:
         return
-    names = {ERR_BAD_POTENTIAL: "unknown potential id", ERR_BAD_SCALAR: "scalar_bits must be 32 or 64", ERR_BAD_ARGUMENT: "bad argument"}
+    names = {ERR_BAD_POTENTIAL: "unknown potential id", ERR_BAD_SCALAR: "scalar_bits must be 32 or 64", ERR_BAD_ARGUMENT: "bad argument",
+             ERR_STATIC_SCRATCH_TOO_SMALL: "system too large for the library's built-in scratch array / output capacity"}
     raise RuntimeError(f"{what} failed: {names.get(code, 'cudaError_t ' + str(code))}")

@@ -20,6 +20,8 @@
 #include <thrust/iterator/transform_iterator.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "azb200.h"
 #include "azb_launch.cuh"
 #include "azb_math.cuh"
@@ -974,6 +976,10 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     launch_nlist_kernel<S, MODE_FILL>(d, image_shifts_ok(g), mean_range_population(a, g, ncell), stream);
     return (int)cudaGetLastError();
     }
+// scratch of azb_nlist_build_static: held by every GPU that loads the library, until exit
+static __device__ __align__(256) unsigned char g_static_workspace[AZB_STATIC_WORKSPACE_BYTES];
+static void* g_static_ptr[AZB_MAX_DEVICES]; // device address of the array, per device (host code must not use the symbol itself)
+static std::mutex g_static_mutex;
     } // namespace azb
 
 extern "C"
@@ -1045,4 +1051,58 @@ extern "C"
         return AZB_ERR_BAD_SCALAR;
         }
 
+    // ---- azb_nlist_build_static: the whole list build with NO allocation anywhere (include/azb200.h). The workspace the count /
+    // fill kernels use is the file-scope array below instead of caller memory. No counterpart in the reference: added
+    // for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses
+    // that forbid it). In host code `g_static_workspace` is only a stand-in for the device symbol: its device address is looked
+    // up once per device (cudaGetSymbolAddress, with that device current) and that pointer is what the kernels get.
+    int azb_nlist_build_static(int scalar_bits, const azb_nlist_args* a, size_t* h_total, void* stream)
+        {
+        if (!a || !h_total)
+            return AZB_ERR_BAD_ARGUMENT;
+        *h_total = 0;
+        if (scalar_bits != 32 && scalar_bits != 64)
+            return AZB_ERR_BAD_SCALAR;
+        if ((a->N && (!a->d_pos || !a->d_n_neigh || !a->d_head_list || !a->d_r_listsq || !a->d_nlist)) || a->N > a->n_max)
+            return AZB_ERR_BAD_ARGUMENT;
+        azb_nlist_args b = *a;
+        b.row_stride_hint = 0; // the two-walk build: its scratch is O(n_max), independent of the row lengths
+        b.n_views = 0;
+        size_t need = 0;
+        int rc = azb_nlist_workspace_size(&b, &need);
+        if (rc)
+            return rc;
+        if (need > AZB_STATIC_WORKSPACE_BYTES)
+            return AZB_ERR_STATIC_SCRATCH_TOO_SMALL; // n_max (or the cell grid) is beyond what the built-in scratch array holds
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess)
+            return (int)e;
+        if (dev < 0 || dev >= AZB_MAX_DEVICES)
+            return AZB_ERR_BAD_ARGUMENT;
+        void* ws = nullptr;
+            {
+            std::lock_guard<std::mutex> lock(azb::g_static_mutex);
+            if (!azb::g_static_ptr[dev])
+                {
+                void* p = nullptr;
+                e = cudaGetSymbolAddress(&p, azb::g_static_workspace); // device `dev` is current: its copy of the array
+                if (e != cudaSuccess)
+                    return (int)e;
+                azb::g_static_ptr[dev] = p;
+                }
+            ws = azb::g_static_ptr[dev];
+            }
+        b.d_workspace = ws;
+        b.workspace_bytes = AZB_STATIC_WORKSPACE_BYTES;
+        // (azb_nlist_count clears the words of the workspace that must start at zero; everything else is overwritten before use)
+        size_t total = 0;
+        rc = azb_nlist_count(scalar_bits, &b, &total, stream);
+        if (rc)
+            return rc;
+        *h_total = total;
+        if (total > a->capacity)
+            return AZB_ERR_STATIC_SCRATCH_TOO_SMALL; // d_nlist cannot hold the list: *h_total says what it takes
+        return azb_nlist_fill(scalar_bits, &b, stream);
+        }
     }

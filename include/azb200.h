@@ -323,6 +323,20 @@ typedef struct azb_nlist_plan_status
 AZB_API int azb_nlist_workspace_size(const azb_nlist_args* args, size_t* bytes);
 AZB_API int azb_nlist_count(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 AZB_API int azb_nlist_fill(int scalar_bits, const azb_nlist_args* args, void* stream);
+/* The same list build (count + scan + fill, two walks) that allocates NOTHING: no cudaMalloc / cudaFree, no allocating library
+ * routine, and no caller workspace — d_workspace / workspace_bytes / row_stride_hint / views of `args` are ignored; the scratch is a
+ * file-scope `static __device__` array of AZB_STATIC_WORKSPACE_BYTES inside the library (16 MiB, held by every GPU that loads
+ * the library until exit; about 330 000 particles incl. ghosts in float, 250 000 in double). The caller passes inputs and
+ * outputs as for azb_nlist_fill, with d_nlist[capacity] allocated up front. Returns AZB_ERR_STATIC_SCRATCH_TOO_SMALL when the
+ * system needs more scratch than the array holds, or when the list needs more than `capacity` entries (*h_total then says how many;
+ * n_neigh / head_list are valid, d_nlist is untouched). Every call on a device shares the one array, which keeps the last call's
+ * contents (the words that must start at zero are cleared by each call): calls that overlap on the GPU — two streams, two host
+ * threads — race; serialise them. Synchronises `stream` like azb_nlist_count.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid allocation). */
+#define AZB_STATIC_WORKSPACE_BYTES (16u * 1024u * 1024u)
+#define AZB_ERR_STATIC_SCRATCH_TOO_SMALL 10005
+AZB_API int azb_nlist_build_static(int scalar_bits, const azb_nlist_args* args, size_t* h_total, void* stream);
 /* after azb_nlist_fill (synchronises the stream): outcome of the tile-plan views requested in args */
 AZB_API int azb_nlist_plan_result(int scalar_bits, const azb_nlist_args* args, azb_nlist_plan_status* status, void* stream);
 
