@@ -1,0 +1,234 @@
+// azb_packed_pair.cuh — tile kernel with packed FP32 arithmetic (sm_100 FFMA2 / FMUL2 / FADD2) for isotropic pair potentials
+// other than PerturbedLennardJones (which has its own, azb_plj_packed.cuh — same walk, kept separate so that its measured
+// behaviour does not move). Written for ExpandedYukawa, the dominant kernel of C5 (8 M particles, 57 list entries per
+// particle, 58 % of them inside r_cut = 2.0): the generic tile kernel spends 48 thread-instructions per list entry at 82 %
+// issue-active and 23 of 32 lanes (the in-range branch), i.e. it is issue-bound. Here every lane evaluates TWO neighbours at a
+// time in the halves of 64-bit register pairs, and nothing branches on the cutoff: an entry that does not count (beyond the
+// cutoff, row padding) is evaluated at r = r_cut and multiplied by a 0 / 1 mask.
+// Scope: float, one particle type, orthorhombic box, modes none / shift; everything else takes the generic kernel.
+//
+// A policy `PK` supplies the per-pair math on pairs of entries:
+//   typedef Pot;                          the potential (Params / Coeff / make / active)
+//   struct K;  static K consts(coeff)     packed constants
+//   static void eval2(K, rsq2, rinv2, f2&, u2&)   force / r and pair energy (unshifted) of two entries; rsq2 is inside the cutoff
+#pragma once
+#include "azb_pair_kernel.cuh"
+#include "azb_pair_potentials.cuh"
+
+namespace azb
+    {
+__device__ __forceinline__ float2 pk2(float a, float b)
+    {
+    return make_float2(a, b);
+    }
+
+// ExpandedYukawa — /root/reference/src/PairEvaluatorExpandedYukawa.h:92-115:
+//   u = eps exp(-kappa (r - delta)) / (r - delta),  f / r = u (kappa + 1 / (r - delta)) / r
+struct PackedExpandedYukawa
+    {
+    typedef ExpandedYukawa Pot;
+    struct K
+        {
+        float2 mdelta, mkappa, kappa, eps;
+        };
+    __device__ __forceinline__ static K consts(const ExpandedYukawa::Coeff<float>& c)
+        {
+        K k;
+        k.mdelta = pk2(-c.delta, -c.delta);
+        k.mkappa = pk2(-c.kappa, -c.kappa);
+        k.kappa = pk2(c.kappa, c.kappa);
+        k.eps = pk2(c.epsilon, c.epsilon);
+        return k;
+        }
+    __device__ __forceinline__ static void eval2(const K& k, const float2 rsq, float2& f, float2& u)
+        {
+        const float2 rinv = pk2(rsqrt_(rsq.x), rsqrt_(rsq.y));
+        const float2 r = __fmul2_rn(rsq, rinv);
+        const float2 rd = __fadd2_rn(r, k.mdelta);
+        const float2 rdinv = pk2(rcp(rd.x), rcp(rd.y));
+        const float2 arg = __fmul2_rn(rd, k.mkappa);
+        const float2 ex = pk2(exp_(arg.x), exp_(arg.y));
+        u = __fmul2_rn(__fmul2_rn(k.eps, ex), rdinv);
+        f = __fmul2_rn(__fmul2_rn(u, __fadd2_rn(k.kappa, rdinv)), rinv);
+        }
+    };
+
+template<class PK, int SHIFT, bool VIRIAL, int TPP>
+__global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgsDev<float> a, const TilePlanDev plan,
+                                                                 const typename PK::Pot::template Params<float>* __restrict__ params,
+                                                                 const float wrap_sq)
+    {
+    typedef typename PK::Pot Pot;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    float4* s_pos = reinterpret_cast<float4*>(smem_raw);
+
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
+    const unsigned int U = __ldg(plan.uniq_count + tile);
+    const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    // the group's first particle: its row header and first slot packet do not depend on the staged tile, so their two memory
+    // round trips are started before the staging gather and hide behind it
+    constexpr unsigned int M = 4 * TPP;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    unsigned int nn_next = 0;
+    const uint2* row_next = nullptr;
+    float4 pi_next = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint2 pkt_next = make_uint2(0u, 0u);
+    auto load_header = [&](const unsigned int p)
+    {
+        const unsigned int idx = tile * plan.tile_size + p;
+        nn_next = 0;
+        if (p < plan.tile_size && idx < a.N)
+            {
+            nn_next = __ldg(a.n_neigh + idx);
+            row_next = reinterpret_cast<const uint2*>(plan.slots + slot_row_begin(plan, a.head_list, idx, TPP)) + lane;
+            pi_next = ld4(a.pos + idx);
+            if (nn_next)
+                pkt_next = __ldg(row_next);
+            }
+    };
+    load_header(gid);
+    warm_tile_rows(a, plan, tile, TPP);
+    stage_rows(s_pos, a.pos, uq, U);
+    // one particle type: every thread derives the coefficients itself (same expressions as the generic kernel's table)
+    const float rc = __ldg(a.rcutsq);
+    const typename Pot::template Coeff<float> c = Pot::make(params[0], rc, SHIFT == 1);
+    const float rc0 = Pot::active(c) ? rc : -1.0f; // an inactive pair (vanishing prefactor) never passes the cutoff test
+    const float r_safe = rc > 0.0f ? rc : 1.0f;    // where masked-out entries are evaluated: any finite, harmless distance
+    const typename PK::K k = PK::consts(c);
+    const float e_shift = SHIFT == 1 ? c.e_shift : 0.0f;
+    __syncthreads();
+    const unsigned int pos_base = smem_addr(s_pos);
+    const float2 kminus1 = pk2(-1.0f, -1.0f);
+
+    for (unsigned int p = gid; p < plan.tile_size; p += groups)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        const bool active = idx < a.N;
+        float2 fx = pk2(0, 0), fy = fx, fz = fx, pe = fx, vxx = fx, vxy = fx, vxz = fx, vyy = fx, vyz = fx, vzz = fx;
+        if (active)
+            {
+            const unsigned int nn = nn_next;
+            const uint2* row = row_next;
+            const float4 pi = pi_next;
+            const float2 pix = pk2(pi.x, pi.x), piy = pk2(pi.y, pi.y), piz = pk2(pi.z, pi.z);
+
+            auto visit2 = [&](const unsigned int sA, const unsigned int sB, const bool vA, const bool vB)
+            {
+                const float4 pA = lds4(pos_base, sA, float()), pB = lds4(pos_base, sB, float());
+                float2 dx = __ffma2_rn(pk2(pA.x, pB.x), kminus1, pix);
+                float2 dy = __ffma2_rn(pk2(pA.y, pB.y), kminus1, piy);
+                float2 dz = __ffma2_rn(pk2(pA.z, pB.z), kminus1, piz);
+                float2 rsq = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+                if (fmaxf(rsq.x, rsq.y) > wrap_sq) // a pair straddling the periodic box: wrap (rare, real call)
+                    {
+                    const Sep<float> wA = wrapped_separation(a.box.Lx, a.box.Ly, a.box.Lz, a.box.Lxinv, a.box.Lyinv, a.box.Lzinv, a.box.flags,
+                                                             dx.x, dy.x, dz.x);
+                    const Sep<float> wB = wrapped_separation(a.box.Lx, a.box.Ly, a.box.Lz, a.box.Lxinv, a.box.Lyinv, a.box.Lzinv, a.box.flags,
+                                                             dx.y, dy.y, dz.y);
+                    dx = pk2(wA.dx, wB.dx);
+                    dy = pk2(wA.dy, wB.dy);
+                    dz = pk2(wA.dz, wB.dz);
+                    rsq = pk2(wA.rsq, wB.rsq);
+                    }
+                // entries that do not count (beyond the cutoff, padding) are evaluated at r_cut and masked to zero
+                const bool inA = vA & (rsq.x < rc0), inB = vB & (rsq.y < rc0);
+                const float2 rq = pk2(inA ? rsq.x : r_safe, inB ? rsq.y : r_safe);
+                const float2 m = pk2(inA ? 1.0f : 0.0f, inB ? 1.0f : 0.0f);
+                float2 f, u;
+                PK::eval2(k, rq, f, u);
+                f = __fmul2_rn(f, m);
+                if (SHIFT == 1)
+                    u = __fadd2_rn(u, pk2(-e_shift, -e_shift));
+                pe = __ffma2_rn(u, m, pe);
+                fx = __ffma2_rn(dx, f, fx);
+                fy = __ffma2_rn(dy, f, fy);
+                fz = __ffma2_rn(dz, f, fz);
+                if (VIRIAL)
+                    {
+                    const float2 hx = __fmul2_rn(f, dx), hy = __fmul2_rn(f, dy), hz = __fmul2_rn(f, dz);
+                    vxx = __ffma2_rn(hx, dx, vxx);
+                    vxy = __ffma2_rn(hx, dy, vxy);
+                    vxz = __ffma2_rn(hx, dz, vxz);
+                    vyy = __ffma2_rn(hy, dy, vyy);
+                    vyz = __ffma2_rn(hy, dz, vyz);
+                    vzz = __ffma2_rn(hz, dz, vzz);
+                    }
+            };
+
+            const unsigned int full = nn / M;
+            const unsigned int nblk = (nn + M - 1u) / M;
+            uint2 next = pkt_next;
+            load_header(p + groups); // the group's next particle, if the tile has more particles than the CTA has groups
+            for (unsigned int b = 0; b < full; ++b)
+                {
+                const uint2 s4 = next;
+                if (b + 1 < nblk)
+                    next = __ldg(row + (b + 1) * TPP);
+                visit2(s4.x & 0xffffu, s4.x >> 16, true, true);
+                visit2(s4.y & 0xffffu, s4.y >> 16, true, true);
+                }
+            if (full < nblk) // the ragged last block: padding slots are 0 (a valid address) and masked out
+                {
+                const unsigned int e0 = full * M + lane;
+                visit2(next.x & 0xffffu, next.x >> 16, e0 < nn, e0 + TPP < nn);
+                visit2(next.y & 0xffffu, next.y >> 16, e0 + 2 * TPP < nn, e0 + 3 * TPP < nn);
+                }
+            }
+        PairAccum<float, VIRIAL> acc;
+        acc.fx = fx.x + fx.y;
+        acc.fy = fy.x + fy.y;
+        acc.fz = fz.x + fz.y;
+        acc.pe = pe.x + pe.y;
+        if (VIRIAL)
+            {
+            acc.vxx = vxx.x + vxx.y;
+            acc.vxy = vxy.x + vxy.y;
+            acc.vxz = vxz.x + vxz.y;
+            acc.vyy = vyy.x + vyy.y;
+            acc.vyz = vyz.x + vyz.y;
+            acc.vzz = vzz.x + vzz.y;
+            }
+        acc.template reduce<TPP>();
+        if (active && lane == 0)
+            acc.store(a, idx);
+        }
+    }
+
+// SpecialTileKernel hook (azb_pair_launch.cuh) for a packed policy: modes none and shift, float, one type, lazy-wrap boxes
+template<class PK, int SHIFT, bool VIRIAL> struct PackedPairLaunch
+    {
+    static bool try_launch(const PairArgsDev<float>& d, const TilePlanDev& plan, const void* d_params, float wrap_sq, bool lazy, bool single,
+                           unsigned int tpp, unsigned int grid, unsigned int block, cudaStream_t stream)
+        {
+        static const bool disabled = getenv("AZB_NO_PACKED") != nullptr; // A/B switch against the generic tile kernel
+        if (disabled || !lazy || !single || block > 128u)
+            return false;
+        typedef typename PK::Pot::template Params<float> param_t;
+        const size_t smem = (size_t)plan.smem_uniq * sizeof(float4);
+        if (smem > AZB_MAX_SMEM)
+            return false;
+#define AZB_PACKED_PAIR(TPP)                                                                                                   \
+    do                                                                                                                         \
+        {                                                                                                                      \
+        if (ensure_smem<packed_pair_tile_kernel<PK, SHIFT, VIRIAL, TPP>>(smem) != 0)                                           \
+            return false;                                                                                                      \
+        packed_pair_tile_kernel<PK, SHIFT, VIRIAL, TPP><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq); \
+        } while (0)
+        switch (tpp)
+            {
+        case 2:
+            AZB_PACKED_PAIR(2);
+            break;
+        case 4:
+            AZB_PACKED_PAIR(4);
+            break;
+        default:
+            return false;
+            }
+#undef AZB_PACKED_PAIR
+        return true;
+        }
+    };
+    } // namespace azb

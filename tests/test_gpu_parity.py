@@ -214,6 +214,21 @@ def test_pair_threads_per_particle_variants(tiles, tpp):
         _check(f"pair/plj/tiles{tiles}/tpp{tpp}/T{ntypes}", f, hs, 32)
 
 
+@pytest.mark.parametrize("periodic", [None, (False, True, True)], ids=["ppp", "npp"])
+@pytest.mark.parametrize("mode", ["none", "shift"])
+@pytest.mark.parametrize("tpp", [0, 2, 4])
+def test_expanded_yukawa_packed_kernel(tpp, mode, periodic):
+    """One particle type, float, tile-staged: the packed-FP32 ExpandedYukawa kernel (csrc/azb_packed_pair.cuh: two neighbours per
+    lane, out-of-range entries masked instead of branched around). Same tolerances as the generic kernel; the generic kernel
+    stays reachable (AZB_NO_PACKED) and is what two-type systems and doubles run."""
+    par_by = {(0, 0): dict(epsilon=1.5, kappa=1.2, delta=0.3)}
+    f, hs = GC.run_pair("ExpandedYukawa", par_by, {(0, 0): 2.0}, 32, n=6000, ntypes=1, mode=mode, tpp=tpp, periodic=periodic, seed=77)
+    _check(f"pair/packed/ExpandedYukawa/{mode}/tpp{tpp}/{'ppp' if periodic is None else 'npp'}", f, hs, 32)
+    # epsilon = 0 switches the pair off (the reference's evaluator returns false): exact zeros
+    f0, hs0 = GC.run_pair("ExpandedYukawa", {(0, 0): dict(epsilon=0.0, kappa=1.2, delta=0.3)}, {(0, 0): 2.0}, 32, n=1500, ntypes=1, mode=mode, tpp=tpp)
+    assert not np.any(f0.forces) and not np.any(f0.energies) and not np.any(hs0.force)
+
+
 @pytest.mark.parametrize("periodic", [(False, True, True), (True, False, False), (False, False, False)], ids=lambda p: "".join("p" if x else "n" for x in p))
 @pytest.mark.parametrize("tiles", [False, True], ids=["direct", "tiles"])
 def test_partly_periodic_boxes(tiles, periodic):
