@@ -130,7 +130,9 @@ __global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgs
                     dx = pk2(wA.dx, wB.dx);
                     dy = pk2(wA.dy, wB.dy);
                     dz = pk2(wA.dz, wB.dz);
-                    rsq = pk2(wA.rsq, wB.rsq);
+                    // same operation sequence as the unwrapped path: an entry's r^2 must not depend on whether its partner in
+                    // the register pair (another entry, or row padding — which differs between plans) needed the wrap
+                    rsq = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
                     }
                 // entries that do not count (beyond the cutoff, padding) are evaluated at r_cut and masked to zero
                 const bool inA = vA & (rsq.x < rc0), inB = vB & (rsq.y < rc0);

@@ -96,7 +96,9 @@ __global__ void __launch_bounds__(256, 4) plj_packed_tile_kernel(const PairArgsD
                     dx = f2(wA.dx, wB.dx);
                     dy = f2(wA.dy, wB.dy);
                     dz = f2(wA.dz, wB.dz);
-                    rsq = f2(wA.rsq, wB.rsq);
+                    // same operation sequence as the unwrapped path: an entry's r^2 must not depend on whether its partner in
+                    // the register pair (another entry, or row padding — which differs between plans) needed the wrap
+                    rsq = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
                     }
                 // entries that do not count (beyond the cutoff, padding) get a huge r^2: r^-6 flushes to zero
                 const bool inA = vA & (rsq.x < rc0), inB = vB & (rsq.y < rc0);

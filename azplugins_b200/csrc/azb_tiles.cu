@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "azb200.h"
 #include "azb_launch.cuh"
 #include "azb_math.cuh"
@@ -339,6 +341,373 @@ __global__ void __launch_bounds__(256) tiles_build_kernel(const Prune prune, con
             atomicMax(status + 2, (unsigned int)(shead + nnp - (slot_stride ? (size_t)first * slot_stride : AZB_SLOT_HEAD(head_list[first], first, W))));
         }
     }
+
+// ---- the default builder (group_width == 0): same four steps, organised for memory-level parallelism -------------------------
+// tiles_build_kernel above walks a tile row by row, one warp per row: n_neigh -> head_list -> row entries (-> pos[j] when
+// pruning) is a chain of dependent global loads per row, twice per build, and a warp has one such chain in flight — measured
+// 6.9 ms for the 4 M LJ list (545 M entries), ~15x what streaming the list costs. Here the row headers of the tile go to
+// shared memory first (one coalesced read), an exclusive scan turns the tile's rows into ONE flat entry range [0, E), and
+// every warp streams a contiguous chunk of it with four independent 32-entry loads in flight (eight when pruning: the
+// pos[j] gathers of four blocks are issued together). A pruning build keeps its per-entry decision in a shared bitmask
+// (E <= 65536 entries per tile), so the slot pass neither gathers pos[j] again nor recomputes a distance; the rank of a
+// kept entry in its slot row is a popcount over the row's bit range. Output is identical to tiles_build_kernel's.
+constexpr unsigned int KEEP_WORDS = 2048u;
+
+template<class P> struct PruneTraits
+    {
+    static constexpr bool on = false;
+    typedef float4 V4;
+    };
+template<class S> struct PruneTraits<PruneDev<S>>
+    {
+    static constexpr bool on = true;
+    typedef typename vec4<S>::type V4;
+    };
+__device__ __forceinline__ bool kept_staged(const NoPrune&, const float4&, const float4&)
+    {
+    return true;
+    }
+template<class S>
+__device__ __forceinline__ bool kept_staged(const PruneDev<S>& p, const typename vec4<S>::type& pi, const typename vec4<S>::type& pj)
+    {
+    S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+    min_image(p.box, dx, dy, dz);
+    const S lim = p.keep_rsq[type_of(pi.w) * p.ntypes + type_of(pj.w)];
+    return dx * dx + dy * dy + dz * dz <= lim * S(1.00001); // same expression as keep_entry()
+    }
+template<class S> __device__ __forceinline__ typename vec4<S>::type load_pos(const PruneDev<S>& p, unsigned int j)
+    {
+    return ld4(p.pos + j);
+    }
+__device__ __forceinline__ float4 load_pos(const NoPrune&, unsigned int)
+    {
+    return make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+// number of set bits in [b0, b1) of a bitmask
+__device__ __forceinline__ unsigned int count_bits(const unsigned int* m, unsigned int b0, unsigned int b1)
+    {
+    if (b1 <= b0)
+        return 0u;
+    const unsigned int w0 = b0 >> 5, w1 = (b1 - 1u) >> 5;
+    const unsigned int lo = 0xffffffffu << (b0 & 31u), hi = 0xffffffffu >> (31u - ((b1 - 1u) & 31u));
+    if (w0 == w1)
+        return __popc(m[w0] & lo & hi);
+    unsigned int c = __popc(m[w0] & lo);
+    for (unsigned int w = w0 + 1u; w < w1; ++w)
+        c += __popc(m[w]);
+    return c + __popc(m[w1] & hi);
+    }
+
+// dynamic shared memory: own[ts] V4 (pruning) | head[ts] u64 | keys[hcap] u32 | list[ucap] u32 | off[ts + 1] u32 |
+//                        keep[KEEP_WORDS] u32 (pruning) | vals[hcap] u16
+template<class Prune>
+__global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune, const bool full_set, const unsigned int* __restrict__ tile_list,
+                                                               const unsigned int slot_stride, unsigned int* __restrict__ row_count,
+                                                               const unsigned int* __restrict__ n_neigh,
+                                                               const unsigned int* __restrict__ nlist,
+                                                               const size_t* __restrict__ head_list,
+                                                               const unsigned int N,
+                                                               const unsigned int tile_size,
+                                                               const unsigned int ucap,
+                                                               const unsigned int hcap_log2,
+                                                               const unsigned int wlog,
+                                                               unsigned int* __restrict__ uniq_count,
+                                                               unsigned int* __restrict__ uniq,
+                                                               uint16_t* __restrict__ slots,
+                                                               unsigned int* __restrict__ status)
+    {
+    typedef PruneTraits<Prune> PT;
+    typedef typename PT::V4 V4;
+    constexpr bool PRUNE = PT::on;
+    constexpr int UN = 4;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int hcap = 1u << hcap_log2;
+    const unsigned int hmask = hcap - 1u;
+    const unsigned int hshift = 32u - hcap_log2;
+    V4* s_own = reinterpret_cast<V4*>(smem_raw);
+    unsigned long long* s_head = reinterpret_cast<unsigned long long*>(s_own + (PRUNE ? tile_size : 0u));
+    unsigned int* keys = reinterpret_cast<unsigned int*>(s_head + tile_size);
+    unsigned int* list = keys + hcap;
+    unsigned int* s_off = list + ucap;
+    unsigned int* s_keep = s_off + tile_size + 1u;
+    uint16_t* vals = reinterpret_cast<uint16_t*>(s_keep + (PRUNE ? KEEP_WORDS : 0u));
+    __shared__ unsigned int s_count, s_fill, s_wtot[8];
+
+    const unsigned int tile = tile_list ? tile_list[blockIdx.x] : blockIdx.x;
+    const unsigned int first = tile * tile_size;
+    const unsigned int last = min(first + tile_size, N);
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
+    const unsigned int W = 1u << wlog, M = 4u << wlog;
+    const unsigned int A = W < 2u ? 8u : M; // AZB_SLOT_ROW_ALIGN(W)
+    auto slot_head = [&](const unsigned int p) -> size_t
+    {
+        const unsigned int i = first + p;
+        return slot_stride ? (size_t)i * slot_stride : (((size_t)s_head[p] + (size_t)A * i) & ~((size_t)A - 1u));
+    };
+    auto slot_at = [&](const size_t shead, const unsigned int o) -> size_t
+    {
+        const unsigned int r = o & (M - 1u); // entry o = b 4W + u W + l sits at b 4W + 4 l + u
+        return shead + (o - r) + 4u * (r & (W - 1u)) + (r >> wlog);
+    };
+
+    // 0. row headers (and own positions) -> shared; exclusive scan of the row lengths
+    for (unsigned int h = threadIdx.x; h < hcap; h += blockDim.x)
+        keys[h] = EMPTY_KEY;
+    if (threadIdx.x == 0)
+        {
+        s_count = 0;
+        s_fill = 0;
+        }
+    const unsigned int p_own = threadIdx.x; // blockDim.x = 256 >= tile_size
+    unsigned int nn_own = 0;
+    if (p_own < tile_size && first + p_own < last)
+        {
+        nn_own = n_neigh[first + p_own];
+        s_head[p_own] = head_list[first + p_own];
+        if (PRUNE)
+            s_own[p_own] = load_pos(prune, first + p_own);
+        }
+    unsigned int incl = nn_own;
+#pragma unroll
+    for (unsigned int d = 1; d < 32; d <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d)
+            incl += t;
+        }
+    if (lane == 31u)
+        s_wtot[warp] = incl;
+    __syncthreads();
+    unsigned int wbase = 0, total = 0;
+    for (unsigned int w = 0; w < nwarps; ++w)
+        {
+        const unsigned int t = s_wtot[w];
+        wbase += w < warp ? t : 0u;
+        total += t;
+        }
+    if (p_own < tile_size)
+        s_off[p_own] = wbase + incl - nn_own;
+    if (threadIdx.x == 0)
+        s_off[tile_size] = total;
+    __syncthreads();
+    const unsigned int E = total;
+    if (PRUNE && E > KEEP_WORDS * 32u) // the keep mask cannot hold this tile: reported like an overflowing set (the host halves the tile)
+        {
+        if (threadIdx.x == 0)
+            {
+            uniq_count[tile] = EMPTY_KEY;
+            atomicMax(status + 0, ucap + 1u);
+            atomicExch(status + 1, 1u);
+            }
+        return;
+        }
+
+    // my warp's chunk of the flat entry range, and the row my first entry falls into
+    const unsigned int chunk = ((E + nwarps - 1u) / nwarps + 31u) & ~31u;
+    const unsigned int e0 = min(E, warp * chunk), e1 = min(E, e0 + chunk);
+    unsigned int r_first = 0;
+    if (e0 < e1)
+        {
+        const unsigned int e = min(e0 + lane, e1 - 1u);
+        unsigned int lo = 0, hi = tile_size; // s_off[lo] <= e < s_off[hi]
+        while (hi - lo > 1u)
+            {
+            const unsigned int mid = (lo + hi) >> 1;
+            if (s_off[mid] <= e)
+                lo = mid;
+            else
+                hi = mid;
+            }
+        r_first = lo;
+        }
+
+    // 1. hash-set insert
+    unsigned int r = r_first;
+    for (unsigned int base = e0; base < e1; base += 32u * UN)
+        {
+        unsigned int j[UN], rr[UN];
+        bool valid[UN], keep[UN];
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            const unsigned int e = base + 32u * u + lane;
+            valid[u] = e < e1;
+            j[u] = 0;
+            if (valid[u])
+                {
+                while (e >= s_off[r + 1u])
+                    ++r;
+                j[u] = nlist[s_head[r] + (e - s_off[r])];
+                }
+            rr[u] = r;
+            }
+        if (PRUNE)
+            {
+            V4 pj[UN];
+#pragma unroll
+            for (int u = 0; u < UN; ++u)
+                if (valid[u])
+                    pj[u] = load_pos(prune, j[u]);
+#pragma unroll
+            for (int u = 0; u < UN; ++u)
+                {
+                keep[u] = valid[u] && kept_staged(prune, s_own[rr[u]], pj[u]);
+                const unsigned int m = __ballot_sync(0xffffffffu, keep[u]);
+                if (lane == 0 && base + 32u * u < e1)
+                    s_keep[(base + 32u * u) >> 5] = m;
+                }
+            }
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            if (!(PRUNE && !full_set ? keep[u] : valid[u]))
+                continue;
+            unsigned int h = tile_hash(j[u], hshift);
+            for (;;)
+                {
+                // most entries are repeats (every neighbour is shared by 6-12 rows of the tile): a plain read finds them
+                // without an atomic; only an empty cell is claimed with a CAS
+                unsigned int old = *(volatile unsigned int*)&keys[h];
+                if (old == EMPTY_KEY)
+                    {
+                    old = atomicCAS(&keys[h], EMPTY_KEY, j[u]);
+                    if (old == EMPTY_KEY)
+                        {
+                        atomicAdd(&s_count, 1u);
+                        break;
+                        }
+                    }
+                if (old == j[u])
+                    break;
+                h = (h + 1u) & hmask;
+                if (*(volatile unsigned int*)&s_count > ucap) // overflowing set: give up (the table could fill)
+                    break;
+                }
+            }
+        }
+    __syncthreads();
+    const unsigned int U = s_count;
+    if (U > ucap)
+        {
+        if (threadIdx.x == 0)
+            {
+            uniq_count[tile] = EMPTY_KEY;
+            atomicMax(status + 0, U);
+            atomicExch(status + 1, 1u);
+            }
+        return;
+        }
+
+    // 2. compact + sort ascending
+    for (unsigned int h = threadIdx.x; h < hcap; h += blockDim.x)
+        {
+        const unsigned int key = keys[h];
+        if (key != EMPTY_KEY)
+            list[atomicAdd(&s_fill, 1u)] = key;
+        }
+    unsigned int P = 1;
+    while (P < U)
+        P <<= 1;
+    __syncthreads();
+    for (unsigned int s = U + threadIdx.x; s < P; s += blockDim.x)
+        list[s] = EMPTY_KEY; // P <= ucap because ucap is a power of two
+    __syncthreads();
+    for (unsigned int size = 2; size <= P; size <<= 1)
+        for (unsigned int stride = size >> 1; stride > 0; stride >>= 1)
+            {
+            for (unsigned int t = threadIdx.x; t < (P >> 1); t += blockDim.x)
+                {
+                const unsigned int lo = 2 * t - (t & (stride - 1u));
+                const unsigned int hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const unsigned int a = list[lo], b = list[hi];
+                if ((a > b) == up)
+                    {
+                    list[lo] = b;
+                    list[hi] = a;
+                    }
+                }
+            __syncthreads();
+            }
+
+    // 3. publish the list; remember each key's rank next to its table position
+    unsigned int* out = uniq + (size_t)tile * ucap;
+    for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
+        {
+        const unsigned int key = list[s];
+        out[s] = key;
+        unsigned int h = tile_hash(key, hshift);
+        while (keys[h] != key)
+            h = (h + 1u) & hmask;
+        vals[h] = (uint16_t)s;
+        }
+    if (threadIdx.x == 0)
+        {
+        uniq_count[tile] = U;
+        atomicMax(status + 0, U);
+        }
+    __syncthreads();
+
+    // 4. list entry -> slot, in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD); a pruned row holds
+    // its kept entries in list order
+    r = r_first;
+    for (unsigned int base = e0; base < e1; base += 32u * UN)
+        {
+        unsigned int j[UN], rr[UN], ee[UN];
+        bool valid[UN];
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            const unsigned int e = base + 32u * u + lane;
+            ee[u] = e;
+            valid[u] = e < e1;
+            j[u] = 0;
+            if (valid[u])
+                {
+                while (e >= s_off[r + 1u])
+                    ++r;
+                if (PRUNE)
+                    valid[u] = (s_keep[e >> 5] >> (e & 31u)) & 1u;
+                if (valid[u])
+                    j[u] = nlist[s_head[r] + (e - s_off[r])];
+                }
+            rr[u] = r;
+            }
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            if (valid[u])
+                {
+                unsigned int h = tile_hash(j[u], hshift);
+                while (keys[h] != j[u])
+                    h = (h + 1u) & hmask;
+                const unsigned int b0 = s_off[rr[u]];
+                const unsigned int o = PRUNE ? count_bits(s_keep, b0, ee[u]) : ee[u] - b0;
+                slots[slot_at(slot_head(rr[u]), o)] = vals[h];
+                }
+        }
+    // per row: padding, kept count, layout checks
+    if (p_own < tile_size && first + p_own < last)
+        {
+        const unsigned int i = first + p_own;
+        const unsigned int b0 = s_off[p_own], b1 = s_off[p_own + 1u];
+        const unsigned int out_n = PRUNE ? count_bits(s_keep, b0, b1) : nn_own;
+        const unsigned int out_p = (out_n + M - 1u) & ~(M - 1u);
+        const size_t shead = slot_head(p_own);
+        for (unsigned int o = out_n; o < out_p; ++o)
+            slots[slot_at(shead, o)] = 0;
+        if (row_count)
+            row_count[i] = out_n;
+        // rows must be disjoint and ordered by particle for the padded layout to be collision-free
+        if (i + 1u < N)
+            {
+            const size_t next_head = (i + 1u < last) ? (size_t)s_head[p_own + 1u] : head_list[i + 1u];
+            if (next_head < (size_t)s_head[p_own] + nn_own)
+                atomicExch(status + 1, 2u);
+            }
+        if (i + 1u == last) // extent of the tile's slot rows (kernels that stage them size their buffer by it)
+            atomicMax(status + 2, (unsigned int)(shead + ((nn_own + M - 1u) & ~(M - 1u)) - slot_head(0u)));
+        }
+    }
     } // namespace azb
 
 extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,
@@ -372,11 +741,32 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
     if (n_tiles == 0)
         return 0;
     const bool prune = a->d_prune_pos != nullptr;
+    // group_width == 0 (rows keep the list's order; the default): the flat-range builder. AZB_TILES_ROWWISE=1 keeps the row-wise
+    // kernel for A/B runs; bank-rotated rows (group_width > 0, opt-in) always take it.
+    static const bool rowwise = getenv("AZB_TILES_ROWWISE") != nullptr;
+    const bool flat = G == 0u && !rowwise;
+    unsigned int wlog = 0;
+    while ((1u << wlog) < W)
+        ++wlog;
     if (prune && (!a->d_prune_rsq || !a->d_row_count || a->prune_ntypes == 0 || G != 0u || (a->prune_scalar_bits != 32 && a->prune_scalar_bits != 64)))
         return AZB_ERR_BAD_ARGUMENT;
 #define AZB_TILES_LAUNCH(PRUNE_T, PRUNE_V)                                                                                              \
     do                                                                                                                                  \
         {                                                                                                                               \
+        if (flat)                                                                                                                       \
+            {                                                                                                                           \
+            const size_t fsmem = smem + (size_t)ts * 8 + ((size_t)ts + 1) * 4                                                           \
+                                 + (azb::PruneTraits<PRUNE_T>::on ? (size_t)ts * sizeof(azb::PruneTraits<PRUNE_T>::V4) + azb::KEEP_WORDS * 4 : 0); \
+            if (fsmem > 48 * 1024)                                                                                                      \
+                {                                                                                                                       \
+                err = cudaFuncSetAttribute(azb::tiles_build_flat_kernel<PRUNE_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem); \
+                if (err != cudaSuccess)                                                                                                 \
+                    return (int)err;                                                                                                    \
+                }                                                                                                                       \
+            azb::tiles_build_flat_kernel<PRUNE_T><<<n_tiles, 256, fsmem, s>>>(PRUNE_V, a->prune_full_set != 0, a->d_tile_list, a->slot_row_stride, a->d_row_count, a->d_n_neigh, a->d_nlist, \
+                                                                            a->d_head_list, a->N, ts, ucap, hcap_log2, wlog, a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status); \
+            break;                                                                                                                      \
+            }                                                                                                                           \
         if (smem > 48 * 1024)                                                                                                           \
             {                                                                                                                           \
             err = cudaFuncSetAttribute(azb::tiles_build_kernel<PRUNE_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
