@@ -188,6 +188,7 @@ class NlistArgs(C.Structure):
         ("d_uniq_count", C.c_void_p),
         ("d_uniq", C.c_void_p),
         ("d_uniq_max", C.c_void_p),
+        ("rows_in_place", C.c_uint),
     ]
 
 

@@ -1,6 +1,7 @@
 """Host side of the GPU cell-list builder (azb_nlist_count / azb_nlist_fill in csrc/azb_nlist.cu)."""
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -78,11 +79,26 @@ def build_cell_nlist(nl, state, row_align=1):
     a.d_workspace, a.workspace_bytes = ws.data_ptr(), ws_bytes.value
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     total = C.c_size_t(0)
+    # rows in place (azb_nlist_args.rows_in_place): from the second build on, the one walk writes the rows straight into a list
+    # array of N * row_stride_hint entries (head_list[i] = i * stride: disjoint, ordered rows with gaps) — no temporary rows, no
+    # scan, no compaction. The array is kept between rebuilds. AZB_NLIST_PACKED=1 keeps the tightly packed list (A/B).
+    in_place = bool(a.row_stride_hint) and not view_keys and os.environ.get("AZB_NLIST_PACKED", "0") != "1" and getattr(nl, "rows_in_place", True)
+    nlist = None
+    if in_place:
+        want = max(state.N, 1) * a.row_stride_hint
+        nlist = getattr(nl, "_nlist_buf", None)
+        if nlist is None or nlist.numel() < want or nlist.device != dev:
+            nlist = torch.empty(want, dtype=torch.int32, device=dev)
+        a.rows_in_place = 1
+        a.d_nlist, a.capacity = nlist.data_ptr(), nlist.numel()
     _abi.check(lib.azb_nlist_count(state.scalar_bits, C.byref(a), C.byref(total), stream), "azb_nlist_count")
-    nlist = torch.zeros(max(total.value, 1), dtype=torch.int32, device=dev)
-    a.d_nlist, a.capacity = nlist.data_ptr(), max(total.value, 1)
+    if nlist is None or nlist.numel() < max(total.value, 1):
+        nlist = torch.empty(max(total.value, 1), dtype=torch.int32, device=dev)
+    a.d_nlist, a.capacity = nlist.data_ptr(), nlist.numel()
     _abi.check(lib.azb_nlist_fill(state.scalar_bits, C.byref(a), stream), "azb_nlist_fill")
+    nl._nlist_buf = nlist if in_place else None
     plans = {}
+    nl_entries = int(n_neigh.sum(dtype=torch.int64).item()) if view_keys else 0
     if view_keys:
         status = _abi.NlistPlanStatus()
         _abi.check(lib.azb_nlist_plan_result(state.scalar_bits, C.byref(a), C.byref(status), stream), "azb_nlist_plan_result")
@@ -115,13 +131,17 @@ def build_cell_nlist(nl, state, row_align=1):
                 uniq_max[bad.long()] = uniq[bad.long() * 2048 + torch.clamp(cnt - 1, min=0)]  # ascending there: the last entry
         if good:
             for v, key in enumerate(view_keys):
-                entries = int(view_rows[v].sum().item()) if view_rows[v] is not None else int(total.value)
+                entries = int(view_rows[v].sum().item()) if view_rows[v] is not None else nl_entries
                 plans[key] = TilePlanHandle(key[0], n_tiles, 2048, max_uniq, key[2], status.max_slot_span[v], uniq_count, uniq, view_slots[v], 0.0,
                                             view_rows[v], entries, uniq_max=uniq_max, slot_row_stride=view_strides[v])
     torch.cuda.current_stream(dev).synchronize()
     del keep
     nl.n_neigh, nl.head_list, nl.nlist, nl.size_nlist = n_neigh, head_list, nlist, int(total.value)
-    nl._row_max = int(n_neigh.max().item()) if state.N else 0
+    if state.N:
+        mx_sum = torch.stack((n_neigh.max().long(), n_neigh.sum(dtype=torch.int64))).cpu()
+        nl._row_max, nl.n_entries = int(mx_sum[0]), int(mx_sum[1])
+    else:
+        nl._row_max, nl.n_entries = 0, 0
     nl._tiles = plans  # plans the build emitted itself; anything else is built on demand (azb_tiles_build)
     # positions the list was built from (locals + ghosts): reference point of the displacement check (md.Integrator) and of
     # the pruning test of force-specific tile plans
@@ -183,7 +203,8 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     n_tiles = (N + tile_size - 1) // tile_size
     uniq_count = torch.zeros(n_tiles, dtype=torch.int32, device=dev)
     uniq = torch.empty(n_tiles * uniq_capacity, dtype=torch.int32, device=dev)
-    slots = torch.zeros(nl.size_nlist + max(4 * lane_width, 8) * (N + 1), dtype=torch.int16, device=dev)  # AZB_SLOTS_SIZE
+    # AZB_SLOTS_SIZE; not cleared: the builder writes every slot row including its padding, nothing reads the gaps between rows
+    slots = torch.empty(nl.size_nlist + max(4 * lane_width, 8) * (N + 1), dtype=torch.int16, device=dev)
     status = torch.zeros(4, dtype=torch.int32, device=dev)
     a = _abi.TileBuildArgs()
     a.d_n_neigh, a.d_nlist, a.d_head_list = nl.n_neigh.data_ptr(), nl.nlist.data_ptr(), nl.head_list.data_ptr()
@@ -207,6 +228,6 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     e1.synchronize()
     if overflow.value:
         return None
-    entries = int(row_count.sum().item()) if row_count is not None else nl.size_nlist
+    entries = int(row_count.sum().item()) if row_count is not None else (nl.n_entries or nl.size_nlist)
     return TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, lane_width, max_span.value, uniq_count, uniq, slots,
                           e0.elapsed_time(e1), row_count, entries)

@@ -15,6 +15,58 @@ template<class S, int SHIFT, bool VIRIAL> static int launch_aniso_variant(const 
     const size_t T2t = (size_t)a.pair.ntypes * a.pair.ntypes;
     if (a.pair.tiles)
         {
+        if (a.pair.tiles->lane_width == 1u)
+            {
+            // plain-order slot rows: the in-range-compacting walk (azb_ring_walk.cuh), 4 lanes per particle unless asked otherwise
+            const unsigned int tpp = a.pair.threads_per_particle ? a.pair.threads_per_particle : 4u;
+            TilePlanDev plan;
+            unsigned int block = 0, grid = 0;
+            const int bad = make_tile_plan(a.pair, tpp, 1u, plan, block, grid);
+            if (bad)
+                return bad;
+            if (a.pair.ntypes > 255)
+                return AZB_ERR_BAD_ARGUMENT; // the ring packs slot | type pair << 16
+            S wrap_sq;
+            const bool lazy = lazy_wrap(d.pair.box, wrap_sq);
+            const bool single = a.pair.ntypes == 1;
+#define AZB_RING_T(TPP, FB, SG)                                                                                                              \
+    do                                                                                                                                       \
+        {                                                                                                                                    \
+        const size_t smem = (size_t)plan.smem_uniq * 2 * sizeof(typename vec4<S>::type) + (size_t)(block / TPP) * ring_stride<S, TPP>()      \
+                            + T2t * (sizeof(coeff_t) + sizeof(S));                                                                           \
+        if (smem > AZB_MAX_SMEM)                                                                                                             \
+            return AZB_ERR_BAD_ARGUMENT;                                                                                                     \
+        if (const int e_ = ensure_smem<aniso_ring_tile_kernel<S, SHIFT, VIRIAL, TPP, FB, SG>>(smem)) return e_;                              \
+        aniso_ring_tile_kernel<S, SHIFT, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq);     \
+        } while (0)
+#define AZB_RING_F(TPP)                    \
+    do                                     \
+        {                                  \
+        if (lazy && single)                \
+            AZB_RING_T(TPP, true, true);   \
+        else if (lazy)                     \
+            AZB_RING_T(TPP, true, false);  \
+        else                               \
+            AZB_RING_T(TPP, false, false); \
+        } while (0)
+            switch (tpp)
+                {
+            case 2:
+                AZB_RING_F(2);
+                break;
+            case 4:
+                AZB_RING_F(4);
+                break;
+            case 8:
+                AZB_RING_F(8);
+                break;
+            default:
+                return AZB_ERR_BAD_ARGUMENT;
+                }
+#undef AZB_RING_F
+#undef AZB_RING_T
+            return (int)cudaGetLastError();
+            }
         const unsigned int tpp = a.pair.tiles->lane_width; // the slot rows are laid out for one group width
         if (!(tpp == 2 || tpp == 4 || tpp == 8 || tpp == 16) || (a.pair.threads_per_particle && a.pair.threads_per_particle != tpp))
             return AZB_ERR_BAD_ARGUMENT;

@@ -7,6 +7,7 @@
 #pragma once
 #include "azb_math.cuh"
 #include "azb_pair_kernel.cuh"
+#include "azb_ring_walk.cuh"
 
 namespace azb
     {
@@ -328,6 +329,103 @@ __global__ void __launch_bounds__(256)
             }
         acc.template reduce<TPP>();
         if (active && lane == 0)
+            acc.store(d, idx);
+        }
+    }
+
+// Tile-staged flavour with in-range compaction (azb_ring_walk.cuh): same staging as aniso_tile_kernel, but the ~150-instruction
+// evaluator runs on queued in-range pairs only, one per lane, instead of under a branch that 49 % of C4a's list entries skip.
+// Slot rows in plain order (plan lane_width 1), TPP lanes per particle.
+template<class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
+__global__ void __launch_bounds__(256)
+    aniso_ring_tile_kernel(const AnisoArgsDev<S> d, const TilePlanDev plan, const TwoPatchMorse::Params<S>* __restrict__ params, const S wrap_sq)
+    {
+    typedef TwoPatchMorse::Coeff<S> coeff_t;
+    typedef typename vec4<S>::type V4;
+    const PairArgsDev<S>& a = d.pair;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    V4* s_pos = reinterpret_cast<V4*>(smem_raw);
+    V4* s_dir = s_pos + plan.smem_uniq;
+    V4* s_queue = s_dir + plan.smem_uniq;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(reinterpret_cast<unsigned char*>(s_queue) + groups * ring_stride<S, TPP>());
+    S* s_rcutsq = reinterpret_cast<S*>(s_coeff + T2);
+
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
+    const unsigned int U = __ldg(plan.uniq_count + tile);
+    const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    warm_tile_rows(a, plan, tile, 1u);
+    constexpr int B = 64 / sizeof(V4);
+    for (unsigned int s0 = threadIdx.x; s0 < U; s0 += B * blockDim.x)
+        {
+        unsigned int g[B];
+        V4 pv[B], qv[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            g[u] = (s0 + u * blockDim.x < U) ? __ldg(uq + s0 + u * blockDim.x) : 0xffffffffu;
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                pv[u] = ld4(a.pos + g[u]);
+                qv[u] = ld4(d.orientation + g[u]);
+                }
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                const unsigned int s = s0 + u * blockDim.x;
+                s_pos[s] = pv[u];
+                V4 n = qv[u];
+                patch_director<S>(qv[u], n.x, n.y, n.z);
+                s_dir[s] = n;
+                }
+        }
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        {
+        const S rc = a.rcutsq[t];
+        s_coeff[t] = TwoPatchMorse::make(params[t], rc, SHIFT == 1);
+        s_rcutsq[t] = rc;
+        }
+    __syncthreads();
+    const unsigned int pos_base = smem_addr(s_pos), dir_base = smem_addr(s_dir);
+    const unsigned int q_addr = smem_addr(s_queue) + gid * ring_stride<S, TPP>();
+    const unsigned int rc_addr = smem_addr(s_rcutsq);
+    const coeff_t c0 = s_coeff[0]; // one particle type: the coefficient set stays in registers
+    const S rc0 = s_rcutsq[0];
+
+    for (unsigned int p = gid; p < plan.tile_size; p += groups) // warp-uniform trip count
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        const bool active = idx < a.N;
+        unsigned int nn = 0, trow = 0;
+        const uint16_t* row = plan.slots;
+        V4 pi = ring_entry<S>(S(0), S(0), S(0), 0u);
+        S nix = S(0), niy = S(0), niz = S(0);
+        if (active)
+            {
+            nn = __ldg(a.n_neigh + idx);
+            row = plan.slots + slot_row_begin(plan, a.head_list, idx, 1);
+            pi = ld4(a.pos + idx);
+            const V4 qi = ld4(d.orientation + idx);
+            patch_director<S>(qi, nix, niy, niz);
+            trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
+            }
+        AnisoAccum<S, VIRIAL> acc;
+        ring_walk_row<S, TPP, FASTBOX, SINGLE, false>(row, nn, pi, trow, a.box, wrap_sq, pos_base, rc_addr, (unsigned int)sizeof(S), rc0, q_addr,
+                                                      [&](const V4& e, const unsigned int slot, const unsigned int tp)
+                                                      {
+                                                          const V4 nj = lds4(dir_base, slot, S());
+                                                          const S rsq = e.x * e.x + e.y * e.y + e.z * e.z;
+                                                          if (SINGLE)
+                                                              tpm_pair<S, VIRIAL>(e.x, e.y, e.z, rsq, nix, niy, niz, nj.x, nj.y, nj.z, c0, acc);
+                                                          else
+                                                              tpm_pair<S, VIRIAL>(e.x, e.y, e.z, rsq, nix, niy, niz, nj.x, nj.y, nj.z, s_coeff[tp], acc);
+                                                      });
+        acc.template reduce<TPP>();
+        if (active && threadIdx.x % TPP == 0)
             acc.store(d, idx);
         }
     }

@@ -20,6 +20,7 @@
 #include <thrust/iterator/transform_iterator.h>
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "azb200.h"
@@ -289,6 +290,7 @@ template<class S> struct NlistDev
     unsigned int* tmp_rows; // MODE_SINGLE: [N * row_stride] rows of fixed capacity, compacted afterwards
     unsigned int row_stride;
     unsigned int* overflow; // MODE_SINGLE: set when a row does not fit row_stride
+    size_t* head_out;       // MODE_SINGLE with rows in place (tmp_rows = the caller's nlist): head_list[i] = i * row_stride
     // tile-plan views (MODE_SINGLE only): every view's slot rows are written straight from the walk, at a fixed stride
     unsigned int n_views, tile_size;
     const TileTable* tables;
@@ -579,6 +581,8 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
         a.n_neigh[i] = count;
         if (MODE == MODE_SINGLE && count > a.row_stride)
             atomicExch(a.overflow, 1u);
+        if (MODE == MODE_SINGLE && a.head_out)
+            a.head_out[i] = (size_t)i * a.row_stride;
         }
     if (plan && active)
         {
@@ -596,6 +600,292 @@ __global__ void __launch_bounds__(128) nlist_kernel(const NlistDev<S> a)
                 if (lane == 0 && a.view_rows[v])
                     a.view_rows[v][i] = n;
                 }
+        }
+    }
+
+// ---- the default walk: one LANE per particle, candidates broadcast ----------------------------------------------------------------
+// nlist_kernel above spends one lane per CANDIDATE: every test costs its lane a 16-byte load, an index computation and a share of
+// the ballot compaction (measured: 1030 warp instructions per particle on C5, issue-bound). Here a warp takes 32 consecutive
+// particles of the cell order — almost always cells of one (y, z) row — and every lane owns ONE particle: the candidates of the
+// row's nine neighbouring (y, z) rows, over the x cells [min cx - 1, max cx + 1] of the warp, are read by a broadcast load (one
+// instruction per candidate and warp) and tested by all 32 lanes at once, ~18 instructions per candidate and warp. A lane only
+// accepts candidates inside its own three-cell window of the range (so the accepted set and its order are exactly those of
+// nlist_kernel: rows r = 0..8, low image, main range, high image, ascending position) and collects them in a 16-entry buffer in
+// shared memory that it writes out 64 bytes at a time. Warps that straddle a row boundary process their rows one after the other.
+// Needs the image-shift form (>= 3 cells along every periodic direction); tile-plan views stay with nlist_kernel.
+constexpr unsigned int NLB_BUF = 16u; // entries buffered per lane
+
+template<class S, int MODE, bool SINGLE_TYPE, bool EXCL, bool DIRECT>
+__global__ void __launch_bounds__(128) nlist_bcast_kernel(const NlistDev<S> a)
+    {
+    typedef typename vec4<S>::type V4;
+    constexpr unsigned int FULL = 0xffffffffu;
+    extern __shared__ __align__(16) unsigned char nlb_smem[];
+    unsigned int* s_buf = reinterpret_cast<unsigned int*>(nlb_smem);                  // [blockDim.x][NLB_BUF]
+    S* s_rl = reinterpret_cast<S*>(s_buf + ((MODE == MODE_COUNT || DIRECT) ? 0u : blockDim.x * NLB_BUF)); // [ntypes^2] (multi-type)
+    if (!SINGLE_TYPE)
+        {
+        for (unsigned int t = threadIdx.x; t < a.ntypes * a.ntypes; t += blockDim.x)
+            s_rl[t] = a.r_listsq[t];
+        __syncthreads();
+        }
+    const unsigned int s_own = blockIdx.x * blockDim.x + threadIdx.x; // position in cell order
+    unsigned int i = 0xffffffffu;
+    if (s_own < a.n_max)
+        i = a.idx_sorted[s_own];
+    const bool active = i < a.N; // ghosts get no row
+    V4 pi = {};
+    unsigned int c = 0;
+    if (active)
+        {
+        pi = ld4(a.pos_sorted + s_own);
+        c = a.cell_sorted[s_own];
+        }
+    const unsigned int trow = SINGLE_TYPE ? 0u : type_of(pi.w) * a.ntypes;
+    const int nx = a.grid.nc[0], ny = a.grid.nc[1], nz = a.grid.nc[2];
+    const int cx = (int)(c % (unsigned int)nx);
+    const int cy = (int)((c / (unsigned int)nx) % (unsigned int)ny);
+    const int cz = (int)(c / ((unsigned int)nx * (unsigned int)ny));
+    const bool per_x = a.grid.periodic & 1u, per_y = (a.grid.periodic >> 1) & 1u, per_z = (a.grid.periodic >> 2) & 1u;
+    const S rl_single = SINGLE_TYPE ? a.r_listsq[0] : S(0);
+
+    // exclusions: the first four of my row in registers, the rest (rare) read from the table
+    unsigned int ex[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    size_t ex0 = 0, ex1 = 0;
+    if (EXCL && active)
+        {
+        ex0 = a.excl_head[i];
+        ex1 = a.excl_head[i + 1];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (ex0 + k < ex1)
+                ex[k] = a.excl_list[ex0 + k];
+        }
+
+    unsigned int* row = nullptr;
+    size_t row_cap = 0;
+    if (MODE == MODE_FILL && active)
+        {
+        row = a.nlist + a.head_list[i];
+        row_cap = a.capacity - a.head_list[i];
+        }
+    if (MODE == MODE_SINGLE && active)
+        {
+        row = a.tmp_rows + (size_t)i * a.row_stride;
+        row_cap = a.row_stride;
+        }
+    unsigned int* buf = s_buf + threadIdx.x * NLB_BUF;
+    unsigned int count = 0;
+    auto flush16 = [&](const unsigned int base) // buffered entries [base, base + 16) -> my row
+    {
+        if (base + NLB_BUF <= row_cap && ((reinterpret_cast<size_t>(row + base) & 15u) == 0u))
+            {
+#pragma unroll
+            for (unsigned int q = 0; q < NLB_BUF / 4u; ++q)
+                reinterpret_cast<uint4*>(row + base)[q] = reinterpret_cast<const uint4*>(buf)[q];
+            }
+        else
+            for (unsigned int k = 0; k < NLB_BUF; ++k)
+                if (base + k < row_cap)
+                    row[base + k] = buf[k];
+    };
+
+    unsigned int todo = __ballot_sync(FULL, active);
+    while (todo) // one pass per (y, z) row of cells among the warp's particles (one, except where the warp straddles a row end)
+        {
+        const int leader = __ffs(todo) - 1;
+        const int ry = __shfl_sync(FULL, cy, leader), rz = __shfl_sync(FULL, cz, leader);
+        const bool mine = active && cy == ry && cz == rz;
+        todo &= ~__ballot_sync(FULL, mine);
+        const int xmin = __reduce_min_sync(FULL, mine ? cx : 0x7fffffff);
+        const int xmax = __reduce_max_sync(FULL, mine ? cx : -1);
+#pragma unroll 1
+        for (int r = 0; r < 9; ++r)
+            {
+            int z = rz + r / 3 - 1, y = ry + r % 3 - 1;
+            S sy = S(0), sz = S(0);
+            if (per_z)
+                {
+                if (z < 0)
+                    {
+                    z += nz;
+                    sz = a.box.Lz; // the cells sit one box length above their image next to me: d = (pi - pj) + L
+                    }
+                else if (z >= nz)
+                    {
+                    z -= nz;
+                    sz = -a.box.Lz;
+                    }
+                }
+            else if (z < 0 || z >= nz)
+                continue;
+            if (per_y)
+                {
+                if (y < 0)
+                    {
+                    y += ny;
+                    sy = a.box.Ly;
+                    }
+                else if (y >= ny)
+                    {
+                    y -= ny;
+                    sy = -a.box.Ly;
+                    }
+                }
+            else if (y < 0 || y >= ny)
+                continue;
+            const unsigned int rb = (unsigned int)((z * ny + y) * nx);
+            // the warp's x range in unwrapped cell coordinates, in up to three segments: cells reached through the low face
+            // (stored at + nx, shift + Lx), the cells inside the box, cells reached through the high face (- nx, - Lx)
+            const int X0 = xmin - 1, X1 = xmax + 1;
+#pragma unroll 1
+            for (int seg = 0; seg < 3; ++seg)
+                {
+                int u0, u1, off;
+                S sx = S(0);
+                if (seg == 0)
+                    {
+                    u0 = X0, u1 = min(X1, -1), off = nx, sx = a.box.Lx;
+                    if (!per_x)
+                        continue;
+                    }
+                else if (seg == 1)
+                    u0 = max(X0, 0), u1 = min(X1, nx - 1), off = 0;
+                else
+                    {
+                    u0 = max(X0, nx), u1 = X1, off = -nx, sx = -a.box.Lx;
+                    if (!per_x)
+                        continue;
+                    }
+                if (u0 > u1)
+                    continue;
+                const unsigned int S0 = a.cell_begin[rb + u0 + off], S1 = a.cell_begin[rb + u1 + off + 1];
+                if (S0 >= S1)
+                    continue;
+                // my own window of the range: cells [cx - 1, cx + 1] of this segment
+                unsigned int w_lo = 0, w_len = 0;
+                if (mine)
+                    {
+                    const int w0 = max(cx - 1, u0), w1 = min(cx + 1, u1);
+                    if (w0 <= w1)
+                        {
+                        w_lo = a.cell_begin[rb + w0 + off];
+                        w_len = a.cell_begin[rb + w1 + off + 1] - w_lo;
+                        }
+                    }
+                if (!__any_sync(FULL, w_len != 0u))
+                    continue;
+                const S px = pi.x, py = pi.y, pz = pi.z;
+                const bool shifted = (sx != S(0)) | (sy != S(0)) | (sz != S(0)); // warp-uniform
+                // r^2 of one candidate: same operations, same order as nlist_kernel (identical lists); adding a zero shift is
+                // the identity, so the unshifted body skips it
+                auto in_list = [&](const V4& pj, const bool sh) -> bool
+                {
+                    S dx = px - pj.x, dy = py - pj.y, dz = pz - pj.z;
+                    if (sh)
+                        {
+                        dx += sx;
+                        dy += sy;
+                        dz += sz;
+                        }
+                    const S rsq = dx * dx + dy * dy + dz * dz;
+                    const S rl = SINGLE_TYPE ? rl_single : s_rl[trow + type_of(pj.w)];
+                    return rsq < rl; // (implies rl > 0)
+                };
+                for (unsigned int s0 = S0; s0 < S1; s0 += 32u)
+                    {
+                    // 32 candidates at a time: every lane tests all of them (broadcast loads) and keeps a bit per hit; its own
+                    // three-cell window and its own position are applied to the mask afterwards, not per candidate
+                    const unsigned int n = min(32u, S1 - s0);
+                    const unsigned int lo = max(w_lo, s0), hi = min(w_lo + w_len, s0 + n);
+                    unsigned int wmask = 0;
+                    if (hi > lo)
+                        wmask = (hi - lo >= 32u ? FULL : ((1u << (hi - lo)) - 1u)) << (lo - s0);
+                    if (s_own - s0 < 32u)
+                        wmask &= ~(1u << (s_own - s0));
+                    if (!__any_sync(FULL, wmask != 0u))
+                        continue;
+                    unsigned int mask = 0;
+                    if (n == 32u)
+                        {
+                        if (shifted)
+                            {
+#pragma unroll
+                            for (unsigned int u = 0; u < 32u; ++u)
+                                if (in_list(ld4(a.pos_sorted + s0 + u), true))
+                                    mask |= 1u << u;
+                            }
+                        else
+                            {
+#pragma unroll
+                            for (unsigned int u = 0; u < 32u; ++u)
+                                if (in_list(ld4(a.pos_sorted + s0 + u), false))
+                                    mask |= 1u << u;
+                            }
+                        }
+                    else
+                        {
+#pragma unroll 4
+                        for (unsigned int u = 0; u < n; ++u)
+                            if (in_list(ld4(a.pos_sorted + s0 + u), true))
+                                mask |= 1u << u;
+                        }
+                    mask &= wmask;
+                    if (MODE == MODE_COUNT && !EXCL)
+                        count += __popc(mask);
+                    else
+                        while (mask)
+                            {
+                            const unsigned int b = __ffs(mask) - 1u;
+                            mask &= mask - 1u;
+                            const unsigned int j = __ldg(a.idx_sorted + s0 + b);
+                            if (EXCL)
+                                {
+                                bool out = j == ex[0] || j == ex[1] || j == ex[2] || j == ex[3];
+                                if (ex1 - ex0 > 4)
+                                    for (size_t e = ex0 + 4; e < ex1; ++e)
+                                        out = out || a.excl_list[e] == j;
+                                if (out)
+                                    continue;
+                                }
+                            if (MODE != MODE_COUNT)
+                                {
+                                if (DIRECT)
+                                    {
+                                    // straight into the row: consecutive entries of a row fill a 32-byte sector within a few
+                                    // chunks, and L2 assembles the sectors
+                                    if (count < row_cap)
+                                        row[count] = j;
+                                    }
+                                else
+                                    {
+                                    buf[count & (NLB_BUF - 1u)] = j;
+                                    if (((count + 1u) & (NLB_BUF - 1u)) == 0u)
+                                        flush16(count + 1u - NLB_BUF);
+                                    }
+                                }
+                            ++count;
+                            }
+                    }
+                }
+            }
+        }
+    if (!active)
+        return;
+    if (MODE != MODE_COUNT && !DIRECT)
+        {
+        const unsigned int base = count & ~(NLB_BUF - 1u);
+        for (unsigned int k = 0; base + k < count; ++k)
+            if (base + k < row_cap)
+                row[base + k] = buf[k];
+        }
+    if (MODE != MODE_FILL)
+        {
+        a.n_neigh[i] = count;
+        if (MODE == MODE_SINGLE && count > a.row_stride)
+            atomicExch(a.overflow, 1u);
+        if (MODE == MODE_SINGLE && a.head_out)
+            a.head_out[i] = (size_t)i * a.row_stride;
         }
     }
 
@@ -637,6 +927,35 @@ __global__ void __launch_bounds__(256) nlist_compact_kernel(const unsigned int* 
 template<class S, int MODE> static void launch_nlist_kernel(const NlistDev<S>& d, bool img, double mean_range, cudaStream_t stream)
     {
     const bool single = d.ntypes == 1, excl = d.excl_head != nullptr;
+    // one lane per particle with broadcast candidates (nlist_bcast_kernel) whenever the image-shift form applies and no tile-plan
+    // views ride on the walk; AZB_NLIST_LANEWISE=1 keeps the lane-per-candidate walk for A/B runs
+    static const bool lanewise = getenv("AZB_NLIST_LANEWISE") != nullptr;
+    const size_t rl_bytes = single ? 0 : (size_t)d.ntypes * d.ntypes * sizeof(S);
+    if (img && !lanewise && d.n_views == 0 && rl_bytes <= 16 * 1024)
+        {
+        const unsigned int grid_b = (d.n_max + 127u) / 128u;
+        // entries go straight into the rows (AZB_NLIST_BUFFERED=1: through a 16-entry buffer per lane in shared memory, A/B)
+        static const bool buffered = getenv("AZB_NLIST_BUFFERED") != nullptr;
+        const size_t smem_b = ((MODE == MODE_COUNT || !buffered) ? 0 : 128 * NLB_BUF * sizeof(unsigned int)) + rl_bytes;
+#define AZB_NLB(T, E)                                                                      \
+    do                                                                                     \
+        {                                                                                  \
+        if (buffered)                                                                      \
+            nlist_bcast_kernel<S, MODE, T, E, false><<<grid_b, 128, smem_b, stream>>>(d);  \
+        else                                                                               \
+            nlist_bcast_kernel<S, MODE, T, E, true><<<grid_b, 128, smem_b, stream>>>(d);   \
+        } while (0)
+        if (single && excl)
+            AZB_NLB(true, true);
+        else if (single)
+            AZB_NLB(true, false);
+        else if (excl)
+            AZB_NLB(false, true);
+        else
+            AZB_NLB(false, false);
+#undef AZB_NLB
+        return;
+        }
     // lanes per particle: 16 when a candidate range (three cells) holds fewer than ~48 particles, so that the tail of a range
     // does not idle half a warp
     const bool narrow = mean_range < 48.0;
@@ -791,6 +1110,18 @@ static size_t cub_temp_bytes(unsigned int n_max, unsigned int N)
     return sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
     }
 
+// rows written straight into the caller's nlist at a fixed stride (azb_nlist_args.rows_in_place): no temporary rows, no
+// compaction, no scan. Not combined with tile-plan views.
+static bool rows_in_place(const azb_nlist_args& a)
+    {
+    return a.rows_in_place != 0 && a.row_stride_hint > 0 && a.n_views == 0;
+    }
+// entries per row of the workspace's temporary rows
+static unsigned int tmp_row_stride(const azb_nlist_args& a)
+    {
+    return rows_in_place(a) ? 0u : a.row_stride_hint;
+    }
+
 // tile-plan views ride on the single walk only
 static unsigned int plan_tiles(const azb_nlist_args& a)
     {
@@ -831,9 +1162,10 @@ template<class S> static NlistDev<S> make_dev(const azb_nlist_args& a, const Wor
     d.head_list = a.d_head_list;
     d.nlist = a.d_nlist;
     d.capacity = a.capacity;
-    d.tmp_rows = w.tmp_rows;
+    d.tmp_rows = rows_in_place(a) ? a.d_nlist : w.tmp_rows;
     d.row_stride = a.row_stride_hint;
     d.overflow = w.flags;
+    d.head_out = rows_in_place(a) ? a.d_head_list : nullptr;
     d.n_views = w.tables ? a.n_views : 0u;
     d.tile_size = a.tile_size ? a.tile_size : 128u;
     d.tables = w.tables;
@@ -874,7 +1206,7 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     if ((rc = check_views(a)))
         return rc;
     const unsigned int n_tiles = plan_tiles(a);
-    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_bytes, a.row_stride_hint, n_tiles);
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_bytes, tmp_row_stride(a), n_tiles);
     if (w.bytes > a.workspace_bytes)
         return AZB_ERR_BAD_ARGUMENT;
     typedef typename vec4<S>::type s4;
@@ -907,9 +1239,37 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     const double range = mean_range_population(a, g, ncell);
     const unsigned int align = a.row_align ? a.row_align : 1;
     const bool single_walk = a.row_stride_hint > 0;
+    const bool in_place = rows_in_place(a);
+    if (in_place && a.N)
+        {
+        if (!a.d_nlist || a.capacity < (size_t)a.N * a.row_stride_hint)
+            return AZB_ERR_BAD_ARGUMENT;
+        // one walk writes n_neigh, head_list and the rows themselves; nothing else to do unless a row outgrew the stride
+        launch_nlist_kernel<S, MODE_SINGLE>(d, img, range, stream);
+        unsigned int h_over = 0;
+        e = cudaMemcpyAsync(&h_over, w.flags, sizeof(h_over), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        if (e == cudaSuccess)
+            e = cudaGetLastError();
+        if (e != cudaSuccess)
+            return (int)e;
+        if (!h_over)
+            {
+            *h_total = (size_t)a.N * a.row_stride_hint;
+            const unsigned int done = 2u; // azb_nlist_fill has nothing left to do
+            e = cudaMemcpyAsync(w.flags + 1, &done, sizeof(done), cudaMemcpyHostToDevice, stream);
+            if (e == cudaSuccess)
+                e = cudaStreamSynchronize(stream);
+            return (int)e;
+            }
+        // overflow: n_neigh is right, the rows are not — packed head_list below, and azb_nlist_fill walks again
+        }
     if (a.N)
         {
-        if (single_walk)
+        if (in_place)
+            ;
+        else if (single_walk)
             launch_nlist_kernel<S, MODE_SINGLE>(d, img, range, stream);
         else
             launch_nlist_kernel<S, MODE_COUNT>(d, img, range, stream);
@@ -929,7 +1289,7 @@ template<class S> static int nlist_count(const azb_nlist_args& a, size_t* h_tota
     if (e == cudaSuccess && single_walk && a.N)
         {
         // rows that all fitted their fixed stride are final: azb_nlist_fill only compacts them. Otherwise it walks again.
-        const unsigned int valid = h_flags[0] ? 0u : 1u;
+        const unsigned int valid = (h_flags[0] || in_place) ? 0u : 1u;
         e = cudaMemcpyAsync(w.flags + 1, &valid, sizeof(valid), cudaMemcpyHostToDevice, stream);
         if (e == cudaSuccess)
             e = cudaStreamSynchronize(stream);
@@ -947,7 +1307,7 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
     if ((rc = check_views(a)))
         return rc;
     const unsigned int n_tiles = plan_tiles(a);
-    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N), a.row_stride_hint, n_tiles);
+    Workspace w = carve(a.d_workspace, a.n_max, a.N, ncell, sizeof(typename vec4<S>::type), cub_temp_bytes(a.n_max, a.N), tmp_row_stride(a), n_tiles);
     if (w.bytes > a.workspace_bytes || (a.N && !a.d_nlist))
         return AZB_ERR_BAD_ARGUMENT;
     if (!a.N)
@@ -961,6 +1321,8 @@ template<class S> static int nlist_fill(const azb_nlist_args& a, cudaStream_t st
         if (e != cudaSuccess)
             return (int)e;
         }
+    if (valid == 2u)
+        return 0; // rows in place: azb_nlist_count wrote the final list
     if (valid)
         {
         const unsigned int grd = (unsigned int)((((size_t)a.N + 3) / 4 * 32 + 255) / 256);
@@ -993,7 +1355,7 @@ extern "C"
         const int rc = azb::make_grid(*a, g, ncell);
         if (rc)
             return rc;
-        *bytes = azb::carve(nullptr, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), a->row_stride_hint, azb::plan_tiles(*a)).bytes;
+        *bytes = azb::carve(nullptr, a->n_max, a->N, ncell, 32, azb::cub_temp_bytes(a->n_max, a->N), azb::tmp_row_stride(*a), azb::plan_tiles(*a)).bytes;
         return 0;
         }
 
@@ -1014,7 +1376,7 @@ extern "C"
             return rc;
         // (the same carve as azb_nlist_count / azb_nlist_fill: the workspace layout depends on sizeof(Scalar4))
         const azb::Workspace w = azb::carve(a->d_workspace, a->n_max, a->N, ncell, scalar_bits == 32 ? 16 : 32, azb::cub_temp_bytes(a->n_max, a->N),
-                                            a->row_stride_hint, n_tiles);
+                                            azb::tmp_row_stride(*a), n_tiles);
         unsigned int h[16];
         cudaError_t e = cudaMemcpyAsync(h, w.plan_status, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
         if (e == cudaSuccess)
@@ -1068,6 +1430,7 @@ extern "C"
         azb_nlist_args b = *a;
         b.row_stride_hint = 0; // the two-walk build: its scratch is O(n_max), independent of the row lengths
         b.n_views = 0;
+        b.rows_in_place = 0;
         size_t need = 0;
         int rc = azb_nlist_workspace_size(&b, &need);
         if (rc)

@@ -353,6 +353,16 @@ class AnisotropicPair(Pair):
 
     def __init__(self, nlist, default_r_cut=None, mode="none"):
         super().__init__(nlist, default_r_cut, 0.0, mode)
+        # in-range compaction (csrc/azb_ring_walk.cuh): the evaluator runs on queued in-range pairs only. Needs plain-order slot
+        # rows (plan lane_width 1) and 2, 4 or 8 lanes per particle. OFF by default — measured on B200 (C4a, 2 048 000 particles,
+        # 20 list entries per particle): 0.350 ms at 4 lanes per particle, 0.304 ms at 2, against 0.288 ms for the branchy tile
+        # kernel: rows this short spend more on the walk's votes than the compaction saves. AZB_ANISO_RING=1 turns it on (A/B).
+        self.ring_walk = os.environ.get("AZB_ANISO_RING", "0") == "1"
+
+    def _slot_lane_width(self, nbar):
+        if self.ring_walk and self.threads_per_particle in (0, 2, 4, 8):
+            return 1
+        return super()._slot_lane_width(nbar)
 
     def _attach(self, state):
         super()._attach(state)

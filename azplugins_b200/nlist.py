@@ -21,7 +21,8 @@ class NeighborList:
         self.n_neigh = None
         self.head_list = None
         self.nlist = None
-        self.size_nlist = 0
+        self.size_nlist = 0  # extent of the nlist array (entries); rows may have gaps between them
+        self.n_entries = 0  # sum of the row lengths
         self._state = None
         self._tiles = {}
 
@@ -48,7 +49,7 @@ class NeighborList:
             on = os.environ.get("AZB_FUSED_PLANS", "0") == "1"
         if not self.size_nlist or os.environ.get("AZB_NO_FUSED_PLANS", "0") == "1" or not on:
             return {}
-        nbar = self.size_nlist / max(state.N, 1)
+        nbar = self.mean_neighbors(state.N)
         out = {}
         for f in self._consumers:
             if getattr(f, "_state", None) is not state or not getattr(f, "use_tiles", False) or not getattr(f, "_tiled_kernels", False):
@@ -95,6 +96,7 @@ class NeighborList:
         self.head_list = torch.from_numpy(head_list.view(np.int64)).to(device)
         self.nlist = torch.from_numpy(nlist.view(np.int32) if nlist.size else np.zeros(1, np.int32)).to(device)
         self.size_nlist = int(nlist.size)
+        self.n_entries = int(n_neigh.sum(dtype=np.int64))
         self._tiles = {}
         self._last_pos = None  # positions at build time unknown: no displacement check, no pruned plans
         return self
@@ -109,7 +111,7 @@ class NeighborList:
         raise RuntimeError("this NeighborList has no builder: use nlist.Cell or set_arrays()")
 
     def mean_neighbors(self, N):
-        return self.size_nlist / max(N, 1)
+        return (self.n_entries or self.size_nlist) / max(N, 1)
 
 
 class Cell(NeighborList):

@@ -309,6 +309,13 @@ typedef struct azb_nlist_args
     unsigned int* d_uniq_count;      /* out [ceil(N / tile_size)] */
     unsigned int* d_uniq;            /* out [ceil(N / tile_size) * uniq_capacity] */
     unsigned int* d_uniq_max;        /* out [ceil(N / tile_size)] largest particle index the tile stages */
+    unsigned int rows_in_place;      /* 1 (with row_stride_hint > 0, n_views == 0, and d_nlist / capacity >= N * row_stride_hint already
+                                        set for azb_nlist_count): the single walk writes the rows straight into d_nlist at
+                                        head_list[i] = i * row_stride_hint — a valid HOOMD-layout list (disjoint rows ordered by
+                                        particle; the kernels read rows through head_list / n_neigh only) with gaps instead of tight
+                                        packing: no temporary rows, no scan, no compaction pass, *h_total = N * row_stride_hint and
+                                        azb_nlist_fill returns at once. A row that outgrows the bound makes azb_nlist_count fall
+                                        back to the packed head_list (*h_total = packed size) and azb_nlist_fill walks again. */
     } azb_nlist_args;
 
 typedef struct azb_nlist_plan_status

@@ -4,6 +4,7 @@ per-type-pair r_cut, non-periodic directions with ghosts outside the box."""
 
 import numpy as np
 import pytest
+import torch
 
 import azplugins_b200 as az
 import cases
@@ -15,6 +16,13 @@ pytestmark = pytest.mark.gpu
 
 def _rows(n_neigh, head, nl, N):
     return [np.sort(nl[int(head[i]): int(head[i]) + int(n_neigh[i])]) for i in range(N)]
+
+
+def _ordered_rows(cell, N):
+    nn = cell.n_neigh.cpu().numpy().view(np.uint32)
+    head = cell.head_list.cpu().numpy().view(np.uint64)
+    nl = cell.nlist.cpu().numpy().view(np.uint32)
+    return [nl[int(head[i]): int(head[i]) + int(nn[i])].copy() for i in range(N)]
 
 
 def _gpu_rows(cell, N):
@@ -45,22 +53,38 @@ def test_cell_nlist_matches_oracle(n, rho, rcut, bits):
     for i in range(n):
         assert np.array_equal(got[i], want[i]), i
     # rebuilding is deterministic (same row order, not just the same sets). The first build walked twice (count, fill); the
-    # second knows how long rows get and walks ONCE into fixed-stride rows (azb_nlist_args.row_stride_hint): same arrays.
+    # second knows how long rows get and walks ONCE, writing the rows in place at a fixed stride
+    # (azb_nlist_args.row_stride_hint + rows_in_place): head_list[i] = i * stride, same rows in the same order.
     first = (cell.nlist.clone(), cell.n_neigh.clone(), cell.head_list.clone())
-    assert cell._row_max == int(hs.n_neigh[:n].max())
+    first_rows = _ordered_rows(cell, n)
+    assert cell._row_max == int(hs.n_neigh[:n].max()) and cell.n_entries == int(hs.n_neigh[:n].sum()) == cell.size_nlist
+    stride = int(cell._row_max * 1.2) + 8
     cell.invalidate()
     cell.compute(st)
-    assert bool((first[0] == cell.nlist).all()) and bool((first[1] == cell.n_neigh).all()) and bool((first[2] == cell.head_list).all())
-    # a bound that is too small (rows outgrew it): the fill pass walks again, same arrays
+    assert cell.size_nlist == n * stride and cell.n_entries == int(hs.n_neigh[:n].sum())
+    assert bool((cell.head_list.cpu() == torch.arange(n, dtype=torch.int64) * stride).all()) and bool((first[1] == cell.n_neigh).all())
+    rows = _ordered_rows(cell, n)
+    assert all(np.array_equal(a, b) for a, b in zip(first_rows, rows))
+    assert cell.mean_neighbors(n) == pytest.approx(hs.n_neigh[:n].mean())
+
+    def same_arrays():
+        return bool((first[0] == cell.nlist[: first[0].numel()]).all()) and bool((first[1] == cell.n_neigh).all()) and bool((first[2] == cell.head_list).all())
+
+    # a bound that is too small (rows outgrew it): the packed head_list comes back and the fill pass walks again, same arrays
     cell._row_max = 3
     cell.invalidate()
     cell.compute(st)
-    assert bool((first[0] == cell.nlist).all()) and bool((first[1] == cell.n_neigh).all()) and bool((first[2] == cell.head_list).all())
-    # and the classic two-walk build on request
+    assert same_arrays() and cell.size_nlist == first[0].numel()
+    # one walk into temporary rows + compaction (tightly packed list) on request
+    cell.rows_in_place = False
+    cell.invalidate()
+    cell.compute(st)
+    assert same_arrays() and cell.size_nlist == first[0].numel()
+    # and the classic two-walk build
     cell.single_walk = False
     cell.invalidate()
     cell.compute(st)
-    assert bool((first[0] == cell.nlist).all())
+    assert same_arrays()
 
 
 def test_cell_nlist_bond_exclusions_and_force_through_cell():
