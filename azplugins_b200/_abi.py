@@ -79,6 +79,7 @@ class TileBuildArgs(C.Structure):
         ("d_tile_list", C.c_void_p),
         ("n_tile_list", C.c_uint),
         ("slot_row_stride", C.c_uint),
+        ("base_plan", C.c_void_p),
     ]
 
 

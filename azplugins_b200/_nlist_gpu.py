@@ -165,7 +165,7 @@ class TilePlanHandle:
         self.c.lane_width, self.c.max_slot_span = lane_width, max_slot_span
         self.c.d_uniq_count, self.c.d_uniq, self.c.d_slots = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr()
         self.c.d_row_count = row_count.data_ptr() if row_count is not None else None
-        self.c.n_entries = int(entries) if (entries is not None and row_count is not None) else 0
+        self.c.n_entries = int(entries) if entries is not None else 0  # (a list with gaps between rows: size_nlist overstates it)
         self.c.slot_row_stride = int(slot_row_stride)
 
     tile_size = property(lambda self: self.c.tile_size)
@@ -189,7 +189,7 @@ class TilePlanHandle:
         return torch.where(count > 0, last, torch.zeros_like(last))
 
 
-def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None):
+def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None, base_plan=None):
     """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles).
     ``prune = (state, keep_rsq)``: drop the entries that cannot come inside the force's cutoff before the next rebuild
     (``keep_rsq``: device Scalar tensor [T*T] of (r_cut + buffer)^2; the state's positions must be the ones the list was built
@@ -219,6 +219,8 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
         a.prune_scalar_bits, a.prune_ntypes = state.scalar_bits, len(state.types)
         a.prune_box = state.box.as_abi()
         a.d_row_count = row_count.data_ptr()
+        if base_plan is not None:
+            a.base_plan = C.cast(base_plan.pointer(), C.c_void_p)
     max_uniq, max_span, overflow = C.c_uint(0), C.c_uint(0), C.c_uint(0)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -708,6 +708,270 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
             atomicMax(status + 2, (unsigned int)(shead + ((nn_own + M - 1u) & ~(M - 1u)) - slot_head(0u)));
         }
     }
+
+// ---- a pruned view derived from the unpruned plan of the same list (azb_tile_build_args.base_plan) ----------------------------
+// Several forces on one list (C5: ExpandedYukawa walks every entry, DPD a pruned view) used to pay the hash build twice. The
+// unpruned plan already names every entry's neighbour by a 16-bit slot into an ASCENDING distinct list, so the pruned view
+// needs no hash and no sort: stage the positions of the tile's distinct neighbours once (U x 16 B), test every entry against
+// its staged neighbour (2-byte slot read, shared-memory position), flag the slots that survive, scan the flags — the ranks of
+// the surviving slots ARE the pruned plan's slots, and its distinct list is the flagged subsequence, still ascending.
+// Output identical to tiles_build_flat_kernel<PruneDev> with full_set = false.
+// dynamic shared memory: pos[ucap_b] V4 | own[ts] V4 | head[ts] u64 | off[ts + 1] u32 | keep[KEEP_WORDS] u32 | rank[ucap_b] u32
+template<class S>
+__global__ void __launch_bounds__(256) tiles_prune_kernel(const PruneDev<S> prune, const unsigned int* __restrict__ b_uniq_count,
+                                                          const unsigned int* __restrict__ b_uniq, const uint16_t* __restrict__ b_slots,
+                                                          const unsigned int b_ucap, const unsigned int b_smem_uniq, const unsigned int b_wlog,
+                                                          const unsigned int b_slot_stride, const unsigned int slot_stride,
+                                                          unsigned int* __restrict__ row_count, const unsigned int* __restrict__ n_neigh,
+                                                          const size_t* __restrict__ head_list, const unsigned int N, const unsigned int tile_size,
+                                                          const unsigned int ucap, const unsigned int wlog, unsigned int* __restrict__ uniq_count,
+                                                          unsigned int* __restrict__ uniq, uint16_t* __restrict__ slots,
+                                                          unsigned int* __restrict__ status)
+    {
+    typedef typename vec4<S>::type V4;
+    constexpr int UN = 4;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    V4* s_pos = reinterpret_cast<V4*>(smem_raw);
+    V4* s_own = s_pos + b_smem_uniq;
+    unsigned long long* s_head = reinterpret_cast<unsigned long long*>(s_own + tile_size);
+    unsigned int* s_off = reinterpret_cast<unsigned int*>(s_head + tile_size);
+    unsigned int* s_keep = s_off + tile_size + 1u;
+    unsigned int* s_rank = s_keep + KEEP_WORDS;
+    __shared__ unsigned int s_wtot[8];
+
+    const unsigned int tile = blockIdx.x;
+    const unsigned int first = tile * tile_size;
+    const unsigned int last = min(first + tile_size, N);
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
+    auto layout = [](const unsigned int o, const unsigned int wl) -> unsigned int
+    {
+        const unsigned int W = 1u << wl, M = 4u << wl, r = o & (M - 1u); // entry o = b 4W + u W + l sits at b 4W + 4 l + u
+        return (o - r) + 4u * (r & (W - 1u)) + (r >> wl);
+    };
+    auto slot_head = [&](const unsigned int p, const unsigned int wl, const unsigned int stride) -> size_t
+    {
+        const unsigned int i = first + p;
+        const size_t A = wl < 1u ? 8u : (4u << wl); // AZB_SLOT_ROW_ALIGN(W)
+        return stride ? (size_t)i * stride : (((size_t)s_head[p] + A * i) & ~(A - 1u));
+    };
+
+    const unsigned int Ub = b_uniq_count[tile];
+    if (Ub == EMPTY_KEY) // the base plan has no set for this tile
+        {
+        if (threadIdx.x == 0)
+            {
+            uniq_count[tile] = EMPTY_KEY;
+            atomicExch(status + 1, 1u);
+            }
+        return;
+        }
+    // 0. the tile's distinct neighbours (positions), row headers, own positions; exclusive scan of the row lengths
+    const unsigned int* buq = b_uniq + (size_t)tile * b_ucap;
+    for (unsigned int s0 = threadIdx.x; s0 < Ub; s0 += 4u * blockDim.x)
+        {
+        unsigned int g[4];
+        V4 pv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            g[u] = (s0 + u * blockDim.x < Ub) ? buq[s0 + u * blockDim.x] : EMPTY_KEY;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != EMPTY_KEY)
+                pv[u] = ld4(prune.pos + g[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != EMPTY_KEY)
+                {
+                s_pos[s0 + u * blockDim.x] = pv[u];
+                s_rank[s0 + u * blockDim.x] = 0u;
+                }
+        }
+    const unsigned int p_own = threadIdx.x; // blockDim.x = 256 >= tile_size
+    unsigned int nn_own = 0;
+    if (p_own < tile_size && first + p_own < last)
+        {
+        nn_own = n_neigh[first + p_own];
+        s_head[p_own] = head_list[first + p_own];
+        s_own[p_own] = ld4(prune.pos + first + p_own);
+        }
+    unsigned int incl = nn_own;
+#pragma unroll
+    for (unsigned int d = 1; d < 32; d <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d)
+            incl += t;
+        }
+    if (lane == 31u)
+        s_wtot[warp] = incl;
+    __syncthreads();
+    unsigned int wbase = 0, total = 0;
+    for (unsigned int w = 0; w < nwarps; ++w)
+        {
+        const unsigned int t = s_wtot[w];
+        wbase += w < warp ? t : 0u;
+        total += t;
+        }
+    if (p_own < tile_size)
+        s_off[p_own] = wbase + incl - nn_own;
+    if (threadIdx.x == 0)
+        s_off[tile_size] = total;
+    __syncthreads();
+    const unsigned int E = total;
+    if (E > KEEP_WORDS * 32u)
+        {
+        if (threadIdx.x == 0)
+            {
+            uniq_count[tile] = EMPTY_KEY;
+            atomicMax(status + 0, ucap + 1u);
+            atomicExch(status + 1, 1u);
+            }
+        return;
+        }
+    const unsigned int chunk = ((E + nwarps - 1u) / nwarps + 31u) & ~31u;
+    const unsigned int e0 = min(E, warp * chunk), e1 = min(E, e0 + chunk);
+    unsigned int r_first = 0;
+    if (e0 < e1)
+        {
+        const unsigned int e = min(e0 + lane, e1 - 1u);
+        unsigned int lo = 0, hi = tile_size; // s_off[lo] <= e < s_off[hi]
+        while (hi - lo > 1u)
+            {
+            const unsigned int mid = (lo + hi) >> 1;
+            if (s_off[mid] <= e)
+                lo = mid;
+            else
+                hi = mid;
+            }
+        r_first = lo;
+        }
+
+    // 1. keep test of every entry against its staged neighbour; surviving slots are flagged
+    unsigned int r = r_first;
+    for (unsigned int base = e0; base < e1; base += 32u * UN)
+        {
+        unsigned int sl[UN], rr[UN];
+        bool valid[UN];
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            const unsigned int e = base + 32u * u + lane;
+            valid[u] = e < e1;
+            sl[u] = 0;
+            if (valid[u])
+                {
+                while (e >= s_off[r + 1u])
+                    ++r;
+                sl[u] = b_slots[slot_head(r, b_wlog, b_slot_stride) + layout(e - s_off[r], b_wlog)];
+                }
+            rr[u] = r;
+            }
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            const bool keep = valid[u] && kept_staged(prune, s_own[rr[u]], s_pos[sl[u]]);
+            const unsigned int m = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0 && base + 32u * u < e1)
+                s_keep[(base + 32u * u) >> 5] = m;
+            if (keep)
+                s_rank[sl[u]] = 1u; // (benign race: every writer stores the same value)
+            }
+        }
+    __syncthreads();
+
+    // 2. ranks of the surviving slots (exclusive scan of the flags, 8 slots per thread) = the pruned plan's slots; its distinct
+    // list is the surviving subsequence of the base list, still ascending
+    unsigned int f[8], mine = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+        {
+        const unsigned int sidx = threadIdx.x * 8u + q;
+        f[q] = sidx < Ub ? s_rank[sidx] : 0u;
+        mine += f[q];
+        }
+    incl = mine;
+#pragma unroll
+    for (unsigned int d = 1; d < 32; d <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d)
+            incl += t;
+        }
+    __syncthreads(); // (s_wtot is reused)
+    if (lane == 31u)
+        s_wtot[warp] = incl;
+    __syncthreads();
+    wbase = 0, total = 0;
+    for (unsigned int w = 0; w < nwarps; ++w)
+        {
+        const unsigned int t = s_wtot[w];
+        wbase += w < warp ? t : 0u;
+        total += t;
+        }
+    const unsigned int U = total;
+    unsigned int* out = uniq + (size_t)tile * ucap;
+    unsigned int run = wbase + incl - mine;
+    if (U <= ucap)
+        {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            {
+            const unsigned int sidx = threadIdx.x * 8u + q;
+            if (sidx < Ub)
+                {
+                s_rank[sidx] = run;
+                if (f[q])
+                    out[run] = buq[sidx];
+                run += f[q];
+                }
+            }
+        }
+    if (threadIdx.x == 0)
+        {
+        uniq_count[tile] = U <= ucap ? U : EMPTY_KEY;
+        atomicMax(status + 0, U);
+        if (U > ucap)
+            atomicExch(status + 1, 1u);
+        }
+    if (U > ucap)
+        return;
+    __syncthreads();
+
+    // 3. surviving entries -> pruned slot rows (list order), in the view's own lane-transposed layout
+    r = r_first;
+    for (unsigned int base = e0; base < e1; base += 32u * UN)
+        {
+#pragma unroll
+        for (int u = 0; u < UN; ++u)
+            {
+            const unsigned int e = base + 32u * u + lane;
+            if (e < e1)
+                {
+                while (e >= s_off[r + 1u])
+                    ++r;
+                if ((s_keep[e >> 5] >> (e & 31u)) & 1u)
+                    {
+                    const unsigned int b0 = s_off[r];
+                    const unsigned int s_old = b_slots[slot_head(r, b_wlog, b_slot_stride) + layout(e - b0, b_wlog)];
+                    slots[slot_head(r, wlog, slot_stride) + layout(count_bits(s_keep, b0, e), wlog)] = (uint16_t)s_rank[s_old];
+                    }
+                }
+            }
+        }
+    if (p_own < tile_size && first + p_own < last)
+        {
+        const unsigned int i = first + p_own;
+        const unsigned int M = 4u << wlog;
+        const unsigned int out_n = count_bits(s_keep, s_off[p_own], s_off[p_own + 1u]);
+        const unsigned int out_p = (out_n + M - 1u) & ~(M - 1u);
+        const size_t shead = slot_head(p_own, wlog, slot_stride);
+        for (unsigned int o = out_n; o < out_p; ++o)
+            slots[shead + layout(o, wlog)] = 0;
+        row_count[i] = out_n;
+        if (i + 1u == last) // extent of the tile's slot rows, as tiles_build_kernel reports it
+            atomicMax(status + 2, (unsigned int)(shead + ((nn_own + M - 1u) & ~(M - 1u)) - slot_head(0u, wlog, slot_stride)));
+        }
+    }
     } // namespace azb
 
 extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,
@@ -741,6 +1005,59 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
     if (n_tiles == 0)
         return 0;
     const bool prune = a->d_prune_pos != nullptr;
+    if (a->base_plan)
+        {
+        // a pruned view derived from the unpruned plan of the same list (tiles_prune_kernel)
+        const azb_tile_plan& b = *a->base_plan;
+        const unsigned int Wb = b.lane_width;
+        if (!prune || !a->d_prune_rsq || !a->d_row_count || a->prune_ntypes == 0 || G != 0u || a->d_tile_list || a->prune_full_set
+            || (a->prune_scalar_bits != 32 && a->prune_scalar_bits != 64) || b.tile_size != ts || b.n_tiles != n_tiles || b.d_row_count
+            || !b.d_uniq_count || !b.d_uniq || !b.d_slots || b.max_uniq > b.uniq_capacity || b.max_uniq > ucap
+            || !(Wb == 1 || Wb == 2 || Wb == 4 || Wb == 8 || Wb == 16))
+            return AZB_ERR_BAD_ARGUMENT;
+        unsigned int wlog_b = 0, wlog_v = 0;
+        while ((1u << wlog_b) < Wb)
+            ++wlog_b;
+        while ((1u << wlog_v) < W)
+            ++wlog_v;
+        const unsigned int su = ((b.max_uniq > 0 ? b.max_uniq : 1u) + 7u) & ~7u;
+        if (su > 2048u)
+            return AZB_ERR_BAD_ARGUMENT; // (the rank scan handles 256 x 8 slots)
+        const size_t v4 = a->prune_scalar_bits == 32 ? 16 : 32;
+        const size_t psmem = (size_t)su * v4 + (size_t)ts * v4 + (size_t)ts * 8 + ((size_t)ts + 1) * 4 + azb::KEEP_WORDS * 4 + (size_t)su * 4;
+        if (a->prune_scalar_bits == 32)
+            {
+            azb::PruneDev<float> p = {(const float4*)a->d_prune_pos, (const float*)a->d_prune_rsq, a->prune_ntypes, azb::make_box<float>(a->prune_box)};
+            if (psmem > 48 * 1024 && (err = cudaFuncSetAttribute(azb::tiles_prune_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)) != cudaSuccess)
+                return (int)err;
+            azb::tiles_prune_kernel<float><<<n_tiles, 256, psmem, s>>>(p, b.d_uniq_count, b.d_uniq, b.d_slots, b.uniq_capacity, su, wlog_b, b.slot_row_stride,
+                                                                      a->slot_row_stride, a->d_row_count, a->d_n_neigh, a->d_head_list, a->N, ts, ucap, wlog_v,
+                                                                      a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status);
+            }
+        else
+            {
+            azb::PruneDev<double> p = {(const azb::double4a*)a->d_prune_pos, (const double*)a->d_prune_rsq, a->prune_ntypes,
+                                       azb::make_box<double>(a->prune_box)};
+            if (psmem > 48 * 1024 && (err = cudaFuncSetAttribute(azb::tiles_prune_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem)) != cudaSuccess)
+                return (int)err;
+            azb::tiles_prune_kernel<double><<<n_tiles, 256, psmem, s>>>(p, b.d_uniq_count, b.d_uniq, b.d_slots, b.uniq_capacity, su, wlog_b, b.slot_row_stride,
+                                                                       a->slot_row_stride, a->d_row_count, a->d_n_neigh, a->d_head_list, a->N, ts, ucap, wlog_v,
+                                                                       a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status);
+            }
+        err = cudaGetLastError();
+        if (err != cudaSuccess)
+            return (int)err;
+        unsigned int hs[4] = {0, 0, 0, 0};
+        err = cudaMemcpyAsync(hs, a->d_status, sizeof(hs), cudaMemcpyDeviceToHost, s);
+        if (err == cudaSuccess)
+            err = cudaStreamSynchronize(s);
+        if (err != cudaSuccess)
+            return (int)err;
+        *h_max_uniq = hs[0];
+        *h_overflow = hs[1];
+        *h_max_slot_span = hs[2];
+        return 0;
+        }
     // group_width == 0 (rows keep the list's order; the default): the flat-range builder. AZB_TILES_ROWWISE=1 keeps the row-wise
     // kernel for A/B runs; bank-rotated rows (group_width > 0, opt-in) always take it.
     static const bool rowwise = getenv("AZB_TILES_ROWWISE") != nullptr;

@@ -73,11 +73,35 @@ class NeighborList:
 
             plan = None
             ts = int(tile_size)
+            if prune is not None and int(group_width) == 0 and os.environ.get("AZB_NO_DERIVED_PLANS", "0") != "1":
+                # a pruned view is derived from the unpruned plan of the same list when some consumer needs that one anyway
+                # (azb_tile_build_args.base_plan: no second hash build)
+                base = self._unpruned_plan(N, ts, int(uniq_capacity))
+                if base is not None:
+                    plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), 0, prune, base_plan=base)
             while plan is None and ts >= 32:
                 plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width), prune)
                 ts //= 2
             self._tiles[key] = plan
         return self._tiles[key]
+
+    def _unpruned_plan(self, N, tile_size, uniq_capacity):
+        """An unpruned, list-ordered plan of the current arrays with this tile size: one that is cached already, or the one
+        another consumer of the list is going to ask for (built now). ``None`` when nobody needs one."""
+        for key, plan in self._tiles.items():
+            if plan is not None and key[0] == tile_size and key[1] == uniq_capacity and key[3] == 0 and key[4] is None \
+                    and plan.tile_size == tile_size and not plan.from_list_build:
+                return plan
+        nbar = self.mean_neighbors(N)
+        for f in self._consumers:
+            if getattr(f, "_state", None) is None or not getattr(f, "use_tiles", False) or not getattr(f, "_tiled_kernels", False):
+                continue
+            req = f._plan_request(nbar)
+            if req["prune"] is None and req["group_width"] == 0 and int(req["tile_size"]) == tile_size:
+                plan = self.tile_plan(N, **req)
+                if plan is not None and plan.tile_size == tile_size:
+                    return plan
+        return None
 
     def r_list(self, types):
         """(T,T) matrix of r_cut_max + buffer over all consumers; 0 where no consumer interacts."""
