@@ -398,7 +398,115 @@ __device__ __forceinline__ unsigned int count_bits(const unsigned int* m, unsign
     return c + __popc(m[w1] & hi);
     }
 
-// dynamic shared memory: own[ts] V4 (pruning) | head[ts] u64 | keys[hcap] u32 | list[ucap] u32 | off[ts + 1] u32 |
+// block-wide exclusive scan of one value per thread (blockDim.x <= 256); s_wtot: 8 words of scratch
+__device__ __forceinline__ unsigned int block_scan_exclusive(const unsigned int v, unsigned int* s_wtot, unsigned int& total)
+    {
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
+    unsigned int incl = v;
+#pragma unroll
+    for (unsigned int d = 1; d < 32; d <<= 1)
+        {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d)
+            incl += t;
+        }
+    __syncthreads(); // (s_wtot may still be read from a previous scan)
+    if (lane == 31u)
+        s_wtot[warp] = incl;
+    __syncthreads();
+    unsigned int wbase = 0;
+    total = 0;
+    for (unsigned int w = 0; w < nwarps; ++w)
+        {
+        const unsigned int t = s_wtot[w];
+        wbase += w < warp ? t : 0u;
+        total += t;
+        }
+    return wbase + incl - v;
+    }
+
+// Ascending sort of the U distinct keys in list[0 .. U) into sorted[0 .. U). list must hold roundup(U, 128) entries.
+// Runs of 128 keys are sorted by one warp each in registers (4 keys per lane, bitonic network over shuffles), then every key
+// finds its final rank as its position in its own run + the number of smaller keys in every other run (binary searches).
+__device__ __forceinline__ void tile_sort(unsigned int* list, unsigned int* sorted, const unsigned int U)
+    {
+    const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nwarps = blockDim.x >> 5;
+    const unsigned int runs = (U + 127u) >> 7;
+    for (unsigned int s = U + threadIdx.x; s < (runs << 7); s += blockDim.x)
+        list[s] = EMPTY_KEY;
+    __syncthreads();
+    for (unsigned int r = warp; r < runs; r += nwarps)
+        {
+        unsigned int* run = list + (r << 7);
+        unsigned int v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            v[q] = run[lane * 4u + q];
+#pragma unroll
+        for (unsigned int size = 2; size <= 128u; size <<= 1)
+            {
+#pragma unroll
+            for (unsigned int j = size >> 1; j > 0; j >>= 1)
+                {
+                if (j >= 4u)
+                    {
+                    const bool lower = (lane & (j >> 2)) == 0u;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        {
+                        const unsigned int o = __shfl_xor_sync(0xffffffffu, v[q], j >> 2);
+                        const bool up = ((lane * 4u + q) & size) == 0u;
+                        v[q] = (lower == up) ? min(v[q], o) : max(v[q], o);
+                        }
+                    }
+                else
+                    {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if ((q & j) == 0u)
+                            {
+                            const bool up = ((lane * 4u + q) & size) == 0u;
+                            const unsigned int a = v[q], b = v[q | j];
+                            if ((a > b) == up)
+                                {
+                                v[q] = b;
+                                v[q | j] = a;
+                                }
+                            }
+                    }
+                }
+            }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            run[lane * 4u + q] = v[q];
+        }
+    __syncthreads();
+    for (unsigned int s = threadIdx.x; s < (runs << 7); s += blockDim.x)
+        {
+        const unsigned int key = list[s];
+        if (key == EMPTY_KEY)
+            continue;
+        unsigned int rank = s & 127u;
+        const unsigned int mine = s >> 7;
+        for (unsigned int r = 0; r < runs; ++r)
+            if (r != mine)
+                {
+                const unsigned int* run = list + (r << 7);
+                unsigned int lo = 0; // number of keys of this run below `key`
+#pragma unroll
+                for (unsigned int step = 64; step > 0; step >>= 1)
+                    if (run[lo + step - 1u] < key)
+                        lo += step;
+                if (run[lo] < key) // (lo <= 127 here: the seven steps add up to at most 127)
+                    ++lo;
+                rank += lo;
+                }
+        sorted[rank] = key;
+        }
+    __syncthreads();
+    }
+
+// dynamic shared memory: own[ts] V4 (pruning) | head[ts] u64 | keys[hcap] u32 | list[max(ucap, 128)] u32 | sorted[ucap] u32 | off[ts + 1] u32 |
 //                        keep[KEEP_WORDS] u32 (pruning) | vals[hcap] u16
 template<class Prune>
 __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune, const bool full_set, const unsigned int* __restrict__ tile_list,
@@ -428,7 +536,8 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
     unsigned long long* s_head = reinterpret_cast<unsigned long long*>(s_own + (PRUNE ? tile_size : 0u));
     unsigned int* keys = reinterpret_cast<unsigned int*>(s_head + tile_size);
     unsigned int* list = keys + hcap;
-    unsigned int* s_off = list + ucap;
+    unsigned int* sorted = list + max(ucap, 128u);
+    unsigned int* s_off = sorted + ucap;
     unsigned int* s_keep = s_off + tile_size + 1u;
     uint16_t* vals = reinterpret_cast<uint16_t*>(s_keep + (PRUNE ? KEEP_WORDS : 0u));
     __shared__ unsigned int s_count, s_fill, s_wtot[8];
@@ -605,36 +714,14 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
         if (key != EMPTY_KEY)
             list[atomicAdd(&s_fill, 1u)] = key;
         }
-    unsigned int P = 1;
-    while (P < U)
-        P <<= 1;
     __syncthreads();
-    for (unsigned int s = U + threadIdx.x; s < P; s += blockDim.x)
-        list[s] = EMPTY_KEY; // P <= ucap because ucap is a power of two
-    __syncthreads();
-    for (unsigned int size = 2; size <= P; size <<= 1)
-        for (unsigned int stride = size >> 1; stride > 0; stride >>= 1)
-            {
-            for (unsigned int t = threadIdx.x; t < (P >> 1); t += blockDim.x)
-                {
-                const unsigned int lo = 2 * t - (t & (stride - 1u));
-                const unsigned int hi = lo + stride;
-                const bool up = (lo & size) == 0;
-                const unsigned int a = list[lo], b = list[hi];
-                if ((a > b) == up)
-                    {
-                    list[lo] = b;
-                    list[hi] = a;
-                    }
-                }
-            __syncthreads();
-            }
+    tile_sort(list, sorted, U);
 
     // 3. publish the list; remember each key's rank next to its table position
     unsigned int* out = uniq + (size_t)tile * ucap;
     for (unsigned int s = threadIdx.x; s < U; s += blockDim.x)
         {
-        const unsigned int key = list[s];
+        const unsigned int key = sorted[s];
         out[s] = key;
         unsigned int h = tile_hash(key, hshift);
         while (keys[h] != key)
@@ -1072,7 +1159,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         {                                                                                                                               \
         if (flat)                                                                                                                       \
             {                                                                                                                           \
-            const size_t fsmem = smem + (size_t)ts * 8 + ((size_t)ts + 1) * 4                                                           \
+            const size_t fsmem = smem + (size_t)(ucap < 128 ? 128 - ucap : 0) * 4 + (size_t)ucap * 4 + (size_t)ts * 8 + ((size_t)ts + 1) * 4                                                           \
                                  + (azb::PruneTraits<PRUNE_T>::on ? (size_t)ts * sizeof(azb::PruneTraits<PRUNE_T>::V4) + azb::KEEP_WORDS * 4 : 0); \
             if (fsmem > 48 * 1024)                                                                                                      \
                 {                                                                                                                       \
