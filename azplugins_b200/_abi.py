@@ -80,6 +80,7 @@ class TileBuildArgs(C.Structure):
         ("n_tile_list", C.c_uint),
         ("slot_row_stride", C.c_uint),
         ("base_plan", C.c_void_p),
+        ("sort_rows", C.c_uint),
     ]
 
 

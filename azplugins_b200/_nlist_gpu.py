@@ -39,7 +39,7 @@ def build_cell_nlist(nl, state, row_align=1):
     a.row_stride_hint = (int(prev_max * 1.2) + 8) if (prev_max and getattr(nl, "single_walk", True)) else 0
     # tile plans the consumers will ask for, emitted by the same walk (views of azb_nlist_args)
     requests = nl.plan_requests(state) if a.row_stride_hint else {}
-    usable = {k: r for k, r in requests.items() if k[3] == 0}
+    usable = {k: r for k, r in requests.items() if k[3] == 0 and not k[5]}
     if len(usable) > 4 or len({k[0] for k in usable}) > 1:
         usable = {}
     view_keys = list(usable)
@@ -158,6 +158,7 @@ class TilePlanHandle:
         self.uniq_count, self.uniq, self.slots, self.row_count = uniq_count, uniq, slots, row_count
         self.uniq_max = uniq_max  # plans emitted by the list build: the staged sets are not ascending, the largest index is kept apart
         self.from_list_build = uniq_max is not None
+        self.sorted_rows = False  # slot rows in ascending slot order instead of list order (azb_tile_build_args.sort_rows)
         self.build_ms = build_ms
         self.entries = entries  # list entries the plan's rows hold (fewer than the list's when pruned)
         self.c = _abi.TilePlan()
@@ -189,7 +190,7 @@ class TilePlanHandle:
         return torch.where(count > 0, last, torch.zeros_like(last))
 
 
-def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None, base_plan=None):
+def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0, prune=None, base_plan=None, sort_rows=False):
     """``azb_tiles_build`` over the list's current arrays; returns ``None`` on overflow (caller retries smaller tiles).
     ``prune = (state, keep_rsq)``: drop the entries that cannot come inside the force's cutoff before the next rebuild
     (``keep_rsq``: device Scalar tensor [T*T] of (r_cut + buffer)^2; the state's positions must be the ones the list was built
@@ -210,6 +211,7 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     a.d_n_neigh, a.d_nlist, a.d_head_list = nl.n_neigh.data_ptr(), nl.nlist.data_ptr(), nl.head_list.data_ptr()
     a.size_nlist, a.N, a.tile_size, a.uniq_capacity, a.lane_width = nl.size_nlist, N, tile_size, uniq_capacity, lane_width
     a.group_width = group_width
+    a.sort_rows = 1 if (sort_rows and group_width == 0) else 0
     a.d_uniq_count, a.d_uniq, a.d_slots, a.d_status = uniq_count.data_ptr(), uniq.data_ptr(), slots.data_ptr(), status.data_ptr()
     row_count = None
     if prune is not None:
@@ -231,5 +233,7 @@ def build_tile_plan(nl, N, tile_size, uniq_capacity, lane_width=1, group_width=0
     if overflow.value:
         return None
     entries = int(row_count.sum().item()) if row_count is not None else (nl.n_entries or nl.size_nlist)
-    return TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, lane_width, max_span.value, uniq_count, uniq, slots,
+    plan = TilePlanHandle(tile_size, n_tiles, uniq_capacity, max_uniq.value, lane_width, max_span.value, uniq_count, uniq, slots,
                           e0.elapsed_time(e1), row_count, entries)
+    plan.sorted_rows = bool(a.sort_rows) or (base_plan is not None and getattr(base_plan, "sorted_rows", False))
+    return plan

@@ -519,6 +519,7 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
                                                                const unsigned int ucap,
                                                                const unsigned int hcap_log2,
                                                                const unsigned int wlog,
+                                                               const bool sort_rows,
                                                                unsigned int* __restrict__ uniq_count,
                                                                unsigned int* __restrict__ uniq,
                                                                uint16_t* __restrict__ slots,
@@ -540,6 +541,7 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
     unsigned int* s_off = sorted + ucap;
     unsigned int* s_keep = s_off + tile_size + 1u;
     uint16_t* vals = reinterpret_cast<uint16_t*>(s_keep + (PRUNE ? KEEP_WORDS : 0u));
+    unsigned int* s_bitmap = reinterpret_cast<unsigned int*>(vals + hcap); // [8 warps][128 words] (sort_rows)
     __shared__ unsigned int s_count, s_fill, s_wtot[8];
 
     const unsigned int tile = tile_list ? tile_list[blockIdx.x] : blockIdx.x;
@@ -735,6 +737,66 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
         }
     __syncthreads();
 
+    // 4'. (sort_rows) slot rows in ASCENDING slot order instead of list order: the lanes of neighbouring particles then read
+    // neighbouring or identical staged positions at the same time (fewer shared-memory bank conflicts in the pair kernels). A warp
+    // takes a row: every (kept) entry sets the bit of its slot in a U-bit map; the row is the enumeration of the set bits.
+    if (sort_rows)
+        {
+        unsigned int* bm = s_bitmap + warp * 128u;
+        const unsigned int nwords = (U + 31u) >> 5;
+        const unsigned int wpl = (nwords + 31u) >> 5; // words per lane (<= 4)
+        for (unsigned int p = warp; p < last - first; p += nwarps)
+            {
+            for (unsigned int w = lane; w < nwords; w += 32u)
+                bm[w] = 0u;
+            __syncwarp();
+            const unsigned int b0 = s_off[p], nn = s_off[p + 1u] - b0;
+            const unsigned int* row = nlist + s_head[p];
+            for (unsigned int kk = lane; kk < nn; kk += 32u)
+                {
+                if (PRUNE && !((s_keep[(b0 + kk) >> 5] >> ((b0 + kk) & 31u)) & 1u))
+                    continue;
+                const unsigned int j = row[kk];
+                unsigned int h = tile_hash(j, hshift);
+                while (keys[h] != j)
+                    h = (h + 1u) & hmask;
+                const unsigned int v = vals[h];
+                atomicOr(&bm[v >> 5], 1u << (v & 31u));
+                }
+            __syncwarp();
+            unsigned int mine = 0;
+            for (unsigned int q = 0; q < wpl; ++q)
+                {
+                const unsigned int w = lane * wpl + q;
+                mine += w < nwords ? __popc(bm[w]) : 0u;
+                }
+            unsigned int incl = mine;
+#pragma unroll
+            for (unsigned int d = 1; d < 32; d <<= 1)
+                {
+                const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d)
+                    incl += t;
+                }
+            unsigned int o = incl - mine;
+            uint16_t* srow = slots + slot_head(p);
+            for (unsigned int q = 0; q < wpl; ++q)
+                {
+                const unsigned int w = lane * wpl + q;
+                unsigned int m = w < nwords ? bm[w] : 0u;
+                while (m)
+                    {
+                    const unsigned int b = __ffs(m) - 1u;
+                    m &= m - 1u;
+                    srow[slot_at(0, o) ] = (uint16_t)(w * 32u + b);
+                    ++o;
+                    }
+                }
+            __syncwarp();
+            }
+        }
+    else
+        {
     // 4. list entry -> slot, in the lane-transposed, padded row layout (include/azb200.h, AZB_SLOT_HEAD); a pruned row holds
     // its kept entries in list order
     r = r_first;
@@ -771,6 +833,7 @@ __global__ void __launch_bounds__(256) tiles_build_flat_kernel(const Prune prune
                 const unsigned int o = PRUNE ? count_bits(s_keep, b0, ee[u]) : ee[u] - b0;
                 slots[slot_at(slot_head(rr[u]), o)] = vals[h];
                 }
+        }
         }
     // per row: padding, kept count, layout checks
     if (p_own < tile_size && first + p_own < last)
@@ -1160,7 +1223,8 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
         if (flat)                                                                                                                       \
             {                                                                                                                           \
             const size_t fsmem = smem + (size_t)(ucap < 128 ? 128 - ucap : 0) * 4 + (size_t)ucap * 4 + (size_t)ts * 8 + ((size_t)ts + 1) * 4                                                           \
-                                 + (azb::PruneTraits<PRUNE_T>::on ? (size_t)ts * sizeof(azb::PruneTraits<PRUNE_T>::V4) + azb::KEEP_WORDS * 4 : 0); \
+                                 + (azb::PruneTraits<PRUNE_T>::on ? (size_t)ts * sizeof(azb::PruneTraits<PRUNE_T>::V4) + azb::KEEP_WORDS * 4 : 0) \
+                                 + (a->sort_rows ? 8 * 128 * 4 : 0);                                                                     \
             if (fsmem > 48 * 1024)                                                                                                      \
                 {                                                                                                                       \
                 err = cudaFuncSetAttribute(azb::tiles_build_flat_kernel<PRUNE_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem); \
@@ -1168,7 +1232,7 @@ extern "C" int azb_tiles_build(const azb_tile_build_args* a, unsigned int* h_max
                     return (int)err;                                                                                                    \
                 }                                                                                                                       \
             azb::tiles_build_flat_kernel<PRUNE_T><<<n_tiles, 256, fsmem, s>>>(PRUNE_V, a->prune_full_set != 0, a->d_tile_list, a->slot_row_stride, a->d_row_count, a->d_n_neigh, a->d_nlist, \
-                                                                            a->d_head_list, a->N, ts, ucap, hcap_log2, wlog, a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status); \
+                                                                            a->d_head_list, a->N, ts, ucap, hcap_log2, wlog, a->sort_rows != 0, a->d_uniq_count, a->d_uniq, a->d_slots, a->d_status); \
             break;                                                                                                                      \
             }                                                                                                                           \
         if (smem > 48 * 1024)                                                                                                           \

@@ -149,8 +149,9 @@ class Pair(Force):
         """What this force asks of a tile plan of its list: ``nl.tile_plan`` keyword arguments. The list build itself can emit
         the plan when it knows the request beforehand (``nlist.NeighborList.build`` collects them from its consumers)."""
         prune, prune_key = self._prune_spec(require_built)
+        gw = self._group_width(nbar) if prune is None else 0
         return dict(tile_size=self.tile_size or self._auto_tile_size(nbar), lane_width=self._slot_lane_width(nbar),
-                    group_width=self._group_width(nbar) if prune is None else 0, prune=prune, prune_key=prune_key)
+                    group_width=gw, prune=prune, prune_key=prune_key, sort_rows=bool(getattr(self.nlist, "sort_rows", False)) and gw == 0)
 
     def _current_plan(self):
         """Tile plan of the current neighbour list for this force's kernel (None: gather from global memory)."""

@@ -25,6 +25,8 @@ class NeighborList:
         self.n_entries = 0  # sum of the row lengths
         self._state = None
         self._tiles = {}
+        # slot rows of the tile plans in ascending slot order instead of list order (azb_tile_build_args.sort_rows)
+        self.sort_rows = os.environ.get("AZB_SORT_ROWS", "0") == "1"
 
     # consumers (pair forces) register so the list covers max r_cut per type pair, like hoomd's nlist subscribers
     def _subscribe(self, force):
@@ -57,17 +59,18 @@ class NeighborList:
             req = f._plan_request(nbar, require_built=False)
             if req["prune"] is not None and os.environ.get("AZB_FUSED_PRUNED", "1") != "1":
                 continue  # A/B switch: pruned views from the hash builder (tighter staged sets) instead of from the list build
-            key = (int(req["tile_size"]), 2048, int(req["lane_width"]), int(req["group_width"]), req["prune_key"])
+            key = (int(req["tile_size"]), 2048, int(req["lane_width"]), int(req["group_width"]), req["prune_key"], bool(req.get("sort_rows", False)))
             out[key] = req
         return out
 
-    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0, prune=None, prune_key=None):
+    def tile_plan(self, N, tile_size=128, uniq_capacity=2048, lane_width=1, group_width=0, prune=None, prune_key=None, sort_rows=False):
         """Tile plan of the current arrays (``azb_tiles_build``), built once per list rebuild and cached; ``None`` when a
         tile holds more than ``uniq_capacity`` distinct neighbours even at the smallest tile size. ``prune`` /
         ``prune_key``: see ``_nlist_gpu.build_tile_plan`` (a pruned plan is specific to the cutoffs of one force). ``lane_width`` is the
         slot-row layout: 1 for the DPD kernels, the lanes per particle for the pair kernels; ``group_width`` the lanes per
         particle of the kernel that walks the rows (bank rotation of the row order; 0 = ``lane_width``)."""
-        key = (int(tile_size), int(uniq_capacity), int(lane_width), int(group_width), prune_key)
+        sort_rows = bool(sort_rows) and int(group_width) == 0
+        key = (int(tile_size), int(uniq_capacity), int(lane_width), int(group_width), prune_key, sort_rows)
         if key not in self._tiles:
             from . import _nlist_gpu
 
@@ -76,28 +79,28 @@ class NeighborList:
             if prune is not None and int(group_width) == 0 and os.environ.get("AZB_NO_DERIVED_PLANS", "0") != "1":
                 # a pruned view is derived from the unpruned plan of the same list when some consumer needs that one anyway
                 # (azb_tile_build_args.base_plan: no second hash build)
-                base = self._unpruned_plan(N, ts, int(uniq_capacity))
+                base = self._unpruned_plan(N, ts, int(uniq_capacity), sort_rows)
                 if base is not None:
                     plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), 0, prune, base_plan=base)
             while plan is None and ts >= 32:
-                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width), prune)
+                plan = _nlist_gpu.build_tile_plan(self, N, ts, int(uniq_capacity), int(lane_width), int(group_width), prune, sort_rows=sort_rows)
                 ts //= 2
             self._tiles[key] = plan
         return self._tiles[key]
 
-    def _unpruned_plan(self, N, tile_size, uniq_capacity):
+    def _unpruned_plan(self, N, tile_size, uniq_capacity, sort_rows=False):
         """An unpruned, list-ordered plan of the current arrays with this tile size: one that is cached already, or the one
         another consumer of the list is going to ask for (built now). ``None`` when nobody needs one."""
         for key, plan in self._tiles.items():
             if plan is not None and key[0] == tile_size and key[1] == uniq_capacity and key[3] == 0 and key[4] is None \
-                    and plan.tile_size == tile_size and not plan.from_list_build:
+                    and plan.tile_size == tile_size and not plan.from_list_build and plan.sorted_rows == sort_rows:
                 return plan
         nbar = self.mean_neighbors(N)
         for f in self._consumers:
             if getattr(f, "_state", None) is None or not getattr(f, "use_tiles", False) or not getattr(f, "_tiled_kernels", False):
                 continue
             req = f._plan_request(nbar)
-            if req["prune"] is None and req["group_width"] == 0 and int(req["tile_size"]) == tile_size:
+            if req["prune"] is None and req["group_width"] == 0 and int(req["tile_size"]) == tile_size and bool(req.get("sort_rows", False)) == sort_rows:
                 plan = self.tile_plan(N, **req)
                 if plan is not None and plan.tile_size == tile_size:
                     return plan

@@ -393,6 +393,11 @@ typedef struct azb_tile_build_args
                                         then derived from it — every entry is tested against its staged neighbour through the base
                                         plan's 16-bit slot, the surviving slots are ranked by a scan — instead of hashed and sorted
                                         from the list again: same plan, a fraction of the cost (several forces on one list) */
+    unsigned int sort_rows;          /* 1 (group_width 0): every slot row holds its entries in ASCENDING slot order (= ascending particle
+                                        index) instead of list order. The pair set is unchanged; the lanes of neighbouring particles
+                                        then read neighbouring or identical staged positions at the same time, which removes most of
+                                        the shared-memory bank conflicts of the tile kernels' gathers. A view derived through
+                                        base_plan inherits the order of its base plan. */
     } azb_tile_build_args;
 
 AZB_API int azb_tiles_build(const azb_tile_build_args* args, unsigned int* h_max_uniq, unsigned int* h_max_slot_span, unsigned int* h_overflow,

@@ -20,13 +20,16 @@ def _list_on_device(n, rho, r_list, seed, shuffle=False):
     return hs, nl
 
 
-@pytest.mark.parametrize("rotate", [False, True])
+@pytest.mark.parametrize("rotate", [False, True, "sorted"])
 @pytest.mark.parametrize("lane_width", [1, 2, 4, 8, 16])
 @pytest.mark.parametrize("tile_size", [32, 64, 128, 256])
 def test_tile_plan_matches_numpy(tile_size, lane_width, rotate):
     n = 5000
     hs, nl = _list_on_device(n, 3.0, 1.4, 11)
-    plan = nl.tile_plan(n, tile_size, 2048, lane_width, group_width=lane_width if rotate else 0)
+    sort_rows = rotate == "sorted"  # slot rows in ascending slot order (azb_tile_build_args.sort_rows)
+    rotate = rotate is True
+    plan = nl.tile_plan(n, tile_size, 2048, lane_width, group_width=lane_width if rotate else 0, sort_rows=sort_rows)
+    assert plan.sorted_rows == sort_rows
     W, M = lane_width, 4 * lane_width
     A = max(M, 8)  # AZB_SLOT_ROW_ALIGN
     assert plan is not None and plan.tile_size == tile_size and plan.n_tiles == (n + tile_size - 1) // tile_size
@@ -47,6 +50,10 @@ def test_tile_plan_matches_numpy(tile_size, lane_width, rotate):
             r = e % M
             stored = slots[sh + (e - r) + 4 * (r % W) + r // W]  # entry e of the row in the lane-transposed layout
             assert np.all(stored[nn[i] :] == 0)  # padding
+            if sort_rows:
+                assert np.all(np.diff(stored[: nn[i]].astype(np.int64)) > 0)  # ascending slots, each neighbour exactly once
+                assert np.array_equal(want[stored[: nn[i]]], np.sort(lst[head[i] : head[i] + nn[i]]))
+                continue
             if not rotate:
                 assert np.array_equal(want[stored[: nn[i]]], lst[head[i] : head[i] + nn[i]])  # slot -> the listed neighbour, in order
                 continue
@@ -87,8 +94,9 @@ def test_tile_plan_is_rebuilt_with_the_list():
     assert nl.tile_plan(n, 128) is not p0
 
 
+@pytest.mark.parametrize("sort_rows", [False, True])
 @pytest.mark.parametrize("bits", [32, 64])
-def test_pruned_plan_gives_bit_identical_forces(bits):
+def test_pruned_plan_gives_bit_identical_forces(bits, sort_rows):
     """Two forces on one list (C5): the DPD force (r_cut 1.0) walks a view of the list (built for 2.0 + 0.4) without the entries
     that were beyond r_cut + buffer when the list was built. Same pair set inside the cutoff, same order, so the forces must
     equal the unpruned plan's bit for bit — also after every particle has moved by up to buffer / 2."""
@@ -99,6 +107,7 @@ def test_pruned_plan_gives_bit_identical_forces(bits):
     snap = W.yukawa_dpd_fluid(n=20000, seed=21, jitter=0.15)
     st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
     cell = nlist.Cell(buffer=0.4)
+    cell.sort_rows = sort_rows  # (slot rows in ascending slot order: the pruned view keeps the relative order of its base plan)
     forces = []
     for prune in (True, False):
         d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
@@ -159,6 +168,7 @@ def test_plans_emitted_by_the_list_build(bits, periodic):
     st = az.State(snap, device="cuda", scalar_bits=bits, seed=42)
     cell = nlist.Cell(buffer=0.4)
     cell.fused_plans = True  # opt-in (off by default: see nlist.NeighborList.plan_requests)
+    cell.sort_rows = False  # the plans the list build emits are in list order: compare with hash plans in list order
     d = pair.DPDGeneralWeight(nlist=cell, kT=1.0, default_r_cut=1.0)
     d.dt = 0.01
     d.params[("A", "A")] = W.C5_DPD_PARAMS[("A", "A")]
