@@ -1,4 +1,6 @@
 // DPD thermostat launcher (float and double; virial on/off; tpp 1..32; direct or tile-staged neighbour data).
+#include <cstdlib>
+
 #include "azb_dpd_kernel.cuh"
 #include "azb_launch.cuh"
 
@@ -48,6 +50,35 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
             LAUNCH(TPP, false, false);     \
         } while (0)
 
+    // lane-private stacks instead of the shared ring (dpd_stack_tile_kernel): AZB_DPD_STACK = lanes per particle (1, 2 or 4)
+    static const char* stack_env = getenv("AZB_DPD_STACK");
+    const unsigned int stack_tpp = (stack_env && a.pair.threads_per_particle == 0) ? (unsigned int)atoi(stack_env) : 0u;
+    if (a.pair.tiles && (stack_tpp == 1u || stack_tpp == 2u || stack_tpp == 4u))
+        {
+        TilePlanDev plan;
+        unsigned int block = 0, grid = 0;
+        const int bad = make_tile_plan(a.pair, stack_tpp, 1u, plan, block, grid);
+        if (bad)
+            return bad;
+        const size_t smem = (size_t)plan.smem_uniq * (2 * sizeof(V4) + sizeof(unsigned int)) + T2 * sizeof(coeff_t)
+                            + (size_t)DPD_STACK_CAP * block * sizeof(uint16_t);
+        if (smem > AZB_MAX_SMEM)
+            return AZB_ERR_BAD_ARGUMENT;
+#define AZB_LAUNCH_S(TPP, FB, SG)                                                                                                 \
+    do                                                                                                                            \
+        {                                                                                                                         \
+        if (const int e_ = ensure_smem<dpd_stack_tile_kernel<S, VIRIAL, TPP, FB, SG>>(smem)) return e_;                           \
+        dpd_stack_tile_kernel<S, VIRIAL, TPP, FB, SG><<<grid, block, smem, stream>>>(d, plan, (const param_t*)d_params, wrap_sq);  \
+        } while (0)
+        if (stack_tpp == 1u)
+            AZB_BY_FLAVOUR(AZB_LAUNCH_S, 1);
+        else if (stack_tpp == 2u)
+            AZB_BY_FLAVOUR(AZB_LAUNCH_S, 2);
+        else
+            AZB_BY_FLAVOUR(AZB_LAUNCH_S, 4);
+#undef AZB_LAUNCH_S
+        return (int)cudaGetLastError();
+        }
     if (a.pair.tiles)
         {
         TilePlanDev plan;

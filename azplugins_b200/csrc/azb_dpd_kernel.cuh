@@ -485,4 +485,168 @@ __global__ void AZB_DPD_TILE_BOUNDS
             acc.store(a, idx);
         }
     }
+
+// ---- tile kernel with a PRIVATE in-range stack per lane (no ring, no votes) -----------------------------------------------------
+// The ring walk above shares a queue between the TPP lanes of a particle and pays for it per visit: two ballots, popc ranks, a
+// warp-wide readiness vote, a warp-wide max, a __syncwarp. With the neighbour data in shared memory nothing is gained from several
+// lanes reading consecutive list entries, so here every lane walks its own share of the row (entries lane, lane + TPP, ...; TPP = 1:
+// the whole row) in plain SIMT: light — four entries at a time, cutoff test, in-range slots pushed (16 bits each) onto the lane's own
+// stack in shared memory; heavy — the lane drains its stack, re-reading the neighbour's staged position (cheaper than carrying the
+// separation through the stack). The warp reconverges after each phase, so a phase costs its longest lane; there is no other
+// coupling between lanes. A lane's pairs are summed in list order, the TPP partial sums by shuffle.
+constexpr unsigned int DPD_STACK_CAP = 16u; // in-range entries per lane between two drains
+
+template<class S, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
+__global__ void __launch_bounds__(256)
+    dpd_stack_tile_kernel(const DPDArgsDev<S> d, const TilePlanDev plan, const DPDThermo::Params<S>* __restrict__ params, const S wrap_sq)
+    {
+    typedef DPDThermo::Coeff<S> coeff_t;
+    typedef typename vec4<S>::type V4;
+    const PairArgsDev<S>& a = d.pair;
+    extern __shared__ __align__(32) unsigned char smem_raw[];
+    const unsigned int T2 = a.ntypes * a.ntypes;
+    const unsigned int groups = blockDim.x / TPP;
+    const unsigned int gid = threadIdx.x / TPP;
+    const unsigned int lane = threadIdx.x % TPP;
+    V4* s_pos = reinterpret_cast<V4*>(smem_raw);
+    V4* s_vel = s_pos + plan.smem_uniq;
+    coeff_t* s_coeff = reinterpret_cast<coeff_t*>(s_vel + plan.smem_uniq);
+    unsigned int* s_tag = reinterpret_cast<unsigned int*>(s_coeff + T2);
+    uint16_t* s_stack = reinterpret_cast<uint16_t*>(s_tag + plan.smem_uniq); // [DPD_STACK_CAP][blockDim.x]
+
+    const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
+    const unsigned int U = __ldg(plan.uniq_count + tile);
+    const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
+    for (unsigned int p = threadIdx.x; p < plan.tile_size; p += blockDim.x)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        if (idx < a.N)
+            {
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const char* r = reinterpret_cast<const char*>(plan.slots + slot_row_begin(plan, a.head_list, idx, 1));
+            for (unsigned int off = 0; off < nn * 2u; off += 128u)
+                prefetch_l2(r + off);
+            if (p % 8u == 0u)
+                {
+                prefetch_l2(a.pos + idx);
+                prefetch_l2(d.vel + idx);
+                }
+            if (p % 32u == 0u)
+                prefetch_l2(d.tag + idx);
+            }
+        }
+    for (unsigned int s0 = threadIdx.x; s0 < U; s0 += 4 * blockDim.x)
+        {
+        unsigned int g[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            g[u] = (s0 + u * blockDim.x < U) ? __ldg(uq + s0 + u * blockDim.x) : 0xffffffffu;
+        V4 pv[4], vv[4];
+        unsigned int tv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                pv[u] = ld4(a.pos + g[u]);
+                vv[u] = ld4(d.vel + g[u]);
+                tv[u] = __ldg(d.tag + g[u]);
+                }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g[u] != 0xffffffffu)
+                {
+                const unsigned int s = s0 + u * blockDim.x;
+                s_pos[s] = pv[u];
+                s_vel[s] = vv[u];
+                s_tag[s] = tv[u];
+                }
+        }
+    for (unsigned int t = threadIdx.x; t < T2; t += blockDim.x)
+        s_coeff[t] = DPDThermo::make(params[t], a.rcutsq[t], d.deltaT, d.T);
+    __syncthreads();
+    const coeff_t c0 = s_coeff[0];
+    const unsigned int pos_addr = smem_addr(s_pos), vel_addr = smem_addr(s_vel), tag_addr = smem_addr(s_tag);
+    const unsigned int coeff_addr = smem_addr(s_coeff);
+    uint16_t* stack = s_stack + threadIdx.x; // entry q at stack[q * blockDim.x]
+    const unsigned int sstride = blockDim.x;
+
+    for (unsigned int p = gid; p < plan.tile_size; p += groups)
+        {
+        const unsigned int idx = tile * plan.tile_size + p;
+        const bool active = idx < a.N;
+        PairAccum<S, VIRIAL> acc;
+        if (active)
+            {
+            const unsigned int nn = __ldg(a.n_neigh + idx);
+            const uint16_t* row = plan.slots + slot_row_begin(plan, a.head_list, idx, 1);
+            const V4 pi = ld4(a.pos + idx);
+            const V4 vi = ld4(d.vel + idx);
+            const unsigned int tag_i = __ldg(d.tag + idx);
+            const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
+            unsigned int k = lane, cnt = 0;
+            for (;;)
+                {
+                // ---- light: four of my entries per pass
+                while (k < nn && cnt + 4u <= DPD_STACK_CAP)
+                    {
+                    unsigned int sl[4];
+                    bool have[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        {
+                        have[u] = k + u * TPP < nn;
+                        sl[u] = have[u] ? (unsigned int)__ldg(row + k + u * TPP) : 0u;
+                        }
+                    bool in[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        {
+                        const V4 pj = lds4(pos_addr, sl[u], S());
+                        S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                        S rc = c0.rcutsq;
+                        if (!SINGLE)
+                            rc = lds_scalar(coeff_addr + (trow + type_of(pj.w)) * (unsigned int)sizeof(coeff_t) + 7u * (unsigned int)sizeof(S), S());
+                        in[u] = have[u] & (separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz) < rc);
+                        }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (in[u])
+                            {
+                            stack[cnt * sstride] = (uint16_t)sl[u];
+                            ++cnt;
+                            }
+                    k += 4u * TPP;
+                    }
+                // ---- heavy: drain my stack
+                for (unsigned int q = 0; q < cnt; ++q)
+                    {
+                    const unsigned int jj = stack[q * sstride];
+                    const V4 pj = lds4(pos_addr, jj, S());
+                    S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                    separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
+                    const V4 e = pack_entry<S>(dx, dy, dz, 0u);
+                    const V4 vj = lds4(vel_addr, jj, S());
+                    const unsigned int tag_j = lds32_at(tag_addr + jj * 4u);
+                    if (SINGLE)
+                        dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c0, d.rk, acc);
+                    else
+                        {
+                        const unsigned int ca = coeff_addr + (trow + type_of(pj.w)) * (unsigned int)sizeof(coeff_t);
+                        const V4 c_lo = lds4_at(ca, S()), c_hi = lds4_at(ca + (unsigned int)sizeof(V4), S());
+                        coeff_t c;
+                        c.A = c_lo.x, c.gamma = c_lo.y, c.sigma = c_lo.z, c.rcutinv = c_lo.w;
+                        c.rcut = c_hi.x, c.half_s = c_hi.y, c.hA = c_hi.z, c.rcutsq = c_hi.w;
+                        dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c, d.rk, acc);
+                        }
+                    }
+                cnt = 0;
+                if (k >= nn)
+                    break;
+                }
+            }
+        acc.template reduce<TPP>();
+        if (active && lane == 0)
+            acc.store(a, idx);
+        }
+    }
     } // namespace azb

@@ -2,8 +2,9 @@
 
 * C1 as BASELINE.json states it — PerturbedLennardJones fluid, NVE, dt = 0.005: the GPU trajectory (GPU integrator, GPU
   forces, GPU list rebuilds) against an oracle trajectory (numpy velocity Verlet in the same order of operations + oracle
-  forces on a list rebuilt every step) in double, positions and forces compared at steps {1, 10, 100, 200} — a short
-  horizon because an MD trajectory amplifies rounding differences exponentially (Lyapunov time ~ 1 tau = 200 steps).
+  forces on a list rebuilt every step) in double, positions and forces compared at steps {1, 10, 100, 200} for N = 4000 and at
+  {1, 10, 100, 1000} for the full 32 000 particles (an MD trajectory amplifies rounding differences exponentially, Lyapunov
+  time ~ 1 tau = 200 steps: the bound widens with the step count).
 * C1 at full size (N = 32 000, 1000 steps, float): size-independent invariants — total energy and linear momentum conserved,
   list rebuilt on the way.
 * The reference's one statistical DPD test replayed (/root/reference/src/pytest/test_pair_dpd.py:12-49): N = 1000 lattice,
@@ -33,16 +34,20 @@ def _wrap(pos, L):
     return np.where(pos < -L / 2, pos + L, pos)
 
 
-def test_nve_trajectory_matches_oracle():
+@pytest.mark.parametrize("m,marks,slack", [(10, (1, 10, 100, 200), 1.0), (20, (1, 10, 100, 1000), 5.0)])
+def test_nve_trajectory_matches_oracle(m, marks, slack):
+    """m = 10: N = 4000, 200 steps. m = 20: C1 as BASELINE.json states it — 32 000 particles, 1000 NVE steps, parity at steps
+    {1, 10, 100, 1000}; over five Lyapunov times rounding differences grow to ~1e-7 (the same growth the 1-GPU / 8-GPU
+    trajectories show, profiles/r2_mgpu_md_check_8gpu.log), hence the wider bound."""
     import azplugins_b200 as az
     from azplugins_b200 import md, nlist, pair, workloads
 
     # jitter 0.05 a, not the 0.15 a of the force benchmarks: at 0.15 a some pairs start at r ~ 0.4 sigma (|F| ~ 1e5) and no
     # integrator survives that at dt = 0.005 — the oracle's trajectory blows up the same way
-    snap = workloads.lj_fluid(m=10, jitter=0.05)  # N = 4000, box 17.1
+    snap = workloads.lj_fluid(m=m, jitter=0.05)  # N = 4000 (box 17.1) / 32 000
     snap.velocity -= snap.velocity.mean(axis=0)
     params = workloads.PLJ_PARAMS[("A", "A")]
-    dt, rc, buffer, steps, marks = 0.005, 3.0, 0.4, 200, (1, 10, 100, 200)
+    dt, rc, buffer, steps = 0.005, 3.0, 0.4, marks[-1]
     L = snap.box.Lx
 
     st = az.State(snap, device="cuda", scalar_bits=64)
@@ -69,13 +74,15 @@ def test_nve_trajectory_matches_oracle():
         gv = st.vel[:, :3].cpu().numpy()
         d = gx - x
         d -= L * np.rint(d / L)  # a particle on the boundary may sit on either side
-        assert np.abs(d).max() < 1e-9 * (1 + mark), (mark, np.abs(d).max())
-        assert np.abs(gv - v).max() < 1e-8 * (1 + mark), (mark, np.abs(gv - v).max())
+        print(f"NVE parity N={snap.N} step {mark}: max|dx|={np.abs(d).max():.3e} max|dv|={np.abs(gv - v).max():.3e} "
+              f"max|df|={np.abs(ig._net.cpu().numpy()[:, :3] - f[:, :3]).max():.3e} (max|f|={np.abs(f[:, :3]).max():.3e})")
+        assert np.abs(d).max() < slack * 1e-9 * (1 + mark), (mark, np.abs(d).max())
+        assert np.abs(gv - v).max() < slack * 1e-8 * (1 + mark), (mark, np.abs(gv - v).max())
         # forces on the oracle's snapshot of this step
-        np.testing.assert_allclose(ig._net.cpu().numpy()[:, :3], f[:, :3], rtol=0, atol=1e-6 * (1 + mark) * np.abs(f[:, :3]).max() / 100)
+        np.testing.assert_allclose(ig._net.cpu().numpy()[:, :3], f[:, :3], rtol=0, atol=slack * 1e-6 * (1 + mark) * np.abs(f[:, :3]).max() / 100)
         assert abs(ig.potential_energy - f[:, 3].sum()) <= 1e-8 * abs(f[:, 3].sum()) * (1 + mark)
     assert ig.timestep == steps
-    assert ig.nlist_rebuilds >= 1  # buffer / 2 = 0.2 is crossed within 200 steps at kT ~ 1
+    assert ig.nlist_rebuilds >= (1 if steps <= 200 else 20)  # buffer / 2 = 0.2 is crossed within 200 steps at kT ~ 1
     assert np.abs(st.image.cpu().numpy()).max() <= 1
 
 
