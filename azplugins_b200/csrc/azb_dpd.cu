@@ -50,9 +50,17 @@ template<class S, bool VIRIAL> static int launch_dpd_variant(const azb_dpd_args&
             LAUNCH(TPP, false, false);     \
         } while (0)
 
-    // lane-private stacks instead of the shared ring (dpd_stack_tile_kernel): AZB_DPD_STACK = lanes per particle (1, 2 or 4)
+    // Tile kernels, lanes per particle left to the engine: lane-private stacks (dpd_stack_tile_kernel) for short and medium rows —
+    // one lane per particle up to 20 entries per row (C5's pruned view: 0.726 -> 0.537 ms), two up to 64 (C2: 0.221 -> 0.204 ms) —
+    // and the shared-ring walk beyond. AZB_DPD_STACK = 1 | 2 | 4 forces a stack width, 0 the ring (A/B).
     static const char* stack_env = getenv("AZB_DPD_STACK");
-    const unsigned int stack_tpp = (stack_env && a.pair.threads_per_particle == 0) ? (unsigned int)atoi(stack_env) : 0u;
+    unsigned int stack_tpp = 0u;
+    if (a.pair.tiles && a.pair.threads_per_particle == 0)
+        {
+        const size_t entries = a.pair.tiles->n_entries ? a.pair.tiles->n_entries : a.pair.size_nlist;
+        const double nbar = a.pair.N ? (double)entries / (double)a.pair.N : 0.0;
+        stack_tpp = stack_env ? (unsigned int)atoi(stack_env) : (nbar <= 20.0 ? 1u : (nbar <= 64.0 ? 2u : 0u));
+        }
     if (a.pair.tiles && (stack_tpp == 1u || stack_tpp == 2u || stack_tpp == 4u))
         {
         TilePlanDev plan;

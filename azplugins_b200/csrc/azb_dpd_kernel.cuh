@@ -583,20 +583,36 @@ __global__ void __launch_bounds__(256)
             const V4 vi = ld4(d.vel + idx);
             const unsigned int tag_i = __ldg(d.tag + idx);
             const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
-            unsigned int k = lane, cnt = 0;
+            // my entries: blocks of four consecutive list entries (one 8-byte load: slot rows start 16-byte aligned and are
+            // padded to a multiple of four), block b of lane l starting at entry 4 (b TPP + l)
+            unsigned int k = 4u * lane, cnt = 0;
+            auto eval = [&](const unsigned int jj)
+            {
+                const V4 pj = lds4(pos_addr, jj, S());
+                S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
+                const V4 e = pack_entry<S>(dx, dy, dz, 0u);
+                const V4 vj = lds4(vel_addr, jj, S());
+                const unsigned int tag_j = lds32_at(tag_addr + jj * 4u);
+                if (SINGLE)
+                    dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c0, d.rk, acc);
+                else
+                    {
+                    const unsigned int ca = coeff_addr + (trow + type_of(pj.w)) * (unsigned int)sizeof(coeff_t);
+                    const V4 c_lo = lds4_at(ca, S()), c_hi = lds4_at(ca + (unsigned int)sizeof(V4), S());
+                    coeff_t c;
+                    c.A = c_lo.x, c.gamma = c_lo.y, c.sigma = c_lo.z, c.rcutinv = c_lo.w;
+                    c.rcut = c_hi.x, c.half_s = c_hi.y, c.hA = c_hi.z, c.rcutsq = c_hi.w;
+                    dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c, d.rk, acc);
+                    }
+            };
             for (;;)
                 {
                 // ---- light: four of my entries per pass
                 while (k < nn && cnt + 4u <= DPD_STACK_CAP)
                     {
-                    unsigned int sl[4];
-                    bool have[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        {
-                        have[u] = k + u * TPP < nn;
-                        sl[u] = have[u] ? (unsigned int)__ldg(row + k + u * TPP) : 0u;
-                        }
+                    const uint2 pk = __ldg(reinterpret_cast<const uint2*>(row + k));
+                    const unsigned int sl[4] = {pk.x & 0xffffu, pk.x >> 16, pk.y & 0xffffu, pk.y >> 16};
                     bool in[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
@@ -606,7 +622,7 @@ __global__ void __launch_bounds__(256)
                         S rc = c0.rcutsq;
                         if (!SINGLE)
                             rc = lds_scalar(coeff_addr + (trow + type_of(pj.w)) * (unsigned int)sizeof(coeff_t) + 7u * (unsigned int)sizeof(S), S());
-                        in[u] = have[u] & (separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz) < rc);
+                        in[u] = (k + u < nn) & (separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz) < rc);
                         }
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
@@ -617,28 +633,16 @@ __global__ void __launch_bounds__(256)
                             }
                     k += 4u * TPP;
                     }
-                // ---- heavy: drain my stack
-                for (unsigned int q = 0; q < cnt; ++q)
+                // ---- heavy: drain my stack, two pairs per pass (two independent Philox chains in flight)
+                unsigned int q = 0;
+                for (; q + 2u <= cnt; q += 2u)
                     {
-                    const unsigned int jj = stack[q * sstride];
-                    const V4 pj = lds4(pos_addr, jj, S());
-                    S dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                    separation<FASTBOX>(a.box, wrap_sq, dx, dy, dz);
-                    const V4 e = pack_entry<S>(dx, dy, dz, 0u);
-                    const V4 vj = lds4(vel_addr, jj, S());
-                    const unsigned int tag_j = lds32_at(tag_addr + jj * 4u);
-                    if (SINGLE)
-                        dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c0, d.rk, acc);
-                    else
-                        {
-                        const unsigned int ca = coeff_addr + (trow + type_of(pj.w)) * (unsigned int)sizeof(coeff_t);
-                        const V4 c_lo = lds4_at(ca, S()), c_hi = lds4_at(ca + (unsigned int)sizeof(V4), S());
-                        coeff_t c;
-                        c.A = c_lo.x, c.gamma = c_lo.y, c.sigma = c_lo.z, c.rcutinv = c_lo.w;
-                        c.rcut = c_hi.x, c.half_s = c_hi.y, c.hA = c_hi.z, c.rcutsq = c_hi.w;
-                        dpd_pair<S, VIRIAL>(e, vi, vj, tag_i, tag_j, c, d.rk, acc);
-                        }
+                    const unsigned int ja = stack[q * sstride], jb = stack[(q + 1u) * sstride];
+                    eval(ja);
+                    eval(jb);
                     }
+                if (q < cnt)
+                    eval(stack[q * sstride]);
                 cnt = 0;
                 if (k >= nn)
                     break;
