@@ -517,24 +517,54 @@ __global__ void __launch_bounds__(256)
     const unsigned int tile = plan.tile_order ? __ldg(plan.tile_order + plan.tile_begin + blockIdx.x) : plan.tile_begin + blockIdx.x;
     const unsigned int U = __ldg(plan.uniq_count + tile);
     const unsigned int* uq = plan.uniq + (size_t)tile * plan.uniq_capacity;
-    for (unsigned int p = threadIdx.x; p < plan.tile_size; p += blockDim.x)
-        {
+    // The group's first particle (the only one when blockDim / TPP == tile_size, the default): its row header, own position /
+    // velocity / tag and its first slot packet do not depend on the staged tile — their memory round trips are started here and
+    // hide behind the staging gather. The rest of a longer row is warmed in L2.
+    unsigned int nn_next = 0, tag_next = 0;
+    const uint16_t* row_next = plan.slots;
+    V4 pi_next = pack_entry<S>(S(0), S(0), S(0), 0u), vi_next = pi_next;
+    uint2 pk_next = make_uint2(0u, 0u);
+    auto load_header = [&](const unsigned int p)
+    {
         const unsigned int idx = tile * plan.tile_size + p;
-        if (idx < a.N)
+        nn_next = 0;
+        if (p < plan.tile_size && idx < a.N)
             {
-            const unsigned int nn = __ldg(a.n_neigh + idx);
-            const char* r = reinterpret_cast<const char*>(plan.slots + slot_row_begin(plan, a.head_list, idx, 1));
-            for (unsigned int off = 0; off < nn * 2u; off += 128u)
-                prefetch_l2(r + off);
-            if (p % 8u == 0u)
-                {
-                prefetch_l2(a.pos + idx);
-                prefetch_l2(d.vel + idx);
-                }
-            if (p % 32u == 0u)
-                prefetch_l2(d.tag + idx);
+            nn_next = __ldg(a.n_neigh + idx);
+            row_next = plan.slots + slot_row_begin(plan, a.head_list, idx, 1);
+            pi_next = ld4(a.pos + idx);
+            vi_next = ld4(d.vel + idx);
+            tag_next = __ldg(d.tag + idx);
+            if (4u * lane < nn_next)
+                pk_next = __ldg(reinterpret_cast<const uint2*>(row_next + 4u * lane));
+            if (lane == 0)
+                for (unsigned int off = 128u; off < nn_next * 2u; off += 128u)
+                    prefetch_l2(reinterpret_cast<const char*>(row_next) + off);
             }
-        }
+    };
+    // (one lane per particle only: with more lanes the extra live registers cost a resident CTA — C2 0.204 -> 0.228 ms)
+    constexpr bool HOIST = TPP == 1;
+    if (HOIST)
+        load_header(gid);
+    else
+        for (unsigned int p = threadIdx.x; p < plan.tile_size; p += blockDim.x)
+            {
+            const unsigned int idx = tile * plan.tile_size + p;
+            if (idx < a.N)
+                {
+                const unsigned int nn = __ldg(a.n_neigh + idx);
+                const char* r = reinterpret_cast<const char*>(plan.slots + slot_row_begin(plan, a.head_list, idx, 1));
+                for (unsigned int off = 0; off < nn * 2u; off += 128u)
+                    prefetch_l2(r + off);
+                if (p % 8u == 0u)
+                    {
+                    prefetch_l2(a.pos + idx);
+                    prefetch_l2(d.vel + idx);
+                    }
+                if (p % 32u == 0u)
+                    prefetch_l2(d.tag + idx);
+                }
+            }
     for (unsigned int s0 = threadIdx.x; s0 < U; s0 += 4 * blockDim.x)
         {
         unsigned int g[4];
@@ -575,13 +605,16 @@ __global__ void __launch_bounds__(256)
         const unsigned int idx = tile * plan.tile_size + p;
         const bool active = idx < a.N;
         PairAccum<S, VIRIAL> acc;
+        if (!HOIST)
+            load_header(p);
         if (active)
             {
-            const unsigned int nn = __ldg(a.n_neigh + idx);
-            const uint16_t* row = plan.slots + slot_row_begin(plan, a.head_list, idx, 1);
-            const V4 pi = ld4(a.pos + idx);
-            const V4 vi = ld4(d.vel + idx);
-            const unsigned int tag_i = __ldg(d.tag + idx);
+            const unsigned int nn = nn_next;
+            const uint16_t* row = row_next;
+            const V4 pi = pi_next;
+            const V4 vi = vi_next;
+            const unsigned int tag_i = tag_next;
+            uint2 pk = pk_next;
             const unsigned int trow = SINGLE ? 0u : type_of(pi.w) * a.ntypes;
             // my entries: blocks of four consecutive list entries (one 8-byte load: slot rows start 16-byte aligned and are
             // padded to a multiple of four), block b of lane l starting at entry 4 (b TPP + l)
@@ -611,8 +644,9 @@ __global__ void __launch_bounds__(256)
                 // ---- light: four of my entries per pass
                 while (k < nn && cnt + 4u <= DPD_STACK_CAP)
                     {
-                    const uint2 pk = __ldg(reinterpret_cast<const uint2*>(row + k));
                     const unsigned int sl[4] = {pk.x & 0xffffu, pk.x >> 16, pk.y & 0xffffu, pk.y >> 16};
+                    if (k + 4u * TPP < nn) // my next block, one pass ahead
+                        pk = __ldg(reinterpret_cast<const uint2*>(row + k + 4u * TPP));
                     bool in[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
@@ -651,6 +685,8 @@ __global__ void __launch_bounds__(256)
         acc.template reduce<TPP>();
         if (active && lane == 0)
             acc.store(a, idx);
+        if (HOIST && p + groups < plan.tile_size)
+            load_header(p + groups); // (more particles than groups: not the default launch shape)
         }
     }
     } // namespace azb
