@@ -10,10 +10,13 @@
 // A policy `PK` supplies the per-pair math on pairs of entries:
 //   typedef Pot;                          the potential (Params / Coeff / make / active)
 //   struct K;  static K consts(coeff)     packed constants
-//   static void eval2(K, rsq2, rinv2, f2&, u2&)   force / r and pair energy (unshifted) of two entries; rsq2 is inside the cutoff
+//   static void eval2(K, rsq2, inA, inB, f2&, u2&)   force / r and pair energy (unshifted) of two entries, multiplied by the
+//                                                    entries' 0 / 1 masks (inA, inB); rsq2 is finite and positive
+//   static bool finite_beyond_cutoff(coeff, rcutsq)   eval2 is finite (no inf, no NaN) for every r^2 >= rcutsq
 #pragma once
 #include "azb_pair_kernel.cuh"
 #include "azb_pair_potentials.cuh"
+#include <type_traits>
 
 namespace azb
     {
@@ -29,26 +32,46 @@ struct PackedExpandedYukawa
     typedef ExpandedYukawa Pot;
     struct K
         {
-        float2 mdelta, mkappa, kappa, eps;
+        float2 mdelta, mkl2e, kappa;
+        float eps;
         };
+    // The kernel is bound by the FMA pipe (an FFMA2 holds it for two cycles: tools/microbench/mufu.cu; 84 % busy in the capture
+    // of the first version), so what counts is the number of FP32 operations per entry, packed or not:
+    //  * exp(-kappa (r - delta)) = ex2((r - delta) * (-kappa log2 e)) with the constant folded once per thread — HOOMD's own
+    //    fast::exp on the GPU is __expf, the same single MUFU.EX2 on a rounded product. The argument's rounding error,
+    //    |t| 6e-8 relative on the exponential, is below one float ulp of the pair force for |t| < 1 and always far below the
+    //    1e-5 parity tolerance (a pair with |t| >> 1 contributes e^-|t| of the particle's force). exp_'s two-term correction
+    //    (five more FP32 operations per entry) is left to the generic kernel;
+    //  * epsilon rides on the 0 / 1 cutoff mask (a select on the ALU pipe instead of a multiplication), and the mask is
+    //    applied once, to u: the force inherits it.
     __device__ __forceinline__ static K consts(const ExpandedYukawa::Coeff<float>& c)
         {
         K k;
+        const float kl = (float)(-(double)c.kappa * 1.4426950408889634);
         k.mdelta = pk2(-c.delta, -c.delta);
-        k.mkappa = pk2(-c.kappa, -c.kappa);
+        k.mkl2e = pk2(kl, kl);
         k.kappa = pk2(c.kappa, c.kappa);
-        k.eps = pk2(c.epsilon, c.epsilon);
+        k.eps = c.epsilon;
         return k;
         }
-    __device__ __forceinline__ static void eval2(const K& k, const float2 rsq, float2& f, float2& u)
+    // eval2 stays finite for every r^2 >= r_cut^2 when delta < r_cut (r - delta > 0, the exponential only underflows): a listed
+    // entry beyond the cutoff can then be evaluated where it is and multiplied by the zero mask, without the r_cut substitute
+    __device__ __forceinline__ static bool finite_beyond_cutoff(const ExpandedYukawa::Coeff<float>& c, const float rcutsq)
+        {
+        return c.delta >= 0.0f && c.delta * c.delta < rcutsq;
+        }
+    // f = force / r and u = pair energy (unshifted) of two entries, both already multiplied by the entries' masks
+    __device__ __forceinline__ static void eval2(const K& k, const float2 rsq, const bool inA, const bool inB, float2& f, float2& u)
         {
         const float2 rinv = pk2(rsqrt_(rsq.x), rsqrt_(rsq.y));
-        const float2 r = __fmul2_rn(rsq, rinv);
-        const float2 rd = __fadd2_rn(r, k.mdelta);
+        const float2 rd = __ffma2_rn(rsq, rinv, k.mdelta);
         const float2 rdinv = pk2(rcp(rd.x), rcp(rd.y));
-        const float2 arg = __fmul2_rn(rd, k.mkappa);
-        const float2 ex = pk2(exp_(arg.x), exp_(arg.y));
-        u = __fmul2_rn(__fmul2_rn(k.eps, ex), rdinv);
+        const float2 t = __fmul2_rn(rd, k.mkl2e);
+        float ea, eb;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ea) : "f"(t.x));
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(eb) : "f"(t.y));
+        const float2 em = pk2(inA ? k.eps : 0.0f, inB ? k.eps : 0.0f);
+        u = __fmul2_rn(__fmul2_rn(pk2(ea, eb), rdinv), em);
         f = __fmul2_rn(__fmul2_rn(u, __fadd2_rn(k.kappa, rdinv)), rinv);
         }
     };
@@ -96,6 +119,9 @@ __global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgs
     const typename Pot::template Coeff<float> c = Pot::make(params[0], rc, SHIFT == 1);
     const float rc0 = Pot::active(c) ? rc : -1.0f; // an inactive pair (vanishing prefactor) never passes the cutoff test
     const float r_safe = rc > 0.0f ? rc : 1.0f;    // where masked-out entries are evaluated: any finite, harmless distance
+    const bool no_subst = rc0 > 0.0f && PK::finite_beyond_cutoff(c, rc);
+    typedef std::integral_constant<bool, true> true_c;
+    typedef std::integral_constant<bool, false> false_c;
     const typename PK::K k = PK::consts(c);
     const float e_shift = SHIFT == 1 ? c.e_shift : 0.0f;
     __syncthreads();
@@ -114,8 +140,11 @@ __global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgs
             const float4 pi = pi_next;
             const float2 pix = pk2(pi.x, pi.x), piy = pk2(pi.y, pi.y), piz = pk2(pi.z, pi.z);
 
-            auto visit2 = [&](const unsigned int sA, const unsigned int sB, const bool vA, const bool vB)
+            // SUBST: entries that do not count are evaluated at r_safe; without it (full blocks of a potential that is finite
+            // beyond the cutoff: every entry is a real list entry, r > 0) they are evaluated where they are — four selects less
+            auto visit2 = [&](const unsigned int sA, const unsigned int sB, const bool vA, const bool vB, auto subst)
             {
+                constexpr bool SUBST = decltype(subst)::value;
                 const float4 pA = lds4(pos_base, sA, float()), pB = lds4(pos_base, sB, float());
                 float2 dx = __ffma2_rn(pk2(pA.x, pB.x), kminus1, pix);
                 float2 dy = __ffma2_rn(pk2(pA.y, pB.y), kminus1, piy);
@@ -136,14 +165,12 @@ __global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgs
                     }
                 // entries that do not count (beyond the cutoff, padding) are evaluated at r_cut and masked to zero
                 const bool inA = vA & (rsq.x < rc0), inB = vB & (rsq.y < rc0);
-                const float2 rq = pk2(inA ? rsq.x : r_safe, inB ? rsq.y : r_safe);
-                const float2 m = pk2(inA ? 1.0f : 0.0f, inB ? 1.0f : 0.0f);
+                const float2 rq = SUBST ? pk2(inA ? rsq.x : r_safe, inB ? rsq.y : r_safe) : rsq;
                 float2 f, u;
-                PK::eval2(k, rq, f, u);
-                f = __fmul2_rn(f, m);
+                PK::eval2(k, rq, inA, inB, f, u);
+                pe = __fadd2_rn(pe, u);
                 if (SHIFT == 1)
-                    u = __fadd2_rn(u, pk2(-e_shift, -e_shift));
-                pe = __ffma2_rn(u, m, pe);
+                    pe = __fadd2_rn(pe, pk2(inA ? -e_shift : 0.0f, inB ? -e_shift : 0.0f));
                 fx = __ffma2_rn(dx, f, fx);
                 fy = __ffma2_rn(dy, f, fy);
                 fz = __ffma2_rn(dz, f, fz);
@@ -163,19 +190,29 @@ __global__ void __launch_bounds__(128, 8) packed_pair_tile_kernel(const PairArgs
             const unsigned int nblk = (nn + M - 1u) / M;
             uint2 next = pkt_next;
             load_header(p + groups); // the group's next particle, if the tile has more particles than the CTA has groups
-            for (unsigned int b = 0; b < full; ++b)
-                {
-                const uint2 s4 = next;
-                if (b + 1 < nblk)
-                    next = __ldg(row + (b + 1) * TPP);
-                visit2(s4.x & 0xffffu, s4.x >> 16, true, true);
-                visit2(s4.y & 0xffffu, s4.y >> 16, true, true);
-                }
+            if (no_subst)
+                for (unsigned int b = 0; b < full; ++b)
+                    {
+                    const uint2 s4 = next;
+                    if (b + 1 < nblk)
+                        next = __ldg(row + (b + 1) * TPP);
+                    visit2(s4.x & 0xffffu, s4.x >> 16, true, true, false_c());
+                    visit2(s4.y & 0xffffu, s4.y >> 16, true, true, false_c());
+                    }
+            else
+                for (unsigned int b = 0; b < full; ++b)
+                    {
+                    const uint2 s4 = next;
+                    if (b + 1 < nblk)
+                        next = __ldg(row + (b + 1) * TPP);
+                    visit2(s4.x & 0xffffu, s4.x >> 16, true, true, true_c());
+                    visit2(s4.y & 0xffffu, s4.y >> 16, true, true, true_c());
+                    }
             if (full < nblk) // the ragged last block: padding slots are 0 (a valid address) and masked out
                 {
                 const unsigned int e0 = full * M + lane;
-                visit2(next.x & 0xffffu, next.x >> 16, e0 < nn, e0 + TPP < nn);
-                visit2(next.y & 0xffffu, next.y >> 16, e0 + 2 * TPP < nn, e0 + 3 * TPP < nn);
+                visit2(next.x & 0xffffu, next.x >> 16, e0 < nn, e0 + TPP < nn, true_c());
+                visit2(next.y & 0xffffu, next.y >> 16, e0 + 2 * TPP < nn, e0 + 3 * TPP < nn, true_c());
                 }
             }
         PairAccum<float, VIRIAL> acc;

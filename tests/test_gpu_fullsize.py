@@ -10,7 +10,8 @@ TwoPatchMorse particles (C4a), tile-staged kernels, float — are held to
   * the reference itself (oracle/_ref: the reference's evaluator headers, Scalar = float, OpenMP over particles) on the
     neighbour list the GPU built: per-particle forces (and torques) within 1e-5 of max(|f_i|, rms|f|). A particle may exceed
     that only if it owns a listed pair within 2e-6 of r_cut^2, where two float pipelines may disagree on membership; every
-    outlier is checked for exactly that, and there must be few of them.
+    outlier is checked for exactly that, and at most 1e-5 of the particles may be such outliers (observed on the B200 box:
+    none in any of the full-size cases, profiles/r2_parity_fullsize.json).
 """
 
 import numpy as np
@@ -114,7 +115,7 @@ def test_c2_dpd_full_size():
     par, rcsq, _, _ = _tables(cases.SPEC_BY_API["DPDGeneralWeight"], W.DPD_PARAMS, 1.0, snap.types)
     hs.dpd(par, rcsq, seed=42, timestep=5, dt=0.01, kT=1.0, nthreads=bench.os.cpu_count() or 1, which="ref")
     # s = 2: the weight is linear at the cutoff, so a membership flip moves the force by ~1e-6 only; few outliers expected
-    worst, n_bad = _compare("c2/dpd", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-4)
+    worst, n_bad = _compare("c2/dpd", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(f, hs)
     bench_report("c2_dpd_1M", worst, n_bad)
 
@@ -128,7 +129,7 @@ def test_plj_4m_full_size():
     par, rcsq, ronsq, _ = _tables(spec, W.PLJ_PARAMS, 3.0, snap.types)
     hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=bench.os.cpu_count() or 1, which="ref")
     # mode none: the pair energy and force jump at r_cut, so a membership flip is visible
-    worst, n_bad = _compare("plj4m", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    worst, n_bad = _compare("plj4m", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(f, hs)
     v = f._virial[:, : snap.N].double().sum(dim=1).cpu().numpy()
     v_ref = hs.virial[:, : snap.N].astype(np.float64).sum(axis=1)
@@ -143,8 +144,8 @@ def test_c4_patchy_full_size():
     _third_law(f)
     par, rcsq, _, _ = _tables(cases.SPEC_BY_API["TwoPatchMorse"], W.TPM_PARAMS, 1.6, snap.types)
     hs.aniso(par, rcsq, nthreads=bench.os.cpu_count() or 1, which="ref")
-    worst, n_bad = _compare("c4/patchy/force", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
-    worst_t, n_bad_t = _compare("c4/patchy/torque", f._torque[:, :3].cpu().numpy(), hs.torque[:, :3], hs, rcsq, 2e-3)
+    worst, n_bad = _compare("c4/patchy/force", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
+    worst_t, n_bad_t = _compare("c4/patchy/torque", f._torque[:, :3].cpu().numpy(), hs.torque[:, :3], hs, rcsq, 1e-5)
     _energy_sum(f, hs)
     bench_report("c4_patchy_2M", max(worst, worst_t), max(n_bad, n_bad_t))
 
@@ -161,7 +162,7 @@ def test_c4_mixture_full_size(workload):
     pdict, rc = W.hertz_tables() if workload == "hertz" else (W.COLLOID_PARAMS, W.COLLOID_RCUT)
     par, rcsq, ronsq, _ = _tables(spec, pdict, rc, snap.types)
     hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=bench.os.cpu_count() or 1, which="ref")
-    worst, n_bad = _compare(f"c4/{workload}", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    worst, n_bad = _compare(f"c4/{workload}", f._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(f, hs)
     bench_report(f"c4_{workload}", worst, n_bad)
 
@@ -191,7 +192,7 @@ def test_c3_melt_full_size():
     par, rcsq, ronsq, _ = _tables(spec, W.PLJ_PARAMS, 3.0, snap.types)
     _third_law(plj)
     hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=threads, which="ref")
-    worst, n_bad = _compare("c3/plj", plj._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    worst, n_bad = _compare("c3/plj", plj._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(plj, hs)
     bench_report("c3_melt_plj", worst, n_bad)
     table = build_bond_table(snap.N, snap.N, snap.bond_group, snap.bond_typeid)
@@ -226,13 +227,13 @@ def test_c5_eydpd_full_size():
     _third_law(ey)
     par, rcsq, _, _ = _tables(cases.SPEC_BY_API["DPDGeneralWeight"], W.C5_DPD_PARAMS, 1.0, snap.types)
     hs.dpd(par, rcsq, seed=42, timestep=5, dt=0.01, kT=1.0, nthreads=threads, which="ref")
-    worst, n_bad = _compare("c5/dpd", dpd._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-4)
+    worst, n_bad = _compare("c5/dpd", dpd._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(dpd, hs)
     bench_report("c5_dpd_8M", worst, n_bad)
     spec = cases.SPEC_BY_API["ExpandedYukawa"]
     par, rcsq, ronsq, _ = _tables(spec, W.EY_PARAMS, 2.0, snap.types)
     hs.pair(spec.potential_id, par, rcsq, ronsq, compute_virial=True, nthreads=threads, which="ref")
-    worst, n_bad = _compare("c5/ey", ey._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 2e-3)
+    worst, n_bad = _compare("c5/ey", ey._force[:, :3].cpu().numpy(), hs.force[:, :3], hs, rcsq, 1e-5)
     _energy_sum(ey, hs)
     v = ey._virial[:, : snap.N].double().sum(dim=1).cpu().numpy()
     v_ref = hs.virial[:, : snap.N].astype(np.float64).sum(axis=1)

@@ -54,7 +54,9 @@ def _check(name, f, hs, bits, torque=False, virial=True, ambiguous_rel=2e-6):
     if bits == 32 and getattr(hs, "nlist", None) is not None and hasattr(hs, "_rcutsq"):
         amb = GC.cutoff_ambiguous(hs, hs._rcutsq, rel=ambiguous_rel)
         out["skipped_cutoff_ambiguous"] = int(amb.sum())
-        assert amb.sum() <= 5 + (5e-3 if ambiguous_rel < 1e-5 else 5e-2) * len(amb)
+        # allowance = 2x what was observed (profiles/r2_parity_report.json: at most 8 of 32 000 and 2 of 6 000 particles for the
+        # 2e-6 window, 50 of 6 000 for the 2e-4 window of DPD with s = 0.5)
+        assert amb.sum() <= (4 + 5e-4 * len(amb) if ambiguous_rel < 1e-5 else 2e-2 * len(amb)), (name, int(amb.sum()), len(amb))
         if amb.any():
             f, hs = _Masked(f, ~amb, False), _Masked(hs, ~amb, True)
     e_f, i = GC.error_metrics(f.forces, hs.force[:, :3])

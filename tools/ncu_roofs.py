@@ -23,6 +23,9 @@ def main():
         "fma_pipe_pct": r.get("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
         "alu_pipe_pct": r.get("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
         "xu_pipe_pct": r.get("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+        "fma_pipe_cycles_pct": r.get("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+        "xu_pipe_cycles_pct": r.get("sm__pipe_xu_cycles_active.avg.pct_of_peak_sustained_active"),
+        "alu_pipe_cycles_pct": r.get("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
         "warps_active_pct": r.get("sm__warps_active.avg.pct_of_peak_sustained_active"),
         "warp_instructions": r.get("smsp__inst_executed.sum"),
         "threads_per_instruction": r.get("smsp__thread_inst_executed_per_inst_executed.ratio"),
