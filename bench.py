@@ -635,6 +635,12 @@ def roofs_from_profile(workload, bits, roofline, kernel):
         roofline["roofs_source"] = r.get("source")
         fracs["issue"] = roofline["issue_frac"]
         fracs["l1_smem"] = roofline["l1_smem_frac"]
+        # cycles the FMA pipe is held (an FFMA2 holds it for two and counts once as an instruction) and the XU pipe (MUFU: 16 lanes
+        # per clock and SM, tools/microbench/mufu.cu), when the capture has them
+        if r.get("fma_pipe_cycles_pct") is not None:
+            roofline["fma_pipe_frac"] = fracs["fma_pipe"] = r["fma_pipe_cycles_pct"] / 100.0
+        if r.get("xu_pipe_pct") is not None:
+            roofline["xu_pipe_frac"] = fracs["xu_pipe"] = r["xu_pipe_pct"] / 100.0
     else:
         roofline["issue_frac"] = roofline["l1_smem_frac"] = None
         roofline["roofs_source"] = "no ncu capture committed for this workload / precision"
