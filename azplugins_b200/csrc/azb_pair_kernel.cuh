@@ -312,6 +312,27 @@ __device__ __forceinline__ void stage_rows(V4* __restrict__ dst, const V4* __res
         }
     }
 
+// The next block's slot packet, requested where the statement stands: as a plain __ldg the compiler sinks the load to the end of
+// a branch-free loop body (its result is only used one iteration later), which turns it into a blocking load — 13 % of the
+// kernel's stall samples in the first capture of the interior-tile walk.
+__device__ __forceinline__ uint2 ldg_packet_here(const uint2* p)
+    {
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+    }
+
+// Is the particle at p (inside the box, as HOOMD keeps its local particles) farther than the cutoff from every PERIODIC face?
+// Then none of its in-range pairs crosses a face: a pair whose minimum image is shorter than r_cut but whose raw separation
+// differs from it by a box edge would need |p| > L / 2 - r_cut in that direction. Thresholds L / 2 - 1.01 r_cut, recomputed per
+// call (per row) rather than kept in registers across the walk. rcutsq > 0.
+template<class S, class V4> __device__ __forceinline__ bool away_from_periodic_faces(const Box<S>& box, const V4& p, const S rcutsq)
+    {
+    const S margin = S(1.01) * rcutsq * rsqrt_(rcutsq);
+    return ((box.flags & 1u) == 0u || fabs(p.x) < S(0.5) * box.Lx - margin) & ((box.flags & 2u) == 0u || fabs(p.y) < S(0.5) * box.Ly - margin)
+           & ((box.flags & 4u) == 0u || fabs(p.z) < S(0.5) * box.Lz - margin);
+    }
+
 template<class Pot, class S, int SHIFT, bool VIRIAL, int TPP, bool FASTBOX, bool SINGLE>
 __global__ void __launch_bounds__(256) pair_tile_kernel(const PairArgsDev<S> a, const TilePlanDev plan,
                                                         const typename Pot::template Params<S>* __restrict__ params, const S wrap_sq)

@@ -147,7 +147,9 @@ typedef struct azb_pair_args
     size_t virial_pitch;           /* >= N */
     unsigned int N;                /* local particles */
     unsigned int n_max;            /* N + ghosts */
-    const void* d_pos;             /* Scalar4[n_max] */
+    const void* d_pos;             /* Scalar4[n_max]; as in HOOMD, the N local particles lie inside the box in its periodic directions
+                                      (ghosts beyond it only where the box is not periodic): the packed ExpandedYukawa kernel skips
+                                      the minimum-image test for particles farther than r_cut from every periodic face */
     const void* d_charge;          /* unused (needsCharge() == false for every azplugins evaluator) */
     azb_box box;
     const unsigned int* d_n_neigh; /* [N] */

@@ -1,4 +1,4 @@
-# round 2, GPU call AI: final state — whole GPU suite, smoke, both bench arms as the driver runs them, launch list of the default bench
+# round 2, GPU call AI (re-run after the ExpandedYukawa face test): final state — whole GPU suite, smoke, both bench arms as the driver runs them, launch list of the default bench
 cd /root/repo; mkdir -p gpurun_out
 ( time python -m pytest tests -x -q -m gpu -s ) > gpurun_out/ai_tests.log 2>&1
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/ai_smoke.log 2>&1
