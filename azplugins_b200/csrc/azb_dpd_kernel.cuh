@@ -645,8 +645,9 @@ __global__ void __launch_bounds__(256)
                 while (k < nn && cnt + 4u <= DPD_STACK_CAP)
                     {
                     const unsigned int sl[4] = {pk.x & 0xffffu, pk.x >> 16, pk.y & 0xffffu, pk.y >> 16};
-                    if (k + 4u * TPP < nn) // my next block, one pass ahead
-                        pk = __ldg(reinterpret_cast<const uint2*>(row + k + 4u * TPP));
+                    if (k + 4u * TPP < nn) // my next block, one pass ahead (as a plain __ldg the compiler moves the load across the
+                                           // back edge to the top of the NEXT pass, next to its use: 15 % of the kernel's stall samples)
+                        pk = ldg_packet_here(reinterpret_cast<const uint2*>(row + k + 4u * TPP));
                     bool in[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)

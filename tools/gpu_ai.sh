@@ -14,3 +14,4 @@ for o in d.get("others",[]): print(o.get("workload","")[:50], o.get("ms_per_step
 print("f64", d["f64"]["ms_per_step"], "amortised", d["amortised"]["ms_per_step"], d["amortised"]["md_step_ms"])
 PY
 tail -3 gpurun_out/ai_bench.err gpurun_out/ai_ref.err
+ncu --set full --clock-control none --import-source on -k regex:"packed_pair_tile_kernel" --launch-skip 2 --launch-count 1 -o gpurun_out/ai_ey -f python bench.py --steps 3 --warmup 3 --no-extras --no-cpu-baseline > gpurun_out/ai_ncu1.log 2>&1
