@@ -23,6 +23,25 @@ import torch
 from . import _abi
 
 
+def chunk_edges(n_rows, chunks, taper=(0.08, 0.04, 0.02)):
+    """Row boundaries of the input chunks. What a step pays after its last input byte is the last launch and the copy of that
+    launch's output rows, and the last launch holds every tile whose highest input row sits in the LAST chunk: that chunk's own
+    tiles, the layer of tiles below it and the tiles on the periodic boundary. So the chunks shrink towards the end — the last
+    ``len(taper)`` chunks hold these fractions of the rows, the others share the rest equally — and the tail shrinks with them
+    (8 equal chunks: 22 % of the tiles in the last launch; tapered: ~9 %). ``taper=()`` gives equal chunks."""
+    K = max(1, int(chunks))
+    taper = tuple(taper)[-(K - 1):] if K > 1 else ()
+    if len(taper) and K - len(taper) >= 1:
+        head = np.linspace(0.0, 1.0 - float(sum(taper)), K - len(taper) + 1)
+        frac = np.concatenate([head, head[-1] + np.cumsum(taper)])
+        frac[-1] = 1.0
+    else:
+        frac = np.linspace(0.0, 1.0, K + 1)
+    edges = np.round(frac * n_rows).astype(np.int64)
+    edges[0], edges[-1] = 0, n_rows
+    return np.maximum.accumulate(edges)
+
+
 def plan_schedule(hi, in_edges, tile_size, N, out_blocks_per_chunk=8, late=None):
     """Pure host logic of the pipelined step (no device access; tests/test_hostio_schedule.py).
 
@@ -85,7 +104,7 @@ class HostStep:
     """``HostStep(force_or_forces, chunks)``: several tile-staged force objects over the same particles and the same neighbour
     list (C5: DPD + ExpandedYukawa) are evaluated by the same launch ranges of one ``azb_host_step`` call."""
 
-    def __init__(self, force, chunks=8, halo=None):
+    def __init__(self, force, chunks=8, halo=None, taper=(0.08, 0.04, 0.02)):
         """``halo``: the ``domain.HaloExchange`` of a decomposed state. The step then pipelines across the ghost exchange too:
         the tiles that read no ghost run as their host inputs arrive, the halo waits only for the last input chunk, and the
         tiles on the domain boundary (and the output rows they own) follow behind it on a side stream."""
@@ -98,6 +117,7 @@ class HostStep:
         self.forces = forces
         self.force = forces[0]
         self.chunks = int(chunks)
+        self.taper = tuple(taper)  # chunk_edges: the last chunks' shares of the rows; () = equal chunks
         st = self.force._state
         dev = st.device
         self.s_in = torch.cuda.Stream(dev)
@@ -160,7 +180,7 @@ class HostStep:
             return
         plan = plans[0]
         K = max(1, min(self.chunks, plan.n_tiles))
-        in_edges = np.linspace(0, st.N, K + 1).astype(np.int64)
+        in_edges = chunk_edges(st.N, K, self.taper)
         hi = self._tile_hi(plan, st.N)
         for p in plans[1:]:
             if p.uniq is not plan.uniq:

@@ -56,6 +56,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--min-seconds", type=float, default=0.6, help="the K-step block is repeated until the timed region is this long (clock sampling)")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="chunks of the pipelined host step (1 = copy, compute, copy)")
+    ap.add_argument("--e2e-taper", default="8,4,2", help="shares (percent of the rows) of the LAST input chunks of the pipelined host step, "
+                    "e.g. 8,4,2; 'none' = equal chunks (hostio.chunk_edges)")
     return ap.parse_args()
 
 
@@ -844,7 +846,8 @@ def run_b200(args):
     tiled = [f for f in forces if getattr(f, "_plan", None) is not None]
     plain = [f for f in forces if f not in tiled]
     pipelined = args.e2e_chunks > 1 and len(tiled) >= 1
-    hs = HostStep(tiled if pipelined else forces[:1], chunks=args.e2e_chunks, halo=halo)
+    taper = () if args.e2e_taper in ("none", "") else tuple(float(x) / 100.0 for x in args.e2e_taper.split(","))
+    hs = HostStep(tiled if pipelined else forces[:1], chunks=args.e2e_chunks, halo=halo, taper=taper)
     rest = plain if pipelined else forces[1:]
     extra_out = [f._force for f in rest]
     pinned_in = hs.pinned_inputs()
@@ -893,7 +896,7 @@ def run_b200(args):
             raise RuntimeError("pipelined host step and plain launch disagree")
     line["e2e"] = {"value": n_total * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": e2e_ms / K,
-                   "note": (f"pipelined in {args.e2e_chunks} chunks: pinned host pos(+vel/orientation) -> device, tile-range launches of "
+                   "note": (f"pipelined in {args.e2e_chunks} chunks (the last ones hold {args.e2e_taper} % of the rows): pinned host pos(+vel/orientation) -> device, tile-range launches of "
                             f"{len(tiled)} force object(s) as inputs arrive"
                             + (", ghost exchange behind the last input chunk, then the tiles that read ghosts" if halo is not None else "")
                             + ", force(+torque) arrays -> pinned host; checked bit-identical to the plain launches"

@@ -84,3 +84,28 @@ def test_degenerate_sizes():
     _check([31, 40, 40], np.array([0, 10, 20, 41]), 16, 41)  # ragged last tile, empty readiness classes
     order, launches, outs = _check(np.arange(8) * 4 + 3, np.linspace(0, 32, 9).astype(np.int64), 4, 32)
     assert len(launches) == 8 and order.tolist() == list(range(8))  # no look-ahead: tile c runs right after chunk c
+
+
+def test_tapered_chunk_edges():
+    """chunk_edges: ascending, covering [0, n_rows], the last chunks holding the tapered shares; the schedule's invariants hold on
+    them, and the last launch of a periodic raster is smaller than with equal chunks."""
+    from azplugins_b200.hostio import chunk_edges
+
+    for n_rows, K in ((1000, 8), (8_001_504, 8), (37, 8), (5, 8), (1000, 1), (1000, 2), (1000, 3), (1000, 4)):
+        e = chunk_edges(n_rows, K)
+        assert len(e) == K + 1 and e[0] == 0 and e[-1] == n_rows and np.all(np.diff(e) >= 0)
+    e = chunk_edges(1_000_000, 8)
+    assert abs((e[-1] - e[-2]) / 1e6 - 0.02) < 1e-3 and abs((e[-2] - e[-3]) / 1e6 - 0.04) < 1e-3 and abs((e[-3] - e[-4]) / 1e6 - 0.08) < 1e-3
+    assert np.array_equal(chunk_edges(1000, 4, taper=()), np.linspace(0, 1000, 5).astype(np.int64))
+    # a raster of 29 layers of 100 tiles: a tile reads up to one layer above it, the first layer wraps around to the last one
+    tile_size, layers, per = 128, 29, 100
+    n_tiles = layers * per
+    N = n_tiles * tile_size
+    t = np.arange(n_tiles)
+    hi = np.minimum((t // per + 2) * per * tile_size, N) - 1
+    hi[:per] = N - 1
+    last = {}
+    for name, edges in (("equal", chunk_edges(N, 8, taper=())), ("tapered", chunk_edges(N, 8))):
+        order, launches, outs = _check(hi, edges, tile_size, N)
+        last[name] = launches[-1][2]
+    assert last["tapered"] <= 0.5 * last["equal"], last
